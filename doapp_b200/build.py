@@ -1,0 +1,72 @@
+"""Build the sm_100a shared library in-tree (doapp_b200/lib/libdoapp_b200.so).
+
+nvcc cross-compiles without a GPU; the built .so is git-ignored but travels to
+the GPU box with the gpurun snapshot.
+"""
+from __future__ import annotations
+
+import os
+import shutil
+import subprocess
+import sys
+
+PKG = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(PKG)
+CSRC = os.path.join(PKG, "csrc")
+LIB_DIR = os.path.join(PKG, "lib")
+LIB = os.path.join(LIB_DIR, "libdoapp_b200.so")
+HOST_LIB = os.path.join(LIB_DIR, "libdoapp_planning_state.so")
+HOST_TEST = os.path.join(LIB_DIR, "planning_state_test")
+
+NVCC_FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
+    "-fmad=false",  # every FMA in the kernels is written explicitly (parity with the oracle)
+    "-Xcompiler", "-fPIC,-fvisibility=hidden,-ffp-contract=off",
+]
+
+
+def _nvcc() -> str:
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    if not os.path.exists(nvcc):
+        raise RuntimeError("nvcc not found: the CUDA library cannot be built")
+    return nvcc
+
+
+def _stale(target: str, sources: list[str]) -> bool:
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(s) > t for s in sources)
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    os.makedirs(LIB_DIR, exist_ok=True)
+    cu = [os.path.join(CSRC, f) for f in ("kernels.cu", "doapp_capi.cu")]
+    deps = cu + [os.path.join(CSRC, f) for f in ("kernels.cuh", "device_math.cuh")] + \
+        [os.path.join(ROOT, "include", "doapp", "doapp.h")]
+    if force or _stale(LIB, deps):
+        cmd = [_nvcc(), *NVCC_FLAGS, "-shared", "-I", os.path.join(ROOT, "include"), "-I", CSRC,
+               *cu, "-o", LIB, "-ldl"]
+        if verbose:
+            cmd.insert(1, "-Xptxas=-v")
+        subprocess.run(cmd, check=True)
+    host_dir = os.path.join(PKG, "host")
+    host_src = os.path.join(host_dir, "planning_state.cpp")
+    if os.path.exists(host_src):
+        hdeps = [host_src, os.path.join(host_dir, "planning_state.hpp"),
+                 os.path.join(host_dir, "ros_mirror.hpp"), LIB]
+        cxx = shutil.which("g++") or "g++"
+        common = ["-O2", "-std=c++17", "-fPIC", "-I", os.path.join(ROOT, "include"), "-I", host_dir]
+        if force or _stale(HOST_LIB, hdeps):
+            subprocess.run([cxx, *common, "-shared", host_src, "-o", HOST_LIB, "-L", LIB_DIR,
+                            "-ldoapp_b200", "-Wl,-rpath,$ORIGIN"], check=True)
+        test_src = os.path.join(host_dir, "planning_state_test.cpp")
+        if os.path.exists(test_src) and (force or _stale(HOST_TEST, hdeps + [test_src, HOST_LIB])):
+            subprocess.run([cxx, *common, test_src, "-o", HOST_TEST, "-L", LIB_DIR,
+                            "-ldoapp_planning_state", "-ldoapp_b200", "-Wl,-rpath,$ORIGIN"],
+                           check=True)
+    return LIB
+
+
+if __name__ == "__main__":
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

@@ -1,0 +1,330 @@
+"""ctypes binding of include/doapp/doapp.h.
+
+This is the Python-side stub a test or a bench uses to reach the C ABI; it adds
+no logic of its own (numpy arrays in, numpy arrays out) and never falls back to
+a CPU path: if the shared library is missing or no CUDA device is present the
+calls raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_PKG, "lib", "libdoapp_b200.so")
+
+OK, INVALID_ARG, CUDA_ERROR, NCCL_ERROR, OOM, NOT_READY = range(6)
+COLLISION_AS_SHIPPED, COLLISION_INTENDED = 0, 1
+SELECT_CEIL_INT, SELECT_FLOAT = 0, 1
+UPDATE_KEEP_BEST, UPDATE_WEIGHTED = 0, 1
+GRID_NONE, GRID_U8, GRID_F32 = 0, 1, 2
+FRAME_CDG, FRAME_OG = 0, 1
+COMM_ID_BYTES = 128
+
+# every symbol include/doapp/doapp.h declares (checked by tests/test_abi.py)
+ABI_SYMBOLS = [
+    "doapp_config_init", "doapp_version", "doapp_status_str", "doapp_create", "doapp_destroy",
+    "doapp_last_error", "doapp_grid_alloc", "doapp_grid_upload", "doapp_grid_download",
+    "doapp_grid_from_msg", "doapp_grid_scatter", "doapp_grid_scatter_dev", "doapp_grid_lookup",
+    "doapp_set_limits", "doapp_noise_generate", "doapp_cost_eval", "doapp_stage_inputs",
+    "doapp_cost_eval_dev", "doapp_read_results", "doapp_plan_lerp", "doapp_plan",
+    "doapp_plan_async", "doapp_plan_wait", "doapp_plan_state", "doapp_replan_dynamic",
+    "doapp_plan_bench", "doapp_comm_unique_id", "doapp_comm_init", "doapp_grid_broadcast",
+    "doapp_launch_count", "doapp_debug_sincos", "doapp_debug_fk",
+]
+
+
+class Config(C.Structure):
+    _fields_ = [
+        ("struct_size", C.c_uint32), ("device", C.c_int32), ("num_climbers", C.c_uint32),
+        ("samples_per_climber", C.c_uint32), ("num_waypoints", C.c_uint32),
+        ("waypoint_dim", C.c_uint32), ("noise_waypoints", C.c_uint32), ("delta_t", C.c_float),
+        ("smooth_scale", C.c_float), ("collision_distance", C.c_float),
+        ("collision_mode", C.c_int32), ("select_mode", C.c_int32), ("update_mode", C.c_int32),
+        ("update_gain", C.c_float), ("limit_weight", C.c_float), ("sigma", C.c_float),
+        ("seed", C.c_uint64), ("sample_offset", C.c_uint64),
+        ("global_samples_per_climber", C.c_uint64),
+    ]
+
+
+class DoappError(RuntimeError):
+    def __init__(self, status: int, message: str):
+        super().__init__(f"doapp status {status}: {message}")
+        self.status = status
+        self.message = message
+
+
+_lib = None
+
+
+def load_library(path: str | None = None) -> C.CDLL:
+    """dlopen the in-tree CUDA library; raises if it has not been built."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    p = path or LIB_PATH
+    if not os.path.exists(p):
+        raise FileNotFoundError(
+            f"{p} not found: build it with `python -m doapp_b200.build` (no CPU fallback exists)")
+    L = C.CDLL(p)
+    vp, f32p = C.c_void_p, C.c_void_p
+    L.doapp_config_init.argtypes = [C.POINTER(Config)]
+    L.doapp_config_init.restype = None
+    L.doapp_version.restype = C.c_uint32
+    L.doapp_status_str.argtypes = [C.c_int]
+    L.doapp_status_str.restype = C.c_char_p
+    L.doapp_create.argtypes = [C.POINTER(Config), C.POINTER(vp)]
+    L.doapp_destroy.argtypes = [vp]
+    L.doapp_destroy.restype = None
+    L.doapp_last_error.argtypes = [vp]
+    L.doapp_last_error.restype = C.c_char_p
+    L.doapp_grid_alloc.argtypes = [vp, C.c_int32, C.c_int32, C.c_uint32, C.c_uint32, C.c_uint32,
+                                   C.c_double]
+    L.doapp_grid_upload.argtypes = [vp, vp, C.c_size_t]
+    L.doapp_grid_download.argtypes = [vp, vp, C.c_size_t]
+    L.doapp_grid_from_msg.argtypes = [vp, C.c_double, C.c_double, vp, C.c_size_t]
+    L.doapp_grid_scatter.argtypes = [vp, f32p, C.c_size_t, C.c_int8, C.c_int]
+    L.doapp_grid_scatter_dev.argtypes = [vp, vp, C.c_size_t, C.c_int8, C.c_int]
+    L.doapp_grid_lookup.argtypes = [vp, f32p, C.c_size_t, vp, vp]
+    L.doapp_set_limits.argtypes = [vp, f32p, f32p]
+    L.doapp_noise_generate.argtypes = [vp, C.c_uint32, f32p]
+    L.doapp_cost_eval.argtypes = [vp, f32p, f32p, f32p, C.c_uint32, f32p, vp, vp, vp]
+    L.doapp_stage_inputs.argtypes = [vp, f32p, f32p, f32p]
+    L.doapp_cost_eval_dev.argtypes = [vp, C.c_uint32, C.c_int, C.c_uint32, vp]
+    L.doapp_read_results.argtypes = [vp, f32p, vp, vp, vp]
+    L.doapp_plan_lerp.argtypes = [f32p, f32p, C.c_uint32, C.c_uint32, f32p]
+    L.doapp_plan.argtypes = [vp, f32p, f32p, f32p, C.c_uint32, f32p, f32p, f32p, vp, vp]
+    L.doapp_plan_async.argtypes = [vp, f32p, f32p, f32p, C.c_uint32, f32p]
+    L.doapp_plan_wait.argtypes = [vp, f32p, f32p, vp, vp]
+    L.doapp_plan_state.argtypes = [vp, f32p, f32p, vp, vp]
+    L.doapp_replan_dynamic.argtypes = [vp, f32p, f32p, f32p, C.c_uint32, f32p, C.c_size_t, f32p,
+                                       vp, vp]
+    L.doapp_plan_bench.argtypes = [vp, C.c_uint32, C.c_uint32, vp]
+    L.doapp_comm_unique_id.argtypes = [vp]
+    L.doapp_comm_init.argtypes = [vp, vp, C.c_int32, C.c_int32]
+    L.doapp_grid_broadcast.argtypes = [vp, C.c_int32]
+    L.doapp_launch_count.argtypes = [vp]
+    L.doapp_launch_count.restype = C.c_uint64
+    L.doapp_debug_sincos.argtypes = [vp, f32p, C.c_size_t, f32p, f32p]
+    L.doapp_debug_fk.argtypes = [vp, f32p, C.c_size_t, f32p]
+    if path is None:
+        _lib = L
+    return L
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def _f32(a):
+    return None if a is None else np.ascontiguousarray(a, dtype=np.float32)
+
+
+def default_config() -> Config:
+    cfg = Config()
+    load_library().doapp_config_init(C.byref(cfg))
+    return cfg
+
+
+def plan_lerp(start, goal, n: int) -> np.ndarray:
+    start, goal = _f32(start), _f32(goal)
+    out = np.empty((n, start.shape[0]), np.float32)
+    st = load_library().doapp_plan_lerp(_p(start), _p(goal), n, start.shape[0], _p(out))
+    if st != OK:
+        raise DoappError(st, "doapp_plan_lerp")
+    return out
+
+
+def comm_unique_id() -> bytes:
+    buf = (C.c_uint8 * COMM_ID_BYTES)()
+    st = load_library().doapp_comm_unique_id(buf)
+    if st != OK:
+        raise DoappError(st, load_library().doapp_last_error(None).decode())
+    return bytes(buf)
+
+
+class Context:
+    """One doapp_ctx: owns the device buffers of one (k, m, n, d) problem on one GPU."""
+
+    def __init__(self, k=1, m=1024, n=64, d=5, n_noise=1, device=0, **kw):
+        self.L = load_library()
+        cfg = default_config()
+        cfg.device = device
+        cfg.num_climbers, cfg.samples_per_climber = k, m
+        cfg.num_waypoints, cfg.waypoint_dim, cfg.noise_waypoints = n, d, n_noise
+        for key, val in kw.items():
+            if not hasattr(cfg, key):
+                raise AttributeError(key)
+            setattr(cfg, key, val)
+        self.cfg = cfg
+        self.k, self.m, self.n, self.d, self.n_noise = k, m, n, d, n_noise
+        self.m_global = cfg.global_samples_per_climber or m
+        h = C.c_void_p()
+        st = self.L.doapp_create(C.byref(cfg), C.byref(h))
+        if st != OK:
+            raise DoappError(st, self.L.doapp_last_error(None).decode())
+        self.h = h
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.doapp_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def _ck(self, st):
+        if st != OK:
+            raise DoappError(st, self.L.doapp_last_error(self.h).decode())
+
+    # -- world model -------------------------------------------------------
+    def set_grid(self, cells: np.ndarray, resolution: float, frame=FRAME_CDG):
+        """cells indexed [iz, iy, ix]; uint8/int8 -> occupancy, float32 -> distance."""
+        assert cells.ndim == 3
+        kind = GRID_F32 if cells.dtype == np.float32 else GRID_U8
+        cells = np.ascontiguousarray(cells if kind == GRID_F32 else cells.astype(np.uint8))
+        nz, ny, nx = cells.shape
+        self._ck(self.L.doapp_grid_alloc(self.h, kind, frame, nx, ny, nz, resolution))
+        self._ck(self.L.doapp_grid_upload(self.h, _p(cells), cells.size))
+
+    def grid_alloc(self, kind, frame, nx, ny, nz, resolution):
+        self._ck(self.L.doapp_grid_alloc(self.h, kind, frame, nx, ny, nz, resolution))
+        self._grid_shape = (nz, ny, nx)
+        self._grid_dtype = np.float32 if kind == GRID_F32 else np.uint8
+
+    def grid_from_msg(self, size: float, granularity: float, grid: np.ndarray):
+        grid = np.ascontiguousarray(grid, dtype=np.int8)
+        self._ck(self.L.doapp_grid_from_msg(self.h, size, granularity, _p(grid), grid.size))
+
+    def grid_download(self, shape, dtype=np.uint8) -> np.ndarray:
+        out = np.empty(shape, dtype)
+        self._ck(self.L.doapp_grid_download(self.h, _p(out), out.size))
+        return out
+
+    def scatter(self, xyz, val=1, clear_first=True):
+        xyz = _f32(xyz).reshape(-1, 3)
+        self._ck(self.L.doapp_grid_scatter(self.h, _p(xyz), xyz.shape[0], val, int(clear_first)))
+
+    def grid_lookup(self, xyz):
+        xyz = _f32(xyz).reshape(-1, 3)
+        idx = np.empty(xyz.shape[0], np.int64)
+        col = np.empty(xyz.shape[0], np.uint8)
+        self._ck(self.L.doapp_grid_lookup(self.h, _p(xyz), xyz.shape[0], _p(idx), _p(col)))
+        return idx, col
+
+    def set_limits(self, lo, hi):
+        lo, hi = _f32(lo), _f32(hi)
+        self._ck(self.L.doapp_set_limits(self.h, _p(lo), _p(hi)))
+
+    # -- stages ------------------------------------------------------------
+    def noise(self, iteration=0) -> np.ndarray:
+        out = np.empty((self.k, self.m, self.n_noise, self.d), np.float32)
+        self._ck(self.L.doapp_noise_generate(self.h, iteration, _p(out)))
+        return out
+
+    def cost_eval(self, base_traj, start, noise=None, iteration=0):
+        base_traj, start, noise = _f32(base_traj), _f32(start), _f32(noise)
+        assert base_traj.size == self.k * self.n * self.d
+        if noise is not None:
+            assert noise.size == self.k * self.m * self.n_noise * self.d
+        scores = np.empty((self.k, self.m), np.float32)
+        coll = np.empty((self.k, self.m), np.int32)
+        am, mn = C.c_int64(), C.c_float()
+        self._ck(self.L.doapp_cost_eval(self.h, _p(base_traj), _p(start), _p(noise), iteration,
+                                        _p(scores), _p(coll), C.addressof(am), C.addressof(mn)))
+        return dict(scores=scores, collisions=coll, argmin=am.value, min_score=mn.value)
+
+    def stage_inputs(self, base_traj, start, noise=None):
+        base_traj, start, noise = _f32(base_traj), _f32(start), _f32(noise)
+        self._ck(self.L.doapp_stage_inputs(self.h, _p(base_traj), _p(start), _p(noise)))
+
+    def cost_eval_dev(self, iteration=0, use_staged_noise=False, repeats=1) -> float:
+        ms = C.c_float()
+        self._ck(self.L.doapp_cost_eval_dev(self.h, iteration, int(use_staged_noise), repeats,
+                                            C.addressof(ms)))
+        return ms.value
+
+    def read_results(self, want_arrays=True):
+        scores = np.empty((self.k, self.m), np.float32) if want_arrays else None
+        coll = np.empty((self.k, self.m), np.int32) if want_arrays else None
+        am, mn = C.c_int64(), C.c_float()
+        self._ck(self.L.doapp_read_results(self.h, _p(scores), _p(coll), C.addressof(am),
+                                           C.addressof(mn)))
+        return dict(scores=scores, collisions=coll, argmin=am.value, min_score=mn.value)
+
+    # -- planner -----------------------------------------------------------
+    def plan(self, start, goal, init_traj, iters, noise=None):
+        self.plan_async(start, goal, init_traj, iters, noise)
+        return self.plan_wait()
+
+    def plan_async(self, start, goal, init_traj, iters, noise=None):
+        start, goal, init_traj, noise = _f32(start), _f32(goal), _f32(init_traj), _f32(noise)
+        assert init_traj.size == self.n * self.d
+        if noise is not None:
+            assert noise.size == iters * self.k * self.m_global * self.n_noise * self.d
+        self._keep = (start, goal, init_traj, noise)
+        self._ck(self.L.doapp_plan_async(self.h, _p(start), _p(goal), _p(init_traj), iters,
+                                         _p(noise)))
+
+    def plan_wait(self):
+        bt, bv = np.empty((self.n, self.d), np.float32), np.empty((self.n, self.d), np.float32)
+        bs, bc = C.c_float(), C.c_int64()
+        self._ck(self.L.doapp_plan_wait(self.h, _p(bt), _p(bv), C.addressof(bs), C.addressof(bc)))
+        return dict(best_traj=bt, best_vel=bv, best_score=bs.value, best_climber=bc.value)
+
+    def plan_state(self):
+        tr = np.empty((self.k, self.n, self.d), np.float32)
+        sc, rd = np.empty(self.k, np.float32), np.empty(self.k, np.int32)
+        fb = np.empty(self.k, np.uint8)
+        self._ck(self.L.doapp_plan_state(self.h, _p(tr), _p(sc), _p(rd), _p(fb)))
+        return dict(trajectories=tr, scores=sc, rounded=rd, found_better=fb)
+
+    def plan_bench(self, iters, repeats=1) -> float:
+        ms = C.c_float()
+        self._ck(self.L.doapp_plan_bench(self.h, iters, repeats, C.addressof(ms)))
+        return ms.value
+
+    def replan_dynamic(self, start, goal, init_traj, clouds):
+        start, goal, init_traj, clouds = _f32(start), _f32(goal), _f32(init_traj), _f32(clouds)
+        iters, npts = clouds.shape[0], clouds.shape[1]
+        bt = np.empty((self.n, self.d), np.float32)
+        bs, ms = C.c_float(), C.c_float()
+        self._ck(self.L.doapp_replan_dynamic(self.h, _p(start), _p(goal), _p(init_traj), iters,
+                                             _p(clouds), npts, _p(bt), C.addressof(bs),
+                                             C.addressof(ms)))
+        return dict(best_traj=bt, best_score=bs.value, elapsed_ms=ms.value)
+
+    # -- multi-GPU ---------------------------------------------------------
+    def comm_init(self, uid: bytes, rank: int, nranks: int):
+        buf = (C.c_uint8 * COMM_ID_BYTES).from_buffer_copy(uid)
+        self._ck(self.L.doapp_comm_init(self.h, buf, rank, nranks))
+
+    def grid_broadcast(self, root=0):
+        self._ck(self.L.doapp_grid_broadcast(self.h, root))
+
+    # -- introspection -----------------------------------------------------
+    def launch_count(self) -> int:
+        return int(self.L.doapp_launch_count(self.h))
+
+    def debug_sincos(self, x):
+        x = _f32(np.atleast_1d(x))
+        s, c = np.empty_like(x), np.empty_like(x)
+        self._ck(self.L.doapp_debug_sincos(self.h, _p(x), x.size, _p(s), _p(c)))
+        return s, c
+
+    def debug_fk(self, waypoints):
+        wp = _f32(waypoints).reshape(-1, self.d)
+        out = np.empty((wp.shape[0], 5, 3), np.float32)
+        self._ck(self.L.doapp_debug_fk(self.h, _p(wp), wp.shape[0], _p(out)))
+        return out

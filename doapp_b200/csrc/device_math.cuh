@@ -1,0 +1,210 @@
+// device_math.cuh — deterministic elementary functions and Philox for the
+// sm_100a kernels.  Written from the specification in DESIGN.md ("deterministic
+// math spec"); the oracle holds an independent C restatement of the same spec
+// and tests/test_parity_gpu.py compares the two bit for bit.
+//
+// The reference calls std::sin / std::cos on the device
+// (perturbator/src/generate_trajectories.cu:304-305) and curand_normal
+// (:297-299); both are replaced here: sin/cos because CUDA's and glibc's
+// results differ in the last ulp (which flips voxel indices), cuRAND by the
+// counter-based Philox4x32-10 the north star asks for.
+#pragma once
+
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+
+#if defined(__CUDACC__)
+#define DM_HD __host__ __device__ __forceinline__
+#else
+#define DM_HD inline
+#endif
+
+namespace dm {
+
+// single-rounding helpers: immune to -fmad / host FP contraction settings
+DM_HD float fma_(float a, float b, float c) {
+#if defined(__CUDA_ARCH__)
+  return __fmaf_rn(a, b, c);
+#else
+  return fmaf(a, b, c);
+#endif
+}
+DM_HD float mul_(float a, float b) {
+#if defined(__CUDA_ARCH__)
+  return __fmul_rn(a, b);
+#else
+  volatile float r = a * b;
+  return r;
+#endif
+}
+DM_HD float add_(float a, float b) {
+#if defined(__CUDA_ARCH__)
+  return __fadd_rn(a, b);
+#else
+  volatile float r = a + b;
+  return r;
+#endif
+}
+DM_HD float sub_(float a, float b) {
+#if defined(__CUDA_ARCH__)
+  return __fsub_rn(a, b);
+#else
+  volatile float r = a - b;
+  return r;
+#endif
+}
+DM_HD float div_(float a, float b) {
+#if defined(__CUDA_ARCH__)
+  return __fdiv_rn(a, b);
+#else
+  volatile float r = a / b;
+  return r;
+#endif
+}
+
+constexpr float kTwoOverPi = 0x1.45f306p-1f;
+constexpr float kP1 = 0x1.921fb6p+0f;   // RN(pi/2)
+constexpr float kP2 = -0x1.777a5cp-25f; // RN(pi/2 - P1)
+constexpr float kP3 = -0x1.ee59dap-50f; // RN(pi/2 - P1 - P2)
+constexpr double kTwoOverPiD = 0x1.45f306dc9c883p-1;
+constexpr double kTwoPiD = 0x1.921fb54442d18p+2;
+constexpr double kP1D = 0x1.921fb54442d18p+0;
+constexpr double kP2D = 0x1.1a62633145c07p-54;
+constexpr float kS1 = -1.6666654611e-1f, kS2 = 8.3321608736e-3f, kS3 = -1.9515295891e-4f;
+constexpr float kC1 = 4.166664568298827e-2f, kC2 = -1.388731625493765e-3f,
+                kC3 = 2.443315711809948e-5f;
+
+// Cold path: |x| >= 2^17, inf or nan.
+#if defined(__CUDACC__)
+__host__ __device__ __noinline__
+#else
+inline
+#endif
+    void
+    sincos_slow(float x, float *r_out, int *q_out) {
+  double xd = fmod((double)x, kTwoPiD);
+  double kd = rint(xd * kTwoOverPiD);
+  double rd = fma(-kd, kP1D, xd);
+  rd = fma(-kd, kP2D, rd);
+  *r_out = (float)rd;
+  *q_out = (int)kd & 3;
+}
+
+DM_HD void sincos(float x, float *s, float *c) {
+  float r;
+  int q;
+  if (fabsf(x) < 131072.0f) {
+    float t = mul_(x, kTwoOverPi);
+    float kf = rintf(t);
+    r = fma_(-kf, kP1, x);
+    r = fma_(-kf, kP2, r);
+    r = fma_(-kf, kP3, r);
+    q = (int)kf & 3;
+  } else if (x != x || fabsf(x) == INFINITY) {
+    *s = NAN;
+    *c = NAN;
+    return;
+  } else {
+    sincos_slow(x, &r, &q);
+  }
+  float z = mul_(r, r);
+  float ps = fma_(kS3, z, kS2);
+  ps = fma_(ps, z, kS1);
+  ps = mul_(ps, z);
+  float sin_r = fma_(ps, r, r);
+  float pc = fma_(kC3, z, kC2);
+  pc = fma_(pc, z, kC1);
+  pc = fma_(pc, z, -0.5f);
+  float cos_r = fma_(pc, z, 1.0f);
+  float sa = (q & 1) ? cos_r : sin_r;
+  float ca = (q & 1) ? sin_r : cos_r;
+  *s = (q & 2) ? -sa : sa;
+  *c = ((q + 1) & 2) ? -ca : ca;
+}
+
+// natural log on (0, 1]
+DM_HD float log_(float x) {
+#if defined(__CUDA_ARCH__)
+  uint32_t ix = __float_as_uint(x);
+#else
+  uint32_t ix;
+  memcpy(&ix, &x, 4);
+#endif
+  ix += 0x3f800000u - 0x3f3504f3u;
+  int e = (int)(ix >> 23) - 127;
+  ix = (ix & 0x007fffffu) + 0x3f3504f3u;
+#if defined(__CUDA_ARCH__)
+  float mant = __uint_as_float(ix);
+#else
+  float mant;
+  memcpy(&mant, &ix, 4);
+#endif
+  float f = sub_(mant, 1.0f);
+  float z = mul_(f, f);
+  float p = 7.0376836292e-2f;
+  p = fma_(p, f, -1.1514610310e-1f);
+  p = fma_(p, f, 1.1676998740e-1f);
+  p = fma_(p, f, -1.2420140846e-1f);
+  p = fma_(p, f, 1.4249322787e-1f);
+  p = fma_(p, f, -1.6668057665e-1f);
+  p = fma_(p, f, 2.0000714765e-1f);
+  p = fma_(p, f, -2.4999993993e-1f);
+  p = fma_(p, f, 3.3333331174e-1f);
+  float y = mul_(mul_(f, z), p);
+  float fe = (float)e;
+  y = fma_(fe, -2.12194440e-4f, y);
+  y = fma_(-0.5f, z, y);
+  float r = add_(f, y);
+  r = fma_(fe, 0.693359375f, r);
+  return r;
+}
+
+struct u4 {
+  uint32_t x, y, z, w;
+};
+
+DM_HD u4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0,
+                       uint32_t k1) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+#if defined(__CUDA_ARCH__)
+    uint32_t h0 = __umulhi(0xD2511F53u, c0), l0 = 0xD2511F53u * c0;
+    uint32_t h1 = __umulhi(0xCD9E8D57u, c2), l1 = 0xCD9E8D57u * c2;
+#else
+    uint64_t p0 = (uint64_t)0xD2511F53u * c0, p1 = (uint64_t)0xCD9E8D57u * c2;
+    uint32_t h0 = (uint32_t)(p0 >> 32), l0 = (uint32_t)p0;
+    uint32_t h1 = (uint32_t)(p1 >> 32), l1 = (uint32_t)p1;
+#endif
+    uint32_t n0 = h1 ^ c1 ^ k0;
+    uint32_t n2 = h0 ^ c3 ^ k1;
+    c0 = n0;
+    c1 = l1;
+    c2 = n2;
+    c3 = l0;
+    k0 += 0x9E3779B9u;
+    k1 += 0xBB67AE85u;
+  }
+  return u4{c0, c1, c2, c3};
+}
+
+// one N(0, sigma^2) draw from two Philox words: cos branch for even joints
+DM_HD float box_muller(uint32_t a, uint32_t b, bool want_sin, float sigma) {
+  float u1 = mul_((float)((a >> 8) + 1u), 0x1p-24f);
+  float u2 = mul_((float)(b >> 8), 0x1p-24f);
+  float rad = sqrtf(mul_(-2.0f, log_(u1)));
+  float s, c;
+  sincos(mul_(u2, 0x1.921fb6p+2f), &s, &c);
+  return mul_(sigma, mul_(rad, want_sin ? s : c));
+}
+
+// noise element (climber c, global sample t, noise waypoint wn, joint j)
+DM_HD float noise_at(uint32_t seed_lo, uint32_t seed_hi, float sigma, uint32_t iteration,
+                     uint32_t c, uint32_t t_global, uint32_t wn, uint32_t j) {
+  u4 r = philox4x32_10(t_global, c, wn, 2u * iteration + (j >> 2), seed_lo, seed_hi);
+  uint32_t a = (j & 2u) ? r.z : r.x;
+  uint32_t b = (j & 2u) ? r.w : r.y;
+  return box_muller(a, b, (j & 1u) != 0, sigma);
+}
+
+} // namespace dm

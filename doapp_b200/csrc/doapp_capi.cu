@@ -1,0 +1,1133 @@
+// doapp_capi.cu — implementation of the C ABI declared in include/doapp/doapp.h.
+//
+// Host side of the hot path: owns every device buffer (plain cudaMalloc; the
+// reference uses cudaMallocManaged for everything, vector.cuh:142-167), stages
+// inputs, enqueues the kernels of kernels.cu on one stream per ctx — the whole
+// planner loop as a single CUDA graph — and reads results back.  There is no
+// CPU fallback: without a device doapp_create fails.
+#include "doapp/doapp.h"
+
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <dlfcn.h>
+#include <new>
+#include <string>
+#include <vector>
+
+#include <cuda_runtime.h>
+#include <nccl.h>
+
+#include "kernels.cuh"
+
+using namespace doapp;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+struct NcclApi {
+  void *handle = nullptr;
+  ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+  ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t,
+                            cudaStream_t) = nullptr;
+  ncclResult_t (*Broadcast)(const void *, void *, size_t, ncclDataType_t, int, ncclComm_t,
+                            cudaStream_t) = nullptr;
+  const char *(*GetErrorString)(ncclResult_t) = nullptr;
+};
+
+NcclApi *nccl_api(std::string *err) {
+  static NcclApi api;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    // torch's bundled libnccl.so.2 is reused when it is already mapped
+    api.handle = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!api.handle) api.handle = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (api.handle) {
+      api.GetUniqueId = (decltype(api.GetUniqueId))dlsym(api.handle, "ncclGetUniqueId");
+      api.CommInitRank = (decltype(api.CommInitRank))dlsym(api.handle, "ncclCommInitRank");
+      api.CommDestroy = (decltype(api.CommDestroy))dlsym(api.handle, "ncclCommDestroy");
+      api.AllReduce = (decltype(api.AllReduce))dlsym(api.handle, "ncclAllReduce");
+      api.Broadcast = (decltype(api.Broadcast))dlsym(api.handle, "ncclBroadcast");
+      api.GetErrorString = (decltype(api.GetErrorString))dlsym(api.handle, "ncclGetErrorString");
+    }
+  }
+  if (!api.handle || !api.GetUniqueId || !api.CommInitRank || !api.AllReduce || !api.Broadcast) {
+    if (err) *err = "libnccl.so.2 not loadable";
+    return nullptr;
+  }
+  return &api;
+}
+
+template <typename T> struct DevBuf {
+  T *p = nullptr;
+  size_t cap = 0; // elements
+};
+
+} // namespace
+
+struct doapp_ctx {
+  doapp_config cfg{};
+  int sm_count = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  std::string err;
+  uint64_t launches = 0;
+
+  uint32_t npad = 0;
+  uint64_t S = 0; // local samples per iteration
+  uint64_t m_global = 0;
+
+  DevBuf<float> traj, aos_tmp, start, noise, scores, final_scores, out, cloud, pts;
+  DevBuf<int32_t> coll, final_coll;
+  DevBuf<unsigned long long> keys, keys_float;
+  DevBuf<uint32_t> cur_hi;
+  DevBuf<uint8_t> found, grid_cells, lookup_coll;
+  DevBuf<long long> lookup_idx;
+  DevBuf<float> dbg_a, dbg_b, dbg_c;
+
+  GridDev grid{};
+  size_t grid_bytes = 0;
+  uint64_t grid_generation = 0;
+
+  float lim_min[kMaxJoints]{}, lim_max[kMaxJoints]{};
+  int use_limits = 0;
+  float rpy_s = 0.0f, rpy_c = 0.0f;
+
+  // staged planner inputs
+  bool plan_staged = false, plan_pending = false;
+  int plan_noise_mode = NOISE_PHILOX;
+  uint32_t plan_iters = 0;
+
+  // cached CUDA graph of the planner loop
+  cudaGraphExec_t graph_exec = nullptr;
+  uint32_t graph_iters = 0;
+  int graph_noise_mode = -1;
+  const float *graph_noise_ptr = nullptr;
+  uint64_t graph_grid_generation = ~0ull;
+  uint64_t graph_kernels = 0;
+  bool use_graph = true;
+
+  ncclComm_t comm = nullptr;
+  int rank = 0, nranks = 1;
+
+  std::vector<float> h_out;
+};
+
+namespace {
+
+doapp_status fail(doapp_ctx *ctx, doapp_status st, const char *fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  if (ctx)
+    ctx->err = buf;
+  else
+    g_create_error = buf;
+  return st;
+}
+
+#define CU(call)                                                                                  \
+  do {                                                                                            \
+    cudaError_t e_ = (call);                                                                      \
+    if (e_ != cudaSuccess)                                                                        \
+      return fail(ctx, e_ == cudaErrorMemoryAllocation ? DOAPP_OOM : DOAPP_CUDA_ERROR,            \
+                  "%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_));             \
+  } while (0)
+
+#define ST(call)                                                                                  \
+  do {                                                                                            \
+    doapp_status s_ = (call);                                                                     \
+    if (s_ != DOAPP_OK) return s_;                                                                \
+  } while (0)
+
+template <typename T> doapp_status ensure(doapp_ctx *ctx, DevBuf<T> &b, size_t elems) {
+  if (elems <= b.cap && b.p) return DOAPP_OK;
+  if (b.p) {
+    CU(cudaStreamSynchronize(ctx->stream));
+    CU(cudaFree(b.p));
+    b.p = nullptr;
+    b.cap = 0;
+  }
+  if (elems == 0) elems = 1;
+  CU(cudaMalloc((void **)&b.p, elems * sizeof(T)));
+  b.cap = elems;
+  return DOAPP_OK;
+}
+
+template <typename T> void release(DevBuf<T> &b) {
+  if (b.p) cudaFree(b.p);
+  b.p = nullptr;
+  b.cap = 0;
+}
+
+void invalidate_graph(doapp_ctx *ctx) {
+  if (ctx->graph_exec) {
+    cudaGraphExecDestroy(ctx->graph_exec);
+    ctx->graph_exec = nullptr;
+  }
+}
+
+CostParams base_cost_params(doapp_ctx *ctx) {
+  const doapp_config &c = ctx->cfg;
+  CostParams p{};
+  p.traj = ctx->traj.p;
+  p.start = ctx->start.p;
+  p.k = c.num_climbers;
+  p.m = c.samples_per_climber;
+  p.n = c.num_waypoints;
+  p.npad = ctx->npad;
+  p.n_noise = c.noise_waypoints;
+  p.seed_lo = (uint32_t)c.seed;
+  p.seed_hi = (uint32_t)(c.seed >> 32);
+  p.sigma = c.sigma;
+  p.sample_offset = c.sample_offset;
+  p.m_global = ctx->m_global;
+  p.dt = c.delta_t;
+  p.smooth_scale = c.smooth_scale;
+  p.coll_dist = c.collision_distance;
+  p.limit_weight = c.limit_weight;
+  for (int j = 0; j < kMaxJoints; ++j) {
+    p.lim_min[j] = ctx->lim_min[j];
+    p.lim_max[j] = ctx->lim_max[j];
+  }
+  p.use_limits = ctx->use_limits;
+  p.collision_mode = c.collision_mode;
+  p.select_mode = c.select_mode;
+  p.rpy_s = ctx->rpy_s;
+  p.rpy_c = ctx->rpy_c;
+  p.grid = ctx->grid;
+  p.total_samples = ctx->S;
+  return p;
+}
+
+// cost pass over the k kept trajectories themselves (zero noise, one "sample"
+// per climber): generate_trajectories.cu:180-191.
+CostParams climber_cost_params(doapp_ctx *ctx) {
+  CostParams p = base_cost_params(ctx);
+  p.m = 1;
+  p.noise_mode = NOISE_ZERO;
+  p.noise = nullptr;
+  p.n_noise = 1;
+  p.sample_offset = 0;
+  p.m_global = 1;
+  p.total_samples = ctx->cfg.num_climbers;
+  return p;
+}
+
+doapp_status upload_traj(doapp_ctx *ctx, const float *host_aos, bool broadcast_first) {
+  const doapp_config &c = ctx->cfg;
+  size_t rows = broadcast_first ? 1 : c.num_climbers;
+  size_t elems = rows * c.num_waypoints * c.waypoint_dim;
+  ST(ensure(ctx, ctx->aos_tmp, (size_t)c.num_climbers * c.num_waypoints * c.waypoint_dim));
+  CU(cudaMemcpyAsync(ctx->aos_tmp.p, host_aos, elems * sizeof(float), cudaMemcpyHostToDevice,
+                     ctx->stream));
+  CU(launch_aos_to_soa(ctx->aos_tmp.p, ctx->traj.p, c.num_climbers, c.num_waypoints, ctx->npad,
+                       c.waypoint_dim, broadcast_first ? 1 : 0, ctx->stream));
+  ctx->launches += 1;
+  return DOAPP_OK;
+}
+
+doapp_status upload_start(doapp_ctx *ctx, const float *start) {
+  CU(cudaMemcpyAsync(ctx->start.p, start, ctx->cfg.waypoint_dim * sizeof(float),
+                     cudaMemcpyHostToDevice, ctx->stream));
+  return DOAPP_OK;
+}
+
+// Enqueue the planner loop (no host synchronisation inside): initial scoring,
+// `iters` x (cost -> [all-reduce] -> update), final scoring and selection.
+doapp_status enqueue_plan(doapp_ctx *ctx, uint32_t iters, int noise_mode, uint64_t *kernels) {
+  const doapp_config &c = ctx->cfg;
+  uint64_t nk = 0;
+  NcclApi *nccl = ctx->comm ? nccl_api(nullptr) : nullptr;
+  CU(cudaMemsetAsync(ctx->keys.p, 0xFF, sizeof(unsigned long long) * c.num_climbers, ctx->stream));
+  // score the unperturbed trajectories -> cur_hi
+  {
+    CostParams p = climber_cost_params(ctx);
+    p.keys = ctx->keys.p;
+    CU(launch_cost(p, c.waypoint_dim, ctx->sm_count, ctx->stream));
+    UpdateParams u{};
+    u.k = c.num_climbers;
+    u.n = c.num_waypoints;
+    u.npad = ctx->npad;
+    u.d = c.waypoint_dim;
+    u.keys = ctx->keys.p;
+    u.cur_hi = ctx->cur_hi.p;
+    u.found_better = ctx->found.p;
+    u.init = 1;
+    CU(launch_update(u, ctx->stream));
+    nk += 2;
+  }
+  const size_t noise_iter_stride =
+      (size_t)c.num_climbers * ctx->m_global * c.noise_waypoints * c.waypoint_dim;
+  for (uint32_t it = 0; it < iters; ++it) {
+    CostParams p = base_cost_params(ctx);
+    p.noise_mode = noise_mode;
+    p.iteration = it;
+    if (noise_mode == NOISE_EXTERNAL) {
+      p.noise = ctx->noise.p + (size_t)it * noise_iter_stride;
+      p.noise_m = ctx->m_global;
+      p.noise_t0 = 0;
+    }
+    p.keys = ctx->keys.p;
+    CU(launch_cost(p, c.waypoint_dim, ctx->sm_count, ctx->stream));
+    if (nccl) {
+      ncclResult_t r = nccl->AllReduce(ctx->keys.p, ctx->keys.p, c.num_climbers, ncclUint64,
+                                       ncclMin, ctx->comm, ctx->stream);
+      if (r != ncclSuccess)
+        return fail(ctx, DOAPP_NCCL_ERROR, "ncclAllReduce: %s",
+                    nccl->GetErrorString ? nccl->GetErrorString(r) : "error");
+    }
+    UpdateParams u{};
+    u.traj = ctx->traj.p;
+    u.noise = p.noise;
+    u.noise_m = p.noise_m;
+    u.noise_t0 = p.noise_t0;
+    u.noise_mode = noise_mode;
+    u.k = c.num_climbers;
+    u.n = c.num_waypoints;
+    u.npad = ctx->npad;
+    u.d = c.waypoint_dim;
+    u.n_noise = c.noise_waypoints;
+    u.iteration = it;
+    u.seed_lo = (uint32_t)c.seed;
+    u.seed_hi = (uint32_t)(c.seed >> 32);
+    u.sigma = c.sigma;
+    u.keys = ctx->keys.p;
+    u.cur_hi = ctx->cur_hi.p;
+    u.found_better = ctx->found.p;
+    u.init = 0;
+    CU(launch_update(u, ctx->stream));
+    nk += 2;
+  }
+  // final float score of every kept trajectory, then the host-style argmin
+  {
+    CostParams p = climber_cost_params(ctx);
+    p.scores = ctx->final_scores.p;
+    p.collisions = ctx->final_coll.p;
+    CU(launch_cost(p, c.waypoint_dim, ctx->sm_count, ctx->stream));
+    FinalParams f{};
+    f.traj = ctx->traj.p;
+    f.start = ctx->start.p;
+    f.scores = ctx->final_scores.p;
+    f.found_better = ctx->found.p;
+    f.k = c.num_climbers;
+    f.n = c.num_waypoints;
+    f.npad = ctx->npad;
+    f.d = c.waypoint_dim;
+    f.dt = c.delta_t;
+    f.out = ctx->out.p;
+    CU(launch_final(f, ctx->stream));
+    nk += 2;
+  }
+  if (kernels) *kernels = nk;
+  return DOAPP_OK;
+}
+
+// restore every climber to the staged initial trajectory (device copy kept in aos_tmp)
+doapp_status reset_climbers(doapp_ctx *ctx) {
+  const doapp_config &c = ctx->cfg;
+  CU(launch_aos_to_soa(ctx->aos_tmp.p, ctx->traj.p, c.num_climbers, c.num_waypoints, ctx->npad,
+                       c.waypoint_dim, 1, ctx->stream));
+  ctx->launches += 1;
+  return DOAPP_OK;
+}
+
+doapp_status run_plan(doapp_ctx *ctx, uint32_t iters, int noise_mode) {
+  if (!ctx->use_graph) {
+    uint64_t nk = 0;
+    ST(enqueue_plan(ctx, iters, noise_mode, &nk));
+    ctx->launches += nk;
+    return DOAPP_OK;
+  }
+  const float *nptr = noise_mode == NOISE_EXTERNAL ? ctx->noise.p : nullptr;
+  bool hit = ctx->graph_exec && ctx->graph_iters == iters && ctx->graph_noise_mode == noise_mode &&
+             ctx->graph_noise_ptr == nptr && ctx->graph_grid_generation == ctx->grid_generation;
+  if (!hit) {
+    invalidate_graph(ctx);
+    cudaGraph_t graph = nullptr;
+    CU(cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal));
+    uint64_t nk = 0;
+    doapp_status st = enqueue_plan(ctx, iters, noise_mode, &nk);
+    cudaError_t ce = cudaStreamEndCapture(ctx->stream, &graph);
+    if (st != DOAPP_OK) {
+      if (graph) cudaGraphDestroy(graph);
+      return st;
+    }
+    if (ce != cudaSuccess)
+      return fail(ctx, DOAPP_CUDA_ERROR, "cudaStreamEndCapture: %s", cudaGetErrorString(ce));
+    ce = cudaGraphInstantiate(&ctx->graph_exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (ce != cudaSuccess)
+      return fail(ctx, DOAPP_CUDA_ERROR, "cudaGraphInstantiate: %s", cudaGetErrorString(ce));
+    ctx->graph_iters = iters;
+    ctx->graph_noise_mode = noise_mode;
+    ctx->graph_noise_ptr = nptr;
+    ctx->graph_grid_generation = ctx->grid_generation;
+    ctx->graph_kernels = nk;
+  }
+  CU(cudaGraphLaunch(ctx->graph_exec, ctx->stream));
+  ctx->launches += ctx->graph_kernels;
+  return DOAPP_OK;
+}
+
+} // namespace
+
+// ======================================================================= ABI
+
+extern "C" {
+
+void doapp_config_init(doapp_config *cfg) {
+  if (!cfg) return;
+  memset(cfg, 0, sizeof(*cfg));
+  cfg->struct_size = sizeof(doapp_config);
+  cfg->device = 0;
+  cfg->num_climbers = 1;
+  cfg->samples_per_climber = 1024;
+  cfg->num_waypoints = 64;
+  cfg->waypoint_dim = 5;
+  cfg->noise_waypoints = 1;
+  cfg->delta_t = 0.1f;
+  cfg->smooth_scale = 0.25f;
+  cfg->collision_distance = 0.05f;
+  cfg->collision_mode = DOAPP_COLLISION_INTENDED;
+  cfg->select_mode = DOAPP_SELECT_CEIL_INT;
+  cfg->update_mode = DOAPP_UPDATE_KEEP_BEST;
+  cfg->update_gain = 10000.0f;
+  cfg->limit_weight = 0.0f;
+  cfg->sigma = 1.0f;
+  cfg->seed = 1234;
+  cfg->sample_offset = 0;
+  cfg->global_samples_per_climber = 0;
+}
+
+uint32_t doapp_version(void) { return DOAPP_ABI_VERSION; }
+
+const char *doapp_status_str(doapp_status s) {
+  switch (s) {
+  case DOAPP_OK: return "OK";
+  case DOAPP_INVALID_ARG: return "INVALID_ARG";
+  case DOAPP_CUDA_ERROR: return "CUDA_ERROR";
+  case DOAPP_NCCL_ERROR: return "NCCL_ERROR";
+  case DOAPP_OOM: return "OOM";
+  case DOAPP_NOT_READY: return "NOT_READY";
+  }
+  return "UNKNOWN";
+}
+
+const char *doapp_last_error(const doapp_ctx *ctx) {
+  return ctx ? ctx->err.c_str() : g_create_error.c_str();
+}
+
+doapp_status doapp_create(const doapp_config *cfg, doapp_ctx **out) {
+  doapp_ctx *ctx = nullptr; // for the CU/fail macros: create errors go to the thread-local slot
+  if (!cfg || !out) return fail(nullptr, DOAPP_INVALID_ARG, "doapp_create: null argument");
+  *out = nullptr;
+  if (cfg->struct_size != sizeof(doapp_config))
+    return fail(nullptr, DOAPP_INVALID_ARG, "doapp_create: struct_size %u != %zu",
+                cfg->struct_size, sizeof(doapp_config));
+  if (cfg->num_climbers == 0 || cfg->samples_per_climber == 0)
+    return fail(nullptr, DOAPP_INVALID_ARG, "doapp_create: k and m must be > 0");
+  if (cfg->num_waypoints == 0 || cfg->num_waypoints > 1024)
+    return fail(nullptr, DOAPP_INVALID_ARG, "doapp_create: num_waypoints must be in 1..1024");
+  if (cfg->waypoint_dim != 4 && cfg->waypoint_dim != 5)
+    return fail(nullptr, DOAPP_INVALID_ARG, "doapp_create: waypoint_dim must be 4 or 5");
+  if (cfg->noise_waypoints != 1 && cfg->noise_waypoints != cfg->num_waypoints)
+    return fail(nullptr, DOAPP_INVALID_ARG, "doapp_create: noise_waypoints must be 1 or n");
+  if (!(cfg->delta_t > 0.0f))
+    return fail(nullptr, DOAPP_INVALID_ARG, "doapp_create: delta_t must be > 0");
+  if (cfg->update_mode != DOAPP_UPDATE_KEEP_BEST)
+    return fail(nullptr, DOAPP_INVALID_ARG,
+                "doapp_create: only DOAPP_UPDATE_KEEP_BEST is implemented");
+  uint64_t mg = cfg->global_samples_per_climber ? cfg->global_samples_per_climber
+                                                : cfg->samples_per_climber;
+  if (cfg->sample_offset + cfg->samples_per_climber > mg || mg > 0xFFFFFFFFull)
+    return fail(nullptr, DOAPP_INVALID_ARG, "doapp_create: shard [%llu,+%u) outside m_global %llu",
+                (unsigned long long)cfg->sample_offset, cfg->samples_per_climber,
+                (unsigned long long)mg);
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return fail(nullptr, DOAPP_CUDA_ERROR,
+                "doapp_create: no CUDA device (%s); this library has no CPU fallback",
+                cudaGetErrorString(e));
+  if (cfg->device < 0 || cfg->device >= ndev)
+    return fail(nullptr, DOAPP_INVALID_ARG, "doapp_create: device %d of %d", cfg->device, ndev);
+  CU(cudaSetDevice(cfg->device));
+  ctx = new (std::nothrow) doapp_ctx();
+  if (!ctx) return fail(nullptr, DOAPP_OOM, "doapp_create: host allocation failed");
+  ctx->cfg = *cfg;
+  ctx->m_global = mg;
+  ctx->npad = (cfg->num_waypoints + 31u) & ~31u;
+  ctx->S = (uint64_t)cfg->num_climbers * cfg->samples_per_climber;
+  const char *ng = getenv("DOAPP_NO_GRAPH");
+  ctx->use_graph = !(ng && ng[0] == '1');
+  host_sincos(-1.5707963267948966f, &ctx->rpy_s, &ctx->rpy_c);
+  doapp_status st = [&]() -> doapp_status {
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, cfg->device));
+    ctx->sm_count = prop.multiProcessorCount;
+    CU(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    CU(cudaEventCreate(&ctx->ev0));
+    CU(cudaEventCreate(&ctx->ev1));
+    const size_t k = cfg->num_climbers, n = cfg->num_waypoints, d = cfg->waypoint_dim;
+    ST(ensure(ctx, ctx->traj, k * d * ctx->npad));
+    ST(ensure(ctx, ctx->aos_tmp, k * n * d));
+    ST(ensure(ctx, ctx->start, 8));
+    ST(ensure(ctx, ctx->scores, ctx->S));
+    ST(ensure(ctx, ctx->coll, ctx->S));
+    ST(ensure(ctx, ctx->final_scores, k));
+    ST(ensure(ctx, ctx->final_coll, k));
+    ST(ensure(ctx, ctx->keys, k));
+    ST(ensure(ctx, ctx->keys_float, k));
+    ST(ensure(ctx, ctx->cur_hi, k));
+    ST(ensure(ctx, ctx->found, k));
+    ST(ensure(ctx, ctx->out, 4 + 2 * n * d));
+    CU(cudaMemsetAsync(ctx->traj.p, 0, sizeof(float) * k * d * ctx->npad, ctx->stream));
+    CU(cudaMemsetAsync(ctx->start.p, 0, sizeof(float) * 8, ctx->stream));
+    CU(cudaMemsetAsync(ctx->found.p, 0, k, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return DOAPP_OK;
+  }();
+  if (st != DOAPP_OK) {
+    g_create_error = ctx->err;
+    doapp_destroy(ctx);
+    return st;
+  }
+  ctx->h_out.resize(4 + 2 * (size_t)cfg->num_waypoints * cfg->waypoint_dim);
+  *out = ctx;
+  return DOAPP_OK;
+}
+
+void doapp_destroy(doapp_ctx *ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->cfg.device);
+  if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+  invalidate_graph(ctx);
+  if (ctx->comm) {
+    NcclApi *api = nccl_api(nullptr);
+    if (api && api->CommDestroy) api->CommDestroy(ctx->comm);
+  }
+  release(ctx->traj); release(ctx->aos_tmp); release(ctx->start); release(ctx->noise);
+  release(ctx->scores); release(ctx->final_scores); release(ctx->out); release(ctx->cloud);
+  release(ctx->pts); release(ctx->coll); release(ctx->final_coll); release(ctx->keys);
+  release(ctx->keys_float); release(ctx->cur_hi); release(ctx->found); release(ctx->grid_cells);
+  release(ctx->lookup_coll); release(ctx->lookup_idx); release(ctx->dbg_a); release(ctx->dbg_b);
+  release(ctx->dbg_c);
+  if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+  if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+  if (ctx->stream) cudaStreamDestroy(ctx->stream);
+  delete ctx;
+}
+
+// ------------------------------------------------------------------ world model
+
+doapp_status doapp_grid_alloc(doapp_ctx *ctx, int32_t kind, int32_t frame, uint32_t nx,
+                              uint32_t ny, uint32_t nz, double resolution) {
+  if (!ctx) return DOAPP_INVALID_ARG;
+  if (kind != DOAPP_GRID_U8 && kind != DOAPP_GRID_F32)
+    return fail(ctx, DOAPP_INVALID_ARG, "doapp_grid_alloc: kind %d", kind);
+  if (frame != DOAPP_FRAME_CDG && frame != DOAPP_FRAME_OG)
+    return fail(ctx, DOAPP_INVALID_ARG, "doapp_grid_alloc: frame %d", frame);
+  if (nx == 0 || ny == 0 || nz == 0 || !(resolution > 0.0))
+    return fail(ctx, DOAPP_INVALID_ARG, "doapp_grid_alloc: empty grid or resolution <= 0");
+  if (frame == DOAPP_FRAME_OG && !(nx == ny && ny == nz))
+    return fail(ctx, DOAPP_INVALID_ARG, "doapp_grid_alloc: FRAME_OG grids are cubes");
+  CU(cudaSetDevice(ctx->cfg.device));
+  const size_t cells = (size_t)nx * ny * nz;
+  const size_t bytes = cells * (kind == DOAPP_GRID_F32 ? 4 : 1);
+  ST(ensure(ctx, ctx->grid_cells, bytes));
+  if (kind == DOAPP_GRID_U8) {
+    CU(cudaMemsetAsync(ctx->grid_cells.p, 0, bytes, ctx->stream)); // occupancy_grid.cpp:15-16
+  } else {
+    // +inf == 0x7f800000: fill through a host pattern (distance "nothing nearby")
+    std::vector<float> inf(cells, INFINITY);
+    CU(cudaMemcpyAsync(ctx->grid_cells.p, inf.data(), bytes, cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+  }
+  GridDev g{};
+  g.cells = ctx->grid_cells.p;
+  g.kind = kind;
+  g.frame = frame;
+  g.nx = nx;
+  g.ny = ny;
+  g.nz = nz;
+  g.res = (float)resolution;                                  // cpu_distance_grid.cu:69
+  g.x_off = (float)(0.5 * (double)nx * resolution);           // :70-71
+  g.y_off = (float)(0.5 * (double)ny * resolution);           // :72-73
+  g.z_max = (float)((double)nz * resolution);                 // :81-82
+  g.res_d = resolution;
+  g.half_d = ((double)nx * resolution) / 2.0;                 // occupancy_grid.cpp:31
+  ctx->grid = g;
+  ctx->grid_bytes = bytes;
+  ctx->grid_generation++;
+  return DOAPP_OK;
+}
+
+doapp_status doapp_grid_upload(doapp_ctx *ctx, const void *host_cells, size_t num_cells) {
+  if (!ctx) return DOAPP_INVALID_ARG;
+  if (!host_cells) return fail(ctx, DOAPP_INVALID_ARG, "doapp_grid_upload: null cells");
+  if (ctx->grid.kind == DOAPP_GRID_NONE) return fail(ctx, DOAPP_NOT_READY, "no grid allocated");
+  size_t cells = (size_t)ctx->grid.nx * ctx->grid.ny * ctx->grid.nz;
+  if (num_cells != cells)
+    return fail(ctx, DOAPP_INVALID_ARG, "doapp_grid_upload: %zu cells, grid has %zu", num_cells,
+                cells);
+  CU(cudaSetDevice(ctx->cfg.device));
+  CU(cudaMemcpyAsync(ctx->grid_cells.p, host_cells, ctx->grid_bytes, cudaMemcpyHostToDevice,
+                     ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  return DOAPP_OK;
+}
+
+doapp_status doapp_grid_download(doapp_ctx *ctx, void *host_cells, size_t num_cells) {
+  if (!ctx) return DOAPP_INVALID_ARG;
+  if (!host_cells) return fail(ctx, DOAPP_INVALID_ARG, "doapp_grid_download: null cells");
+  if (ctx->grid.kind == DOAPP_GRID_NONE) return fail(ctx, DOAPP_NOT_READY, "no grid allocated");
+  size_t cells = (size_t)ctx->grid.nx * ctx->grid.ny * ctx->grid.nz;
+  if (num_cells != cells)
+    return fail(ctx, DOAPP_INVALID_ARG, "doapp_grid_download: %zu cells, grid has %zu", num_cells,
+                cells);
+  CU(cudaSetDevice(ctx->cfg.device));
+  CU(cudaMemcpyAsync(host_cells, ctx->grid_cells.p, ctx->grid_bytes, cudaMemcpyDeviceToHost,
+                     ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  return DOAPP_OK;
+}
+
+doapp_status doapp_grid_from_msg(doapp_ctx *ctx, double size, double granularity,
+                                 const int8_t *grid, size_t len) {
+  if (!ctx) return DOAPP_INVALID_ARG;
+  if (!(size > 0.0) || !(granularity > 0.0) || !grid)
+    return fail(ctx, DOAPP_INVALID_ARG, "doapp_grid_from_msg: bad size/granularity/grid");
+  size_t n = (size_t)(size / granularity); // occupancy_grid.cpp:10
+  if (n == 0 || n > 2048) return fail(ctx, DOAPP_INVALID_ARG, "doapp_grid_from_msg: %zu cells/edge", n);
+  if (len != n * n * n)
+    return fail(ctx, DOAPP_INVALID_ARG, "doapp_grid_from_msg: len %zu != %zu^3", len, n);
+  bool same = ctx->grid.kind == DOAPP_GRID_U8 && ctx->grid.frame == DOAPP_FRAME_OG &&
+              ctx->grid.nx == n && ctx->grid.res_d == granularity;
+  if (!same)
+    ST(doapp_grid_alloc(ctx, DOAPP_GRID_U8, DOAPP_FRAME_OG, (uint32_t)n, (uint32_t)n, (uint32_t)n,
+                        granularity));
+  return doapp_grid_upload(ctx, grid, len);
+}
+
+doapp_status doapp_grid_scatter_dev(doapp_ctx *ctx, const float *xyz_dev, size_t num_points,
+                                    int8_t val, int clear_first) {
+  if (!ctx) return DOAPP_INVALID_ARG;
+  if (ctx->grid.kind != DOAPP_GRID_U8)
+    return fail(ctx, DOAPP_NOT_READY, "doapp_grid_scatter: needs a U8 grid");
+  if (num_points && !xyz_dev) return fail(ctx, DOAPP_INVALID_ARG, "doapp_grid_scatter: null cloud");
+  CU(cudaSetDevice(ctx->cfg.device));
+  if (clear_first) CU(cudaMemsetAsync(ctx->grid_cells.p, 0, ctx->grid_bytes, ctx->stream));
+  ScatterParams sp{};
+  sp.xyz = xyz_dev;
+  sp.num_points = num_points;
+  sp.grid = ctx->grid;
+  sp.cells = ctx->grid_cells.p;
+  sp.val = val;
+  CU(launch_scatter(sp, ctx->sm_count, ctx->stream));
+  if (num_points) ctx->launches += 1;
+  CU(cudaStreamSynchronize(ctx->stream));
+  return DOAPP_OK;
+}
+
+doapp_status doapp_grid_scatter(doapp_ctx *ctx, const float *xyz, size_t num_points, int8_t val,
+                                int clear_first) {
+  if (!ctx) return DOAPP_INVALID_ARG;
+  if (num_points && !xyz) return fail(ctx, DOAPP_INVALID_ARG, "doapp_grid_scatter: null cloud");
+  CU(cudaSetDevice(ctx->cfg.device));
+  ST(ensure(ctx, ctx->cloud, num_points * 3));
+  if (num_points)
+    CU(cudaMemcpyAsync(ctx->cloud.p, xyz, num_points * 3 * sizeof(float), cudaMemcpyHostToDevice,
+                       ctx->stream));
+  return doapp_grid_scatter_dev(ctx, ctx->cloud.p, num_points, val, clear_first);
+}
+
+doapp_status doapp_grid_lookup(doapp_ctx *ctx, const float *xyz, size_t num_points,
+                               int64_t *cell_index, uint8_t *collides) {
+  if (!ctx) return DOAPP_INVALID_ARG;
+  if (ctx->grid.kind == DOAPP_GRID_NONE) return fail(ctx, DOAPP_NOT_READY, "no grid allocated");
+  if (num_points == 0) return DOAPP_OK;
+  if (!xyz || !cell_index || !collides)
+    return fail(ctx, DOAPP_INVALID_ARG, "doapp_grid_lookup: null argument");
+  CU(cudaSetDevice(ctx->cfg.device));
+  ST(ensure(ctx, ctx->pts, num_points * 3));
+  ST(ensure(ctx, ctx->lookup_idx, num_points));
+  ST(ensure(ctx, ctx->lookup_coll, num_points));
+  CU(cudaMemcpyAsync(ctx->pts.p, xyz, num_points * 3 * sizeof(float), cudaMemcpyHostToDevice,
+                     ctx->stream));
+  CU(launch_lookup(ctx->grid, ctx->pts.p, num_points, ctx->cfg.collision_distance,
+                   ctx->lookup_idx.p, ctx->lookup_coll.p, ctx->stream));
+  ctx->launches += 1;
+  CU(cudaMemcpyAsync(cell_index, ctx->lookup_idx.p, num_points * sizeof(long long),
+                     cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaMemcpyAsync(collides, ctx->lookup_coll.p, num_points, cudaMemcpyDeviceToHost,
+                     ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  return DOAPP_OK;
+}
+
+doapp_status doapp_set_limits(doapp_ctx *ctx, const float *min_d, const float *max_d) {
+  if (!ctx) return DOAPP_INVALID_ARG;
+  if (!min_d || !max_d) {
+    ctx->use_limits = 0;
+  } else {
+    for (uint32_t j = 0; j < ctx->cfg.waypoint_dim; ++j) {
+      ctx->lim_min[j] = min_d[j];
+      ctx->lim_max[j] = max_d[j];
+    }
+    ctx->use_limits = 1;
+  }
+  invalidate_graph(ctx);
+  return DOAPP_OK;
+}
+
+// ----------------------------------------------------------------------- noise
+
+doapp_status doapp_noise_generate(doapp_ctx *ctx, uint32_t iteration, float *noise_out) {
+  if (!ctx) return DOAPP_INVALID_ARG;
+  if (!noise_out) return fail(ctx, DOAPP_INVALID_ARG, "doapp_noise_generate: null output");
+  CU(cudaSetDevice(ctx->cfg.device));
+  const doapp_config &c = ctx->cfg;
+  size_t total = (size_t)ctx->S * c.noise_waypoints * c.waypoint_dim;
+  ST(ensure(ctx, ctx->dbg_a, total));
+  CostParams p = base_cost_params(ctx);
+  p.iteration = iteration;
+  CU(launch_noise_fill(p, c.waypoint_dim, ctx->dbg_a.p, ctx->stream));
+  ctx->launches += 1;
+  CU(cudaMemcpyAsync(noise_out, ctx->dbg_a.p, total * sizeof(float), cudaMemcpyDeviceToHost,
+                     ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  return DOAPP_OK;
+}
+
+// ------------------------------------------------------------- cost evaluation
+
+doapp_status doapp_stage_inputs(doapp_ctx *ctx, const float *base_traj, const float *start,
+                                const float *noise) {
+  if (!ctx) return DOAPP_INVALID_ARG;
+  if (!base_traj || !start)
+    return fail(ctx, DOAPP_INVALID_ARG, "doapp_stage_inputs: null trajectory or start");
+  CU(cudaSetDevice(ctx->cfg.device));
+  const doapp_config &c = ctx->cfg;
+  ST(upload_traj(ctx, base_traj, false));
+  ST(upload_start(ctx, start));
+  if (noise) {
+    size_t total = (size_t)ctx->S * c.noise_waypoints * c.waypoint_dim;
+    ST(ensure(ctx, ctx->noise, total));
+    CU(cudaMemcpyAsync(ctx->noise.p, noise, total * sizeof(float), cudaMemcpyHostToDevice,
+                       ctx->stream));
+  }
+  CU(cudaStreamSynchronize(ctx->stream));
+  return DOAPP_OK;
+}
+
+static doapp_status enqueue_cost_eval(doapp_ctx *ctx, uint32_t iteration, int noise_mode) {
+  const doapp_config &c = ctx->cfg;
+  CU(cudaMemsetAsync(ctx->keys_float.p, 0xFF, sizeof(unsigned long long) * c.num_climbers,
+                     ctx->stream));
+  CostParams p = base_cost_params(ctx);
+  p.noise_mode = noise_mode;
+  p.iteration = iteration;
+  if (noise_mode == NOISE_EXTERNAL) {
+    p.noise = ctx->noise.p;
+    p.noise_m = c.samples_per_climber;
+    p.noise_t0 = c.sample_offset;
+  }
+  p.scores = ctx->scores.p;
+  p.collisions = ctx->coll.p;
+  p.keys_float = ctx->keys_float.p;
+  CU(launch_cost(p, c.waypoint_dim, ctx->sm_count, ctx->stream));
+  ctx->launches += 1;
+  return DOAPP_OK;
+}
+
+doapp_status doapp_read_results(doapp_ctx *ctx, float *scores, int32_t *collisions,
+                                int64_t *argmin, float *min_score) {
+  if (!ctx) return DOAPP_INVALID_ARG;
+  CU(cudaSetDevice(ctx->cfg.device));
+  const doapp_config &c = ctx->cfg;
+  std::vector<unsigned long long> keys(c.num_climbers);
+  if (scores)
+    CU(cudaMemcpyAsync(scores, ctx->scores.p, ctx->S * sizeof(float), cudaMemcpyDeviceToHost,
+                       ctx->stream));
+  if (collisions)
+    CU(cudaMemcpyAsync(collisions, ctx->coll.p, ctx->S * sizeof(int32_t), cudaMemcpyDeviceToHost,
+                       ctx->stream));
+  CU(cudaMemcpyAsync(keys.data(), ctx->keys_float.p, keys.size() * sizeof(unsigned long long),
+                     cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  // planning_state.cu:113-122 over the per-climber winners: strict <, first wins
+  float lowest = INFINITY;
+  int64_t best = -1;
+  for (uint32_t cl = 0; cl < c.num_climbers; ++cl) {
+    uint32_t hi = (uint32_t)(keys[cl] >> 32);
+    float sc;
+    memcpy(&sc, &hi, 4);
+    if (hi == 0xFFFFFFFFu) continue;
+    if (sc < lowest) {
+      lowest = sc;
+      best = (int64_t)((uint64_t)cl * ctx->m_global + (uint32_t)keys[cl]);
+    }
+  }
+  if (argmin) *argmin = best;
+  if (min_score) *min_score = lowest;
+  return DOAPP_OK;
+}
+
+doapp_status doapp_cost_eval(doapp_ctx *ctx, const float *base_traj, const float *start,
+                             const float *noise, uint32_t iteration, float *scores,
+                             int32_t *collisions, int64_t *argmin, float *min_score) {
+  if (!ctx) return DOAPP_INVALID_ARG;
+  ST(doapp_stage_inputs(ctx, base_traj, start, noise));
+  ST(enqueue_cost_eval(ctx, iteration, noise ? NOISE_EXTERNAL : NOISE_PHILOX));
+  return doapp_read_results(ctx, scores, collisions, argmin, min_score);
+}
+
+doapp_status doapp_cost_eval_dev(doapp_ctx *ctx, uint32_t iteration, int use_staged_noise,
+                                 uint32_t repeats, float *elapsed_ms) {
+  if (!ctx) return DOAPP_INVALID_ARG;
+  if (use_staged_noise && !ctx->noise.p)
+    return fail(ctx, DOAPP_NOT_READY, "doapp_cost_eval_dev: no staged noise");
+  CU(cudaSetDevice(ctx->cfg.device));
+  if (repeats == 0) repeats = 1;
+  CU(cudaEventRecord(ctx->ev0, ctx->stream));
+  for (uint32_t r = 0; r < repeats; ++r)
+    ST(enqueue_cost_eval(ctx, iteration, use_staged_noise ? NOISE_EXTERNAL : NOISE_PHILOX));
+  CU(cudaEventRecord(ctx->ev1, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  float ms = 0.0f;
+  CU(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+  if (elapsed_ms) *elapsed_ms = ms;
+  return DOAPP_OK;
+}
+
+// --------------------------------------------------------------------- planner
+
+doapp_status doapp_plan_lerp(const float *start, const float *goal, uint32_t n, uint32_t d,
+                             float *out) {
+  if (!start || !goal || !out || n == 0 || d == 0) return DOAPP_INVALID_ARG;
+  // planning_state.cu:50-52: step = (goal - current) / num_waypoints
+  for (uint32_t j = 0; j < d; ++j) {
+    volatile float step = (goal[j] - start[j]) / (float)n;
+    for (uint32_t w = 0; w < n; ++w) {
+      volatile float inc = (float)(w + 1) * step;
+      out[(size_t)w * d + j] = start[j] + inc;
+    }
+  }
+  return DOAPP_OK;
+}
+
+doapp_status doapp_plan_async(doapp_ctx *ctx, const float *start, const float *goal,
+                              const float *init_traj, uint32_t iters, const float *noise) {
+  if (!ctx) return DOAPP_INVALID_ARG;
+  if (!start || !init_traj)
+    return fail(ctx, DOAPP_INVALID_ARG, "doapp_plan: null start or init_traj");
+  (void)goal; // only the message assembly needs it (host side)
+  CU(cudaSetDevice(ctx->cfg.device));
+  const doapp_config &c = ctx->cfg;
+  ST(upload_traj(ctx, init_traj, true));
+  ST(upload_start(ctx, start));
+  int mode = NOISE_PHILOX;
+  if (noise) {
+    size_t total = (size_t)iters * c.num_climbers * ctx->m_global * c.noise_waypoints *
+                   c.waypoint_dim;
+    ST(ensure(ctx, ctx->noise, total));
+    CU(cudaMemcpyAsync(ctx->noise.p, noise, total * sizeof(float), cudaMemcpyHostToDevice,
+                       ctx->stream));
+    mode = NOISE_EXTERNAL;
+  }
+  ctx->plan_staged = true;
+  ctx->plan_noise_mode = mode;
+  ctx->plan_iters = iters;
+  ST(run_plan(ctx, iters, mode));
+  ctx->plan_pending = true;
+  return DOAPP_OK;
+}
+
+doapp_status doapp_plan_wait(doapp_ctx *ctx, float *best_traj, float *best_vel, float *best_score,
+                             int64_t *best_climber) {
+  if (!ctx) return DOAPP_INVALID_ARG;
+  if (!ctx->plan_pending) return fail(ctx, DOAPP_NOT_READY, "doapp_plan_wait: no plan in flight");
+  CU(cudaSetDevice(ctx->cfg.device));
+  const size_t nd = (size_t)ctx->cfg.num_waypoints * ctx->cfg.waypoint_dim;
+  CU(cudaMemcpyAsync(ctx->h_out.data(), ctx->out.p, (4 + 2 * nd) * sizeof(float),
+                     cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  ctx->plan_pending = false;
+  if (best_score) *best_score = ctx->h_out[0];
+  if (best_climber) memcpy(best_climber, &ctx->h_out[2], 8);
+  if (best_traj) memcpy(best_traj, &ctx->h_out[4], nd * sizeof(float));
+  if (best_vel) memcpy(best_vel, &ctx->h_out[4 + nd], nd * sizeof(float));
+  return DOAPP_OK;
+}
+
+doapp_status doapp_plan(doapp_ctx *ctx, const float *start, const float *goal,
+                        const float *init_traj, uint32_t iters, const float *noise,
+                        float *best_traj, float *best_vel, float *best_score,
+                        int64_t *best_climber) {
+  ST(doapp_plan_async(ctx, start, goal, init_traj, iters, noise));
+  return doapp_plan_wait(ctx, best_traj, best_vel, best_score, best_climber);
+}
+
+doapp_status doapp_plan_state(doapp_ctx *ctx, float *trajectories, float *scores,
+                              int32_t *rounded, uint8_t *found_better) {
+  if (!ctx) return DOAPP_INVALID_ARG;
+  CU(cudaSetDevice(ctx->cfg.device));
+  const doapp_config &c = ctx->cfg;
+  const size_t k = c.num_climbers, n = c.num_waypoints, d = c.waypoint_dim, npad = ctx->npad;
+  CU(cudaStreamSynchronize(ctx->stream));
+  if (trajectories) {
+    std::vector<float> soa(k * d * npad);
+    CU(cudaMemcpy(soa.data(), ctx->traj.p, soa.size() * sizeof(float), cudaMemcpyDeviceToHost));
+    for (size_t cl = 0; cl < k; ++cl)
+      for (size_t w = 0; w < n; ++w)
+        for (size_t j = 0; j < d; ++j)
+          trajectories[(cl * n + w) * d + j] = soa[(cl * d + j) * npad + w];
+  }
+  if (scores || rounded) {
+    std::vector<float> sc(k);
+    CU(cudaMemcpy(sc.data(), ctx->final_scores.p, k * sizeof(float), cudaMemcpyDeviceToHost));
+    for (size_t cl = 0; cl < k; ++cl) {
+      if (scores) scores[cl] = sc[cl];
+      if (rounded)
+        rounded[cl] = (sc[cl] < 2147483648.0f) ? (int32_t)ceilf(sc[cl]) : 0x7FFFFFFF;
+    }
+  }
+  if (found_better)
+    CU(cudaMemcpy(found_better, ctx->found.p, k, cudaMemcpyDeviceToHost));
+  return DOAPP_OK;
+}
+
+doapp_status doapp_plan_bench(doapp_ctx *ctx, uint32_t iters, uint32_t repeats,
+                              float *elapsed_ms) {
+  if (!ctx) return DOAPP_INVALID_ARG;
+  if (!ctx->plan_staged) return fail(ctx, DOAPP_NOT_READY, "doapp_plan_bench: call doapp_plan first");
+  if (ctx->plan_noise_mode == NOISE_EXTERNAL && iters > ctx->plan_iters)
+    return fail(ctx, DOAPP_INVALID_ARG, "doapp_plan_bench: staged noise covers %u iterations",
+                ctx->plan_iters);
+  CU(cudaSetDevice(ctx->cfg.device));
+  if (repeats == 0) repeats = 1;
+  // make sure the graph exists before the timed region
+  ST(reset_climbers(ctx));
+  ST(run_plan(ctx, iters, ctx->plan_noise_mode));
+  CU(cudaStreamSynchronize(ctx->stream));
+  CU(cudaEventRecord(ctx->ev0, ctx->stream));
+  for (uint32_t r = 0; r < repeats; ++r) {
+    ST(reset_climbers(ctx));
+    ST(run_plan(ctx, iters, ctx->plan_noise_mode));
+  }
+  CU(cudaEventRecord(ctx->ev1, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  float ms = 0.0f;
+  CU(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+  if (elapsed_ms) *elapsed_ms = ms;
+  ctx->plan_pending = true;
+  return DOAPP_OK;
+}
+
+doapp_status doapp_replan_dynamic(doapp_ctx *ctx, const float *start, const float *goal,
+                                  const float *init_traj, uint32_t iters, const float *clouds,
+                                  size_t num_points, float *best_traj, float *best_score,
+                                  float *elapsed_ms) {
+  if (!ctx) return DOAPP_INVALID_ARG;
+  if (!start || !init_traj || (!clouds && num_points && iters))
+    return fail(ctx, DOAPP_INVALID_ARG, "doapp_replan_dynamic: null argument");
+  if (ctx->grid.kind != DOAPP_GRID_U8)
+    return fail(ctx, DOAPP_NOT_READY, "doapp_replan_dynamic: needs a U8 grid");
+  (void)goal;
+  CU(cudaSetDevice(ctx->cfg.device));
+  const doapp_config &c = ctx->cfg;
+  ST(upload_traj(ctx, init_traj, true));
+  ST(upload_start(ctx, start));
+  const size_t cloud_elems = (size_t)iters * num_points * 3;
+  ST(ensure(ctx, ctx->cloud, cloud_elems));
+  if (cloud_elems)
+    CU(cudaMemcpyAsync(ctx->cloud.p, clouds, cloud_elems * sizeof(float), cudaMemcpyHostToDevice,
+                       ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  CU(cudaEventRecord(ctx->ev0, ctx->stream));
+  CU(cudaMemsetAsync(ctx->keys.p, 0xFF, sizeof(unsigned long long) * c.num_climbers, ctx->stream));
+  // the initial score is taken against the first cloud's grid
+  auto rebuild = [&](uint32_t it) -> doapp_status {
+    CU(cudaMemsetAsync(ctx->grid_cells.p, 0, ctx->grid_bytes, ctx->stream));
+    ScatterParams sp{};
+    sp.xyz = ctx->cloud.p + (size_t)it * num_points * 3;
+    sp.num_points = num_points;
+    sp.grid = ctx->grid;
+    sp.cells = ctx->grid_cells.p;
+    sp.val = 1;
+    CU(launch_scatter(sp, ctx->sm_count, ctx->stream));
+    if (num_points) ctx->launches += 1;
+    return DOAPP_OK;
+  };
+  UpdateParams u{};
+  u.traj = ctx->traj.p;
+  u.noise_mode = NOISE_PHILOX;
+  u.k = c.num_climbers;
+  u.n = c.num_waypoints;
+  u.npad = ctx->npad;
+  u.d = c.waypoint_dim;
+  u.n_noise = c.noise_waypoints;
+  u.seed_lo = (uint32_t)c.seed;
+  u.seed_hi = (uint32_t)(c.seed >> 32);
+  u.sigma = c.sigma;
+  u.keys = ctx->keys.p;
+  u.cur_hi = ctx->cur_hi.p;
+  u.found_better = ctx->found.p;
+  for (uint32_t it = 0; it < iters; ++it) {
+    ST(rebuild(it));
+    // the world moved: re-score the kept trajectories against the new grid
+    CostParams p0 = climber_cost_params(ctx);
+    p0.keys = ctx->keys.p;
+    CU(launch_cost(p0, c.waypoint_dim, ctx->sm_count, ctx->stream));
+    UpdateParams ui = u;
+    ui.init = 1;
+    CU(launch_update(ui, ctx->stream));
+    CostParams p = base_cost_params(ctx);
+    p.noise_mode = NOISE_PHILOX;
+    p.iteration = it;
+    p.keys = ctx->keys.p;
+    CU(launch_cost(p, c.waypoint_dim, ctx->sm_count, ctx->stream));
+    UpdateParams uu = u;
+    uu.iteration = it;
+    uu.init = 0;
+    CU(launch_update(uu, ctx->stream));
+    ctx->launches += 4;
+  }
+  {
+    CostParams p = climber_cost_params(ctx);
+    p.scores = ctx->final_scores.p;
+    p.collisions = ctx->final_coll.p;
+    CU(launch_cost(p, c.waypoint_dim, ctx->sm_count, ctx->stream));
+    FinalParams f{};
+    f.traj = ctx->traj.p;
+    f.start = ctx->start.p;
+    f.scores = ctx->final_scores.p;
+    f.found_better = ctx->found.p;
+    f.k = c.num_climbers;
+    f.n = c.num_waypoints;
+    f.npad = ctx->npad;
+    f.d = c.waypoint_dim;
+    f.dt = c.delta_t;
+    f.out = ctx->out.p;
+    CU(launch_final(f, ctx->stream));
+    ctx->launches += 2;
+  }
+  CU(cudaEventRecord(ctx->ev1, ctx->stream));
+  ctx->plan_pending = true;
+  ST(doapp_plan_wait(ctx, best_traj, nullptr, best_score, nullptr));
+  float ms = 0.0f;
+  CU(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+  if (elapsed_ms) *elapsed_ms = ms;
+  return DOAPP_OK;
+}
+
+// ------------------------------------------------------------------- multi-GPU
+
+doapp_status doapp_comm_unique_id(uint8_t id[DOAPP_COMM_ID_BYTES]) {
+  if (!id) return DOAPP_INVALID_ARG;
+  std::string err;
+  NcclApi *api = nccl_api(&err);
+  if (!api) return fail(nullptr, DOAPP_NCCL_ERROR, "%s", err.c_str());
+  static_assert(sizeof(ncclUniqueId) <= DOAPP_COMM_ID_BYTES, "ncclUniqueId size");
+  ncclUniqueId uid;
+  ncclResult_t r = api->GetUniqueId(&uid);
+  if (r != ncclSuccess) return fail(nullptr, DOAPP_NCCL_ERROR, "ncclGetUniqueId failed (%d)", (int)r);
+  memset(id, 0, DOAPP_COMM_ID_BYTES);
+  memcpy(id, &uid, sizeof(uid));
+  return DOAPP_OK;
+}
+
+doapp_status doapp_comm_init(doapp_ctx *ctx, const uint8_t id[DOAPP_COMM_ID_BYTES], int32_t rank,
+                             int32_t nranks) {
+  if (!ctx) return DOAPP_INVALID_ARG;
+  if (!id || nranks < 1 || rank < 0 || rank >= nranks)
+    return fail(ctx, DOAPP_INVALID_ARG, "doapp_comm_init: rank %d of %d", rank, nranks);
+  if (ctx->comm) return fail(ctx, DOAPP_INVALID_ARG, "doapp_comm_init: already initialised");
+  std::string err;
+  NcclApi *api = nccl_api(&err);
+  if (!api) return fail(ctx, DOAPP_NCCL_ERROR, "%s", err.c_str());
+  CU(cudaSetDevice(ctx->cfg.device));
+  ncclUniqueId uid;
+  memcpy(&uid, id, sizeof(uid));
+  ncclResult_t r = api->CommInitRank(&ctx->comm, nranks, uid, rank);
+  if (r != ncclSuccess) {
+    ctx->comm = nullptr;
+    return fail(ctx, DOAPP_NCCL_ERROR, "ncclCommInitRank: %s",
+                api->GetErrorString ? api->GetErrorString(r) : "error");
+  }
+  ctx->rank = rank;
+  ctx->nranks = nranks;
+  invalidate_graph(ctx);
+  return DOAPP_OK;
+}
+
+doapp_status doapp_grid_broadcast(doapp_ctx *ctx, int32_t root) {
+  if (!ctx) return DOAPP_INVALID_ARG;
+  if (!ctx->comm) return fail(ctx, DOAPP_NOT_READY, "doapp_grid_broadcast: no communicator");
+  if (ctx->grid.kind == DOAPP_GRID_NONE) return fail(ctx, DOAPP_NOT_READY, "no grid allocated");
+  NcclApi *api = nccl_api(nullptr);
+  CU(cudaSetDevice(ctx->cfg.device));
+  ncclResult_t r = api->Broadcast(ctx->grid_cells.p, ctx->grid_cells.p, ctx->grid_bytes, ncclUint8,
+                                  root, ctx->comm, ctx->stream);
+  if (r != ncclSuccess)
+    return fail(ctx, DOAPP_NCCL_ERROR, "ncclBroadcast: %s",
+                api->GetErrorString ? api->GetErrorString(r) : "error");
+  CU(cudaStreamSynchronize(ctx->stream));
+  return DOAPP_OK;
+}
+
+// --------------------------------------------------------------- introspection
+
+uint64_t doapp_launch_count(const doapp_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+doapp_status doapp_debug_sincos(doapp_ctx *ctx, const float *angles, size_t count, float *sin_out,
+                                float *cos_out) {
+  if (!ctx) return DOAPP_INVALID_ARG;
+  if (count == 0) return DOAPP_OK;
+  if (!angles || !sin_out || !cos_out) return fail(ctx, DOAPP_INVALID_ARG, "null argument");
+  CU(cudaSetDevice(ctx->cfg.device));
+  ST(ensure(ctx, ctx->dbg_a, count));
+  ST(ensure(ctx, ctx->dbg_b, count));
+  ST(ensure(ctx, ctx->dbg_c, count));
+  CU(cudaMemcpyAsync(ctx->dbg_a.p, angles, count * sizeof(float), cudaMemcpyHostToDevice,
+                     ctx->stream));
+  CU(launch_debug_sincos(ctx->dbg_a.p, count, ctx->dbg_b.p, ctx->dbg_c.p, ctx->stream));
+  ctx->launches += 1;
+  CU(cudaMemcpyAsync(sin_out, ctx->dbg_b.p, count * sizeof(float), cudaMemcpyDeviceToHost,
+                     ctx->stream));
+  CU(cudaMemcpyAsync(cos_out, ctx->dbg_c.p, count * sizeof(float), cudaMemcpyDeviceToHost,
+                     ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  return DOAPP_OK;
+}
+
+doapp_status doapp_debug_fk(doapp_ctx *ctx, const float *waypoints, size_t count,
+                            float *points_out) {
+  if (!ctx) return DOAPP_INVALID_ARG;
+  if (count == 0) return DOAPP_OK;
+  if (!waypoints || !points_out) return fail(ctx, DOAPP_INVALID_ARG, "null argument");
+  CU(cudaSetDevice(ctx->cfg.device));
+  const size_t d = ctx->cfg.waypoint_dim;
+  ST(ensure(ctx, ctx->dbg_a, count * d));
+  ST(ensure(ctx, ctx->dbg_b, count * 15));
+  CU(cudaMemcpyAsync(ctx->dbg_a.p, waypoints, count * d * sizeof(float), cudaMemcpyHostToDevice,
+                     ctx->stream));
+  CU(launch_debug_fk(ctx->dbg_a.p, count, (int)d, ctx->rpy_s, ctx->rpy_c, ctx->dbg_b.p,
+                     ctx->stream));
+  ctx->launches += 1;
+  CU(cudaMemcpyAsync(points_out, ctx->dbg_b.p, count * 15 * sizeof(float), cudaMemcpyDeviceToHost,
+                     ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  return DOAPP_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,105 @@
+// kernels.cuh — parameter blocks and launchers of the sm_100a kernels.
+#pragma once
+
+#include <cstddef>
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace doapp {
+
+constexpr int kMaxJoints = 5;
+constexpr uint64_t kKeyNone = 0xFFFFFFFFFFFFFFFFull;
+
+enum NoiseMode : int { NOISE_ZERO = 0, NOISE_EXTERNAL = 1, NOISE_PHILOX = 2 };
+
+// Device view of the voxel grid (dense, index ix + nx*iy + nx*ny*iz).
+struct GridDev {
+  const void *cells;
+  int kind;  // doapp_grid_kind
+  int frame; // doapp_grid_frame
+  uint32_t nx, ny, nz;
+  // CDG frame (cpu_distance_grid.cu:69-82), all fp32
+  float res, x_off, y_off, z_max;
+  // OG frame (occupancy_grid.cpp:29-40), fp64
+  double res_d, half_d;
+};
+
+struct CostParams {
+  // trajectories, structure-of-arrays: traj[c][j][npad]
+  const float *traj;
+  const float *start; // [d] device
+  const float *noise; // external buffer or nullptr
+  uint64_t noise_m;   // samples per climber in the external buffer
+  uint64_t noise_t0;  // global sample index of the buffer's first column
+  int noise_mode;
+  uint32_t k, m, n, npad, n_noise;
+  uint32_t iteration, seed_lo, seed_hi;
+  float sigma;
+  uint64_t sample_offset, m_global;
+  float dt, smooth_scale, coll_dist, limit_weight;
+  float lim_min[kMaxJoints], lim_max[kMaxJoints];
+  int use_limits;
+  int collision_mode, select_mode;
+  float rpy_s, rpy_c; // deterministic sin/cos of the fixed -pi/2 pitch (gt.cu:456)
+  GridDev grid;
+  float *scores;                 // [k*m] or nullptr
+  int32_t *collisions;           // [k*m] or nullptr
+  unsigned long long *keys;      // [k] packed argmin keys for the update rule, or nullptr
+  unsigned long long *keys_float; // [k] packed (float bits, t) keys for the host-style argmin
+  uint32_t samples_per_warp;
+  uint64_t total_samples;
+};
+
+struct UpdateParams {
+  float *traj; // [k][d][npad]
+  const float *noise;
+  uint64_t noise_m, noise_t0;
+  int noise_mode;
+  uint32_t k, n, npad, d, n_noise;
+  uint32_t iteration, seed_lo, seed_hi;
+  float sigma;
+  unsigned long long *keys; // [k], consumed and reset
+  uint32_t *cur_hi;         // [k]
+  uint8_t *found_better;    // [k]
+  int init;                 // 1: seed cur_hi from keys, no trajectory change
+};
+
+struct FinalParams {
+  const float *traj; // [k][d][npad]
+  const float *start;
+  const float *scores;         // [k] float score of every climber's kept trajectory
+  const uint8_t *found_better; // [k]
+  uint32_t k, n, npad, d;
+  float dt;
+  // out: [0]=best score, [1..2]=best climber (int64 bits), [4 ..] traj [n][d], then vel [n][d]
+  float *out;
+};
+
+struct ScatterParams {
+  const float *xyz;
+  uint64_t num_points;
+  GridDev grid;
+  uint8_t *cells;
+  int8_t val;
+};
+
+cudaError_t launch_cost(const CostParams &p, int d, int sm_count, cudaStream_t st);
+cudaError_t launch_update(const UpdateParams &p, cudaStream_t st);
+cudaError_t launch_final(const FinalParams &p, cudaStream_t st);
+cudaError_t launch_scatter(const ScatterParams &p, int sm_count, cudaStream_t st);
+cudaError_t launch_lookup(const GridDev &g, const float *xyz, uint64_t count, float coll_dist,
+                          long long *cell_index, uint8_t *collides, cudaStream_t st);
+cudaError_t launch_noise_fill(const CostParams &p, int d, float *out, cudaStream_t st);
+cudaError_t launch_aos_to_soa(const float *aos, float *soa, uint32_t k, uint32_t n, uint32_t npad,
+                              uint32_t d, int broadcast_first, cudaStream_t st);
+cudaError_t launch_debug_sincos(const float *x, uint64_t count, float *s, float *c,
+                                cudaStream_t st);
+cudaError_t launch_debug_fk(const float *wp, uint64_t count, int d, float rpy_s, float rpy_c,
+                            float *out, cudaStream_t st);
+cudaError_t launch_reduce_keys_float(const unsigned long long *keys, uint32_t k,
+                                     unsigned long long *out, cudaStream_t st);
+
+// host-side evaluation of the deterministic sin/cos (for rpy_s / rpy_c)
+void host_sincos(float x, float *s, float *c);
+
+} // namespace doapp

@@ -1,0 +1,681 @@
+/*
+ * doapp_oracle.c — CPU restatement of the reference's perturbator cost path.
+ * TEST INFRASTRUCTURE ONLY (see doapp_oracle.h).  Build: oracle/Makefile
+ * (gcc -O3 -march=x86-64-v3 -ffp-contract=off: every rounding is written
+ * explicitly; fmaf() below is a single-rounding fused multiply-add).
+ */
+#include "doapp_oracle.h"
+
+#include <limits.h>
+#include <math.h>
+#include <pthread.h>
+#include <stdlib.h>
+#include <string.h>
+
+void orc_params_init(orc_params *p) {
+  memset(p, 0, sizeof(*p));
+  p->k = 1;
+  p->m = 1024;
+  p->n = 64;
+  p->d = 5;
+  p->n_noise = 1;
+  p->delta_t = 0.1f;            /* planning_state.cuh:55 */
+  p->smooth_scale = 0.25f;      /* gt.cu:81,107: two `*= 0.5f` */
+  p->collision_distance = 0.05f; /* gt.cu:389 */
+  p->collision_mode = ORC_COLLISION_INTENDED;
+  p->select_mode = ORC_SELECT_CEIL_INT;
+  p->sum_order = ORC_SUM_TREE32;
+  p->sigma = 1.0f;
+  p->seed = 1234; /* gt.cu:23 */
+}
+
+/* ------------------------------------------------------------------------
+ * Deterministic elementary functions.  The reference calls std::sin/std::cos
+ * on the device (gt.cu:304-305); CUDA's and glibc's sinf differ in the last
+ * ulp, which would flip voxel indices, so both sides of the parity check use
+ * this specification instead (DESIGN.md "deterministic math spec"):
+ *   |x| < 2^17:  t = x*(2/pi) [RN]; kf = rintf(t);
+ *                r = fma(-kf,P1,x); r = fma(-kf,P2,r); r = fma(-kf,P3,r)
+ *   otherwise :  xd = fmod(x, 2*pi) in binary64 (exact), then the two-constant
+ *                reduction in binary64, r -> float
+ *   z = r*r
+ *   sin_r = fma(fma(fma(S3,z,S2),z,S1)*z, r, r)
+ *   cos_r = fma(fma(fma(fma(C3,z,C2),z,C1),z,-0.5), z, 1)
+ *   quadrant q = k & 3 : (s,c) = (sin_r,cos_r), (cos_r,-sin_r), (-sin_r,-cos_r), (-cos_r,sin_r)
+ * Polynomial coefficients: Cephes sinf/cosf minimax on [-pi/4, pi/4].
+ * ---------------------------------------------------------------------- */
+static const float ORC_TWO_OVER_PI = 0x1.45f306p-1f;
+static const float ORC_P1 = 0x1.921fb6p+0f;    /* RN(pi/2)               */
+static const float ORC_P2 = -0x1.777a5cp-25f;  /* RN(pi/2 - P1)          */
+static const float ORC_P3 = -0x1.ee59dap-50f;  /* RN(pi/2 - P1 - P2)     */
+static const double ORC_TWO_OVER_PI_D = 0x1.45f306dc9c883p-1;
+static const double ORC_TWO_PI_D = 0x1.921fb54442d18p+2;
+static const double ORC_P1_D = 0x1.921fb54442d18p+0;
+static const double ORC_P2_D = 0x1.1a62633145c07p-54;
+static const float ORC_S1 = -1.6666654611e-1f;
+static const float ORC_S2 = 8.3321608736e-3f;
+static const float ORC_S3 = -1.9515295891e-4f;
+static const float ORC_C1 = 4.166664568298827e-2f;
+static const float ORC_C2 = -1.388731625493765e-3f;
+static const float ORC_C3 = 2.443315711809948e-5f;
+
+void orc_sincosf(float x, float *s, float *c) {
+  float r;
+  int q;
+  if (fabsf(x) < 131072.0f) {
+    float t = x * ORC_TWO_OVER_PI;
+    float kf = rintf(t);
+    r = fmaf(-kf, ORC_P1, x);
+    r = fmaf(-kf, ORC_P2, r);
+    r = fmaf(-kf, ORC_P3, r);
+    q = (int)kf & 3;
+  } else if (x != x || fabsf(x) == INFINITY) {
+    *s = NAN;
+    *c = NAN;
+    return;
+  } else {
+    /* exact remainder by the binary64 value of 2*pi keeps the argument small;
+     * accuracy decays with |x| but the result stays bounded and deterministic */
+    double xd = fmod((double)x, ORC_TWO_PI_D);
+    double kd = rint(xd * ORC_TWO_OVER_PI_D);
+    double rd = fma(-kd, ORC_P1_D, xd);
+    rd = fma(-kd, ORC_P2_D, rd);
+    r = (float)rd;
+    q = (int)kd & 3;
+  }
+  float z = r * r;
+  float ps = fmaf(ORC_S3, z, ORC_S2);
+  ps = fmaf(ps, z, ORC_S1);
+  ps = ps * z;
+  float sin_r = fmaf(ps, r, r);
+  float pc = fmaf(ORC_C3, z, ORC_C2);
+  pc = fmaf(pc, z, ORC_C1);
+  pc = fmaf(pc, z, -0.5f);
+  float cos_r = fmaf(pc, z, 1.0f);
+  switch (q) {
+  case 0: *s = sin_r; *c = cos_r; break;
+  case 1: *s = cos_r; *c = -sin_r; break;
+  case 2: *s = -sin_r; *c = -cos_r; break;
+  default: *s = -cos_r; *c = sin_r; break;
+  }
+}
+
+/* natural log for x in (0, 1] (Box-Muller radius), Cephes logf polynomial on
+ * [sqrt(1/2), sqrt(2)) evaluated with explicit fmaf. */
+float orc_logf(float x) {
+  uint32_t ix;
+  memcpy(&ix, &x, 4);
+  ix += 0x3f800000u - 0x3f3504f3u;
+  int e = (int)(ix >> 23) - 127;
+  ix = (ix & 0x007fffffu) + 0x3f3504f3u;
+  float mant;
+  memcpy(&mant, &ix, 4);
+  float f = mant - 1.0f;
+  float z = f * f;
+  float p = 7.0376836292e-2f;
+  p = fmaf(p, f, -1.1514610310e-1f);
+  p = fmaf(p, f, 1.1676998740e-1f);
+  p = fmaf(p, f, -1.2420140846e-1f);
+  p = fmaf(p, f, 1.4249322787e-1f);
+  p = fmaf(p, f, -1.6668057665e-1f);
+  p = fmaf(p, f, 2.0000714765e-1f);
+  p = fmaf(p, f, -2.4999993993e-1f);
+  p = fmaf(p, f, 3.3333331174e-1f);
+  float y = (f * z) * p;
+  float fe = (float)e;
+  y = fmaf(fe, -2.12194440e-4f, y);
+  y = fmaf(-0.5f, z, y);
+  float r = f + y;
+  r = fmaf(fe, 0.693359375f, r);
+  return r;
+}
+
+/* ------------------------------------------------------------------------
+ * Stage 1.  Replaces init_cudarand / curand_normal (gt.cu:17-25,37-44,297-299;
+ * XORWOW, not reproduced: the reference's tests pin nothing about the stream).
+ * Philox4x32-10, key = (seed lo, seed hi), counter =
+ * (t_global, climber, noise waypoint, 2*iteration + call); four outputs give
+ * two Box-Muller pairs; joint j uses call j/4, pair (j%4)/2, cos for even j.
+ * ---------------------------------------------------------------------- */
+void orc_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]) {
+  uint32_t c0 = ctr[0], c1 = ctr[1], c2 = ctr[2], c3 = ctr[3];
+  uint32_t k0 = key[0], k1 = key[1];
+  for (int r = 0; r < 10; ++r) {
+    uint64_t p0 = (uint64_t)0xD2511F53u * c0;
+    uint64_t p1 = (uint64_t)0xCD9E8D57u * c2;
+    uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0;
+    uint32_t n1 = (uint32_t)p1;
+    uint32_t n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1;
+    uint32_t n3 = (uint32_t)p0;
+    c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+    k0 += 0x9E3779B9u;
+    k1 += 0xBB67AE85u;
+  }
+  out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+
+static float orc_box_muller(uint32_t a, uint32_t b, int want_sin, float sigma) {
+  float u1 = (float)((a >> 8) + 1u) * 0x1p-24f; /* (0,1] */
+  float u2 = (float)(b >> 8) * 0x1p-24f;        /* [0,1) */
+  float rad = sqrtf(-2.0f * orc_logf(u1));
+  float s, c;
+  orc_sincosf(u2 * 0x1.921fb6p+2f, &s, &c);
+  float zn = rad * (want_sin ? s : c);
+  return sigma * zn;
+}
+
+float orc_noise_at(const orc_params *p, uint32_t iteration, uint32_t c, uint64_t t_global,
+                   uint32_t wn, uint32_t j) {
+  uint32_t ctr[4] = {(uint32_t)t_global, c, wn, 2u * iteration + (j >> 2)};
+  uint32_t key[2] = {(uint32_t)p->seed, (uint32_t)(p->seed >> 32)};
+  uint32_t r[4];
+  orc_philox4x32_10(ctr, key, r);
+  uint32_t pair = (j & 3u) >> 1;
+  return orc_box_muller(r[2 * pair], r[2 * pair + 1], (int)(j & 1u), p->sigma);
+}
+
+void orc_noise_fill(const orc_params *p, uint32_t iteration, float *noise) {
+  for (uint32_t c = 0; c < p->k; ++c)
+    for (uint32_t t = 0; t < p->m; ++t)
+      for (uint32_t wn = 0; wn < p->n_noise; ++wn)
+        for (uint32_t j = 0; j < p->d; ++j)
+          noise[(((size_t)c * p->m + t) * p->n_noise + wn) * p->d + j] =
+              orc_noise_at(p, iteration, c, p->sample_offset + t, wn, j);
+}
+
+/* ------------------------------------------------------------------------
+ * Stage 2: forward kinematics, gt.cu:303-387 (rotation builders) and
+ * gt.cu:397-463 (chain).  Matrix products accumulate like matrix.cuh:274-313:
+ * c = T(); c += a[k]*b[k] for k = 0..2, which nvcc contracts to one FMA per
+ * term; the restatement writes those FMAs explicitly.  The mat-vec product is
+ * the INTENDED u[i] += a[i][j]*v[j] (matrix.cuh:315-336 ignores v).
+ * ---------------------------------------------------------------------- */
+typedef struct { float a[3][3]; } orc_m3;
+typedef struct { float v[3]; } orc_v3;
+
+static orc_m3 orc_rotx(float th) { /* gt.cu:303-318 */
+  float s, c;
+  orc_sincosf(th, &s, &c);
+  orc_m3 R = {{{1.0f, 0.0f, 0.0f}, {0.0f, c, -s}, {0.0f, s, c}}};
+  return R;
+}
+static orc_m3 orc_roty(float th) { /* gt.cu:320-335 */
+  float s, c;
+  orc_sincosf(th, &s, &c);
+  orc_m3 R = {{{c, 0.0f, s}, {0.0f, 1.0f, 0.0f}, {-s, 0.0f, c}}};
+  return R;
+}
+static orc_m3 orc_rotz(float th) { /* gt.cu:337-352 */
+  float s, c;
+  orc_sincosf(th, &s, &c);
+  orc_m3 R = {{{c, -s, 0.0f}, {s, c, 0.0f}, {0.0f, 0.0f, 1.0f}}};
+  return R;
+}
+static orc_m3 orc_eye(void) { /* gt.cu:375-387 */
+  orc_m3 R = {{{1.0f, 0.0f, 0.0f}, {0.0f, 1.0f, 0.0f}, {0.0f, 0.0f, 1.0f}}};
+  return R;
+}
+static orc_m3 orc_matmul(const orc_m3 *A, const orc_m3 *B) { /* matrix.cuh:274-313 */
+  orc_m3 C;
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) {
+      float acc = 0.0f;
+      for (int k = 0; k < 3; ++k) acc = fmaf(A->a[i][k], B->a[k][j], acc);
+      C.a[i][j] = acc;
+    }
+  return C;
+}
+static orc_v3 orc_matvec(const orc_m3 *A, const orc_v3 *v) { /* matrix.cuh:315-336, D2 fixed */
+  orc_v3 u;
+  for (int i = 0; i < 3; ++i) {
+    float acc = 0.0f;
+    for (int j = 0; j < 3; ++j) acc = fmaf(A->a[i][j], v->v[j], acc);
+    u.v[i] = acc;
+  }
+  return u;
+}
+static orc_v3 orc_matvec_as_shipped(const orc_m3 *A, const orc_v3 *v) { /* matrix.cuh:315-336 */
+  (void)v;
+  orc_v3 u;
+  for (int i = 0; i < 3; ++i) {
+    float acc = 0.0f;
+    for (int j = 0; j < 3; ++j) acc += A->a[i][j];
+    u.v[i] = acc;
+  }
+  return u;
+}
+static orc_v3 orc_vadd(const orc_v3 *a, const orc_v3 *b) { /* vector.cuh:253-264 */
+  orc_v3 w = {{a->v[0] + b->v[0], a->v[1] + b->v[1], a->v[2] + b->v[2]}};
+  return w;
+}
+static orc_m3 orc_rot_rpy(float roll, float pitch, float yaw) { /* gt.cu:354-367 */
+  orc_m3 R = orc_rotx(roll);
+  orc_m3 cur = orc_roty(pitch);
+  R = orc_matmul(&R, &cur);
+  cur = orc_rotz(yaw);
+  R = orc_matmul(&R, &cur);
+  return R;
+}
+
+static void orc_fk_impl(const float *waypoint, uint32_t d, float out[5][3], int shipped_matvec) {
+  /* link translations, gt.cu:407,418,429,440,451 (= rexarm.urdf joint origins) */
+  static const float T[5][3] = {{0.0f, -0.0015f, 0.0715f},
+                                {0.0f, 0.0f, 0.045f},
+                                {0.0f, 0.0f, 0.1f},
+                                {0.0f, 0.0f, 0.1f},
+                                {0.0f, -0.0125f, 0.08f}};
+  orc_m3 stat = orc_eye();          /* gt.cu:406 */
+  orc_v3 pos = {{0.0f, 0.0f, 0.0f}}; /* Vector(3) value-initialises, vector.cuh:79-88 */
+  for (int link = 0; link < 5; ++link) {
+    /* a 4-joint waypoint has no wrist_rotate angle (the reference reads
+     * waypoint[4] out of bounds): use 0. */
+    float th = (uint32_t)link < d ? waypoint[link] : 0.0f;
+    orc_m3 dyn = (link == 1) ? orc_rotz(th) : orc_roty(th); /* axes y,z,y,y,y */
+    orc_v3 t = {{T[link][0], T[link][1], T[link][2]}};
+    orc_v3 sp = shipped_matvec ? orc_matvec_as_shipped(&stat, &pos) : orc_matvec(&stat, &pos);
+    orc_v3 q = orc_vadd(&sp, &t);
+    pos = shipped_matvec ? orc_matvec_as_shipped(&dyn, &q) : orc_matvec(&dyn, &q);
+    if (link == 4) {
+      /* gt.cu:456-459 */
+      stat = orc_rot_rpy(0.0f, -1.5707963267948966f, 0.0f);
+      orc_v3 t2 = {{0.0f, -0.005f, 0.07f}};
+      orc_v3 sp2 = shipped_matvec ? orc_matvec_as_shipped(&stat, &pos) : orc_matvec(&stat, &pos);
+      pos = orc_vadd(&sp2, &t2);
+    }
+    out[link][0] = pos.v[0];
+    out[link][1] = pos.v[1];
+    out[link][2] = pos.v[2];
+  }
+}
+
+void orc_fk_points(const float *waypoint, uint32_t d, float out[5][3]) {
+  orc_fk_impl(waypoint, d, out, 0);
+}
+void orc_fk_points_as_shipped_matvec(const float *waypoint, uint32_t d, float out[5][3]) {
+  orc_fk_impl(waypoint, d, out, 1);
+}
+
+/* ------------------------------------------------------------------------
+ * Stage 3: grid lookup.  CDG frame: cdg.cu:69-82 (offsets) and :113-126
+ * (bounds, fp32 add, IEEE fp32 divide, truncation).  OG frame: og.cpp:29-40
+ * (fp64).  Deviations: dense pitch; half-open bounds, and an
+ * index that still lands on n (rounding of x + offset) is outside.
+ * ---------------------------------------------------------------------- */
+int64_t orc_grid_index(const orc_grid *g, float x, float y, float z) {
+  if (g->frame == ORC_FRAME_CDG) {
+    float res = (float)g->resolution;                            /* cdg.cu:69 */
+    float x_off = (float)(0.5 * (double)g->nx * g->resolution);  /* cdg.cu:70-71 */
+    float y_off = (float)(0.5 * (double)g->ny * g->resolution);  /* cdg.cu:72-73 */
+    float z_max = (float)((double)g->nz * g->resolution);        /* cdg.cu:81-82 */
+    if (!(x >= -x_off && x < x_off) || !(y >= -y_off && y < y_off) || !(z >= 0.0f && z < z_max))
+      return -1;
+    float fx = (x + x_off) / res; /* cdg.cu:120 */
+    float fy = (y + y_off) / res; /* cdg.cu:121 */
+    float fz = z / res;           /* cdg.cu:122 */
+    uint64_t ix = (uint64_t)fx, iy = (uint64_t)fy, iz = (uint64_t)fz;
+    if (ix >= g->nx || iy >= g->ny || iz >= g->nz) return -1;
+    return (int64_t)((uint64_t)g->nx * g->ny * iz + (uint64_t)g->nx * iy + ix); /* cdg.cu:124-125 */
+  } else {
+    double size = (double)g->nx * g->resolution;
+    double half = size / 2.0; /* og.cpp:31-33 */
+    double xs = (double)x + half, ys = (double)y + half, zs = (double)z + half;
+    if (!(xs >= 0.0 && ys >= 0.0 && zs >= 0.0)) return -1;
+    double fx = xs / g->resolution, fy = ys / g->resolution, fz = zs / g->resolution; /* og.cpp:35-37 */
+    if (!(fx < (double)g->nx && fy < (double)g->ny && fz < (double)g->nz)) return -1;
+    uint64_t ix = (uint64_t)fx, iy = (uint64_t)fy, iz = (uint64_t)fz;
+    if (ix >= g->nx || iy >= g->ny || iz >= g->nz) return -1;
+    return (int64_t)(ix + (uint64_t)g->nx * iy + (uint64_t)g->nx * g->ny * iz); /* og.cpp:26 */
+  }
+}
+
+int orc_grid_collides(const orc_grid *g, float x, float y, float z, float collision_distance) {
+  if (g->kind == ORC_GRID_NONE || !g->cells) return 0;
+  int64_t idx = orc_grid_index(g, x, y, z);
+  if (idx < 0) return 0; /* HUGE_VALF <= 0.05f is false, cdg.cu:117 */
+  if (g->kind == ORC_GRID_U8) return ((const uint8_t *)g->cells)[idx] != 0;
+  return ((const float *)g->cells)[idx] <= collision_distance; /* gt.cu:412 */
+}
+
+size_t orc_grid_scatter(orc_grid *g, const float *xyz, size_t num_points, int8_t val,
+                        int clear_first) {
+  size_t cells = (size_t)g->nx * g->ny * g->nz;
+  if (clear_first) memset(g->cells, 0, cells); /* og.cpp:15-16 */
+  size_t inside = 0;
+  for (size_t i = 0; i < num_points; ++i) {
+    int64_t idx = orc_grid_index(g, xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]); /* og.cpp:47-57 */
+    if (idx < 0) continue;
+    ((int8_t *)g->cells)[idx] = val; /* og.cpp:44 */
+    ++inside;
+  }
+  return inside;
+}
+
+uint32_t orc_num_collisions(const orc_params *p, const orc_grid *g, const float *waypoint) {
+  if (p->collision_mode == ORC_COLLISION_AS_SHIPPED) return 0; /* gt.cu:394 */
+  if (!g || g->kind == ORC_GRID_NONE) return 0;
+  float pts[5][3];
+  orc_fk_points(waypoint, p->d, pts);
+  uint32_t cnt = 0;
+  for (int l = 0; l < 5; ++l)
+    cnt += (uint32_t)orc_grid_collides(g, pts[l][0], pts[l][1], pts[l][2], p->collision_distance);
+  return cnt;
+}
+
+/* ------------------------------------------------------------------------
+ * Stages 2-4 for one sample.
+ * ---------------------------------------------------------------------- */
+static float orc_tree32(const float *per_waypoint, uint32_t n) {
+  float part[32];
+  for (int l = 0; l < 32; ++l) part[l] = 0.0f;
+  for (uint32_t w = 0; w < n; ++w) part[w & 31u] = part[w & 31u] + per_waypoint[w];
+  for (int off = 16; off >= 1; off >>= 1) {
+    float nxt[32];
+    for (int l = 0; l < 32; ++l) nxt[l] = part[l] + part[l ^ off];
+    memcpy(part, nxt, sizeof(part));
+  }
+  return part[0];
+}
+
+float orc_cost_sample(const orc_params *p, const orc_grid *g, const float *base,
+                      const float *start, const float *noise, int32_t *collisions,
+                      float *noisy_out, float *vel_out, float *acc_out, float *smooth_out,
+                      int32_t *violated_out) {
+  const uint32_t n = p->n, d = p->d;
+  float xprev[8], vprev[8], x[8], v[8];
+  float *acc2 = (float *)malloc(sizeof(float) * n * 2);
+  float *lim2 = acc2 + n;
+  int32_t coll = 0, violated = 0;
+  float seq_sum = 0.0f, seq_lim = 0.0f; /* element-by-element order of gt.test.cu:187-195 */
+  for (uint32_t j = 0; j < d; ++j) {
+    xprev[j] = start[j]; /* gt.cu:285: initial_waypoint is the prior of waypoint 0 ... */
+    vprev[j] = start[j]; /* ... for BOTH derivative passes (gt.test.cu:179-185) */
+  }
+  for (uint32_t w = 0; w < n; ++w) {
+    const float *eps = noise ? noise + (size_t)(p->n_noise == 1 ? 0 : w) * d : NULL;
+    float a2 = 0.0f, l2 = 0.0f;
+    for (uint32_t j = 0; j < d; ++j) {
+      x[j] = base[(size_t)w * d + j] + (eps ? eps[j] : 0.0f); /* gt.cu:53-57 */
+      v[j] = (x[j] - xprev[j]) / p->delta_t;                  /* gt.cu:288 */
+      float a = (v[j] - vprev[j]) / p->delta_t;               /* gt.cu:288 via :260-267 */
+      float sq = a * a;                                       /* gt.cu:76 */
+      a2 = a2 + sq;
+      seq_sum = seq_sum + sq;
+      if (noisy_out) noisy_out[(size_t)w * d + j] = x[j];
+      if (vel_out) vel_out[(size_t)w * d + j] = v[j];
+      if (acc_out) acc_out[(size_t)w * d + j] = a;
+      if (p->limit_min && p->limit_max) {
+        float over = x[j] - p->limit_max[j], under = p->limit_min[j] - x[j];
+        float h = fmaxf(0.0f, fmaxf(over, under));
+        if (h > 0.0f) violated = 1;
+        float hs = h * h;
+        l2 = l2 + hs;
+        seq_lim = seq_lim + hs;
+      }
+    }
+    acc2[w] = a2;
+    lim2[w] = l2;
+    coll += (int32_t)orc_num_collisions(p, g, x); /* gt.cu:86-103 */
+    for (uint32_t j = 0; j < d; ++j) {
+      xprev[j] = x[j];
+      vprev[j] = v[j];
+    }
+  }
+  float sum, lsum;
+  if (p->sum_order == ORC_SUM_SEQUENTIAL) { /* gt.test.cu:187-195 */
+    sum = seq_sum;
+    lsum = seq_lim;
+  } else {
+    sum = orc_tree32(acc2, n);
+    lsum = orc_tree32(lim2, n);
+  }
+  float smooth = p->smooth_scale * sum; /* gt.cu:81,107 */
+  float score = (float)coll + smooth;   /* gt.cu:100,108 */
+  if (p->limit_weight != 0.0f && p->limit_min && p->limit_max) {
+    float lc = p->limit_weight * lsum;
+    score = score + lc;
+  }
+  free(acc2);
+  if (collisions) *collisions = coll;
+  if (smooth_out) *smooth_out = smooth;
+  if (violated_out) *violated_out = violated;
+  return score;
+}
+
+static int32_t orc_round_score(float s) { /* gt.cu:109: int(ceilf(score)), saturating */
+  return (s < 2147483648.0f) ? (int32_t)ceilf(s) : INT_MAX;
+}
+
+/* ---- threaded evaluation over samples (idiom of cdg.cu:88-110) ---------- */
+typedef struct {
+  const orc_params *p;
+  const orc_grid *g;
+  const float *base_traj, *start, *noise;
+  uint32_t iteration;
+  float *scores;
+  int32_t *collisions;
+  size_t s0, s1;
+  size_t noise_m;      /* m of the noise buffer */
+  uint64_t noise_t0;   /* global sample index of the buffer's first column */
+} orc_job;
+
+static void *orc_eval_range(void *arg) {
+  orc_job *jb = (orc_job *)arg;
+  const orc_params *p = jb->p;
+  size_t nd = (size_t)p->n_noise * p->d;
+  float *tmp = (float *)malloc(sizeof(float) * nd);
+  for (size_t s = jb->s0; s < jb->s1; ++s) {
+    uint32_t c = (uint32_t)(s / p->m);
+    uint32_t t = (uint32_t)(s % p->m);
+    uint64_t tg = p->sample_offset + t;
+    const float *nz;
+    if (jb->noise) {
+      nz = jb->noise + ((size_t)c * jb->noise_m + (size_t)(tg - jb->noise_t0)) * nd;
+    } else {
+      for (uint32_t wn = 0; wn < p->n_noise; ++wn)
+        for (uint32_t j = 0; j < p->d; ++j)
+          tmp[(size_t)wn * p->d + j] = orc_noise_at(p, jb->iteration, c, tg, wn, j);
+      nz = tmp;
+    }
+    int32_t coll;
+    float sc = orc_cost_sample(p, jb->g, jb->base_traj + (size_t)c * p->n * p->d, jb->start, nz,
+                               &coll, NULL, NULL, NULL, NULL, NULL);
+    jb->scores[s] = sc;
+    if (jb->collisions) jb->collisions[s] = coll;
+  }
+  free(tmp);
+  return NULL;
+}
+
+static void orc_eval_all(const orc_params *p, const orc_grid *g, const float *base_traj,
+                         const float *start, const float *noise, size_t noise_m,
+                         uint64_t noise_t0, uint32_t iteration, float *scores,
+                         int32_t *collisions, int num_threads) {
+  size_t S = (size_t)p->k * p->m;
+  if (num_threads < 1) num_threads = 1;
+  if ((size_t)num_threads > S) num_threads = (int)(S ? S : 1);
+  orc_job *jobs = (orc_job *)calloc((size_t)num_threads, sizeof(orc_job));
+  pthread_t *th = (pthread_t *)calloc((size_t)num_threads, sizeof(pthread_t));
+  size_t per = (S + (size_t)num_threads - 1) / (size_t)num_threads;
+  for (int i = 0; i < num_threads; ++i) {
+    orc_job jb = {p, g, base_traj, start, noise, iteration, scores, collisions,
+                  0, 0, noise_m, noise_t0};
+    jb.s0 = per * (size_t)i < S ? per * (size_t)i : S;
+    jb.s1 = per * (size_t)(i + 1) < S ? per * (size_t)(i + 1) : S;
+    jobs[i] = jb;
+    if (num_threads == 1)
+      orc_eval_range(&jobs[i]);
+    else
+      pthread_create(&th[i], NULL, orc_eval_range, &jobs[i]);
+  }
+  if (num_threads > 1)
+    for (int i = 0; i < num_threads; ++i) pthread_join(th[i], NULL);
+  free(jobs);
+  free(th);
+}
+
+int64_t orc_cost_eval(const orc_params *p, const orc_grid *g, const float *base_traj,
+                      const float *start, const float *noise, uint32_t iteration,
+                      float *scores, int32_t *collisions, float *min_score, int num_threads) {
+  size_t S = (size_t)p->k * p->m;
+  float *sc = scores ? scores : (float *)malloc(sizeof(float) * (S ? S : 1));
+  orc_eval_all(p, g, base_traj, start, noise, p->m, p->sample_offset, iteration, sc, collisions,
+               num_threads);
+  /* ps.cu:113-122: strict <, first lowest wins, starts at +inf */
+  uint64_t mg = p->m_global ? p->m_global : p->m;
+  float lowest = INFINITY;
+  int64_t best = -1;
+  for (size_t s = 0; s < S; ++s) {
+    if (sc[s] < lowest) {
+      lowest = sc[s];
+      best = (int64_t)((s / p->m) * mg + p->sample_offset + (s % p->m));
+    }
+  }
+  if (min_score) *min_score = lowest;
+  if (!scores) free(sc);
+  return best;
+}
+
+void orc_plan_lerp(const float *start, const float *goal, uint32_t n, uint32_t d, float *out) {
+  /* ps.cu:50-52: step_sizes[dim] = (goal - current) / num_waypoints; the write
+   * of `result` is missing in the reference. */
+  for (uint32_t j = 0; j < d; ++j) {
+    float step = (goal[j] - start[j]) / (float)n;
+    for (uint32_t w = 0; w < n; ++w) out[(size_t)w * d + j] = start[j] + (float)(w + 1) * step;
+  }
+}
+
+static uint32_t orc_key_hi(const orc_params *p, float score) {
+  if (p->select_mode == ORC_SELECT_CEIL_INT) return (uint32_t)orc_round_score(score);
+  if (score != score) return 0xFFFFFFFFu;
+  uint32_t b;
+  memcpy(&b, &score, 4);
+  return b;
+}
+
+void orc_plan(const orc_params *p, const orc_grid *g, const float *start, const float *init_traj,
+              uint32_t iters, const float *noise, float *best_traj, float *best_vel,
+              float *best_score, int64_t *best_climber, float *climber_traj,
+              float *climber_scores, int32_t *climber_rounded, uint8_t *found_better,
+              int num_threads) {
+  const uint32_t k = p->k, m = p->m, n = p->n, d = p->d;
+  const size_t nd = (size_t)n * d, nnd = (size_t)p->n_noise * d;
+  float *traj = (float *)malloc(sizeof(float) * k * nd);
+  uint32_t *cur_hi = (uint32_t *)malloc(sizeof(uint32_t) * k);
+  uint8_t *fb = (uint8_t *)calloc(k, 1);
+  float *scores = (float *)malloc(sizeof(float) * (size_t)k * m);
+  float *tmpn = (float *)malloc(sizeof(float) * nnd);
+  for (uint32_t c = 0; c < k; ++c) memcpy(traj + c * nd, init_traj, sizeof(float) * nd);
+  /* gt.cu:180-191: score the unperturbed trajectory first (noise == 0) */
+  for (uint32_t c = 0; c < k; ++c) {
+    float s0 = orc_cost_sample(p, g, traj + c * nd, start, NULL, NULL, NULL, NULL, NULL, NULL, NULL);
+    cur_hi[c] = orc_key_hi(p, s0);
+  }
+  uint64_t mg = p->m_global ? p->m_global : m;
+  for (uint32_t it = 0; it < iters; ++it) {
+    const float *nz_it = noise ? noise + (size_t)it * k * mg * nnd : NULL;
+    orc_eval_all(p, g, traj, start, nz_it, (size_t)mg, 0, it, scores, NULL, num_threads);
+    for (uint32_t c = 0; c < k; ++c) {
+      /* gt.cu:109-111 atomicMin over the block, then :225-241 keep-best with
+       * the lowest sample index winning ties */
+      uint64_t best_key = UINT64_MAX;
+      for (uint32_t t = 0; t < m; ++t) {
+        uint64_t key = ((uint64_t)orc_key_hi(p, scores[(size_t)c * m + t]) << 32) |
+                       (uint32_t)(p->sample_offset + t);
+        if (key < best_key) best_key = key;
+      }
+      uint32_t hi = (uint32_t)(best_key >> 32);
+      uint64_t tg = (uint32_t)best_key;
+      if (hi < cur_hi[c]) {
+        const float *nz;
+        if (nz_it) {
+          nz = nz_it + ((size_t)c * mg + tg) * nnd;
+        } else {
+          for (uint32_t wn = 0; wn < p->n_noise; ++wn)
+            for (uint32_t j = 0; j < d; ++j) tmpn[wn * d + j] = orc_noise_at(p, it, c, tg, wn, j);
+          nz = tmpn;
+        }
+        for (uint32_t w = 0; w < n; ++w)
+          for (uint32_t j = 0; j < d; ++j)
+            traj[c * nd + (size_t)w * d + j] =
+                traj[c * nd + (size_t)w * d + j] + nz[(size_t)(p->n_noise == 1 ? 0 : w) * d + j];
+        cur_hi[c] = hi;
+        fb[c] = 1;
+      }
+    }
+  }
+  /* final: float score of every climber's kept trajectory, then ps.cu:113-122 */
+  float lowest = INFINITY;
+  int64_t bc = -1;
+  for (uint32_t c = 0; c < k; ++c) {
+    float s = orc_cost_sample(p, g, traj + c * nd, start, NULL, NULL, NULL, NULL, NULL, NULL, NULL);
+    if (climber_scores) climber_scores[c] = s;
+    if (climber_rounded) climber_rounded[c] = orc_round_score(s);
+    if (s < lowest) {
+      lowest = s;
+      bc = c;
+    }
+  }
+  uint32_t sel = bc < 0 ? 0 : (uint32_t)bc;
+  if (best_traj) memcpy(best_traj, traj + sel * nd, sizeof(float) * nd);
+  if (best_vel)
+    for (uint32_t w = 0; w < n; ++w)
+      for (uint32_t j = 0; j < d; ++j) {
+        float prior = w ? traj[sel * nd + (size_t)(w - 1) * d + j] : start[j];
+        best_vel[(size_t)w * d + j] = (traj[sel * nd + (size_t)w * d + j] - prior) / p->delta_t;
+      }
+  if (best_score) *best_score = bc < 0 ? INFINITY : lowest;
+  if (best_climber) *best_climber = (bc >= 0 && fb[bc]) ? bc : -1;
+  if (climber_traj) memcpy(climber_traj, traj, sizeof(float) * k * nd);
+  if (found_better) memcpy(found_better, fb, k);
+  free(traj);
+  free(cur_hi);
+  free(fb);
+  free(scores);
+  free(tmpn);
+}
+
+void orc_update_vector(const orc_params *p, const float *scores, const float *noise,
+                       float *update) {
+  /* gt.test.cu:200-208 (host statement of gt.cu:117-133); n_noise == 1 */
+  size_t S = (size_t)p->k * p->m;
+  float best = scores[0];
+  for (size_t s = 1; s < S; ++s)
+    if (ceilf(scores[s]) < ceilf(best)) best = scores[s]; /* gt.test.cu:201 */
+  for (uint32_t c = 0; c < p->k; ++c)
+    for (uint32_t j = 0; j < p->d; ++j) update[(size_t)c * p->d + j] = 0.0f;
+  for (uint32_t c = 0; c < p->k; ++c)
+    for (uint32_t t = 0; t < p->m; ++t)
+      for (uint32_t j = 0; j < p->d; ++j) {
+        float wgt = best / ceilf(scores[(size_t)c * p->m + t]);
+        float term = wgt * noise[((size_t)c * p->m + t) * p->d + j];
+        update[(size_t)c * p->d + j] = update[(size_t)c * p->d + j] + term;
+      }
+}
+
+void orc_build_message(const float *cur, const float *goal, const float *traj, const float *vel,
+                       uint32_t n, uint32_t d, float delta_t, float *positions,
+                       float *velocities, float *time_from_start) {
+  /* ps.cu:179-191: point 0 = current state, velocity towards waypoint 0 */
+  for (uint32_t j = 0; j < d; ++j) {
+    positions[j] = cur[j];
+    velocities[j] = (traj[j] - cur[j]) / delta_t;
+  }
+  time_from_start[0] = 0.0f;
+  /* ps.cu:192-202: look-forward velocities; the read of waypoint n runs past
+   * the end in the reference -> 0 for the last waypoint */
+  for (uint32_t i = 0; i < n; ++i) {
+    for (uint32_t j = 0; j < d; ++j) {
+      positions[(size_t)(i + 1) * d + j] = traj[(size_t)i * d + j];
+      velocities[(size_t)(i + 1) * d + j] = (i + 1 < n) ? vel[(size_t)(i + 1) * d + j] : 0.0f;
+    }
+    time_from_start[i + 1] = delta_t * (float)i;
+  }
+  /* ps.cu:204-208: goal with zero velocity */
+  for (uint32_t j = 0; j < d; ++j) {
+    positions[(size_t)(n + 1) * d + j] = goal[j];
+    velocities[(size_t)(n + 1) * d + j] = 0.0f;
+  }
+  /* the reference reuses the moved-from `point`, so the goal keeps the stamp of
+   * the last waypoint (ps.cu:200,204-208) */
+  time_from_start[n + 1] = n ? delta_t * (float)(n - 1) : 0.0f;
+}
