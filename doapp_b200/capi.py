@@ -31,7 +31,7 @@ ABI_SYMBOLS = [
     "doapp_set_limits", "doapp_noise_generate", "doapp_cost_eval", "doapp_stage_inputs",
     "doapp_cost_eval_dev", "doapp_read_results", "doapp_plan_lerp", "doapp_plan",
     "doapp_plan_async", "doapp_plan_wait", "doapp_plan_state", "doapp_replan_dynamic",
-    "doapp_plan_bench", "doapp_comm_unique_id", "doapp_comm_init", "doapp_grid_broadcast",
+    "doapp_plan_bench", "doapp_plan_profile", "doapp_comm_unique_id", "doapp_comm_init", "doapp_grid_broadcast",
     "doapp_launch_count", "doapp_debug_sincos", "doapp_debug_fk",
 ]
 
@@ -102,6 +102,7 @@ def load_library(path: str | None = None) -> C.CDLL:
     L.doapp_replan_dynamic.argtypes = [vp, f32p, f32p, f32p, C.c_uint32, f32p, C.c_size_t, f32p,
                                        vp, vp]
     L.doapp_plan_bench.argtypes = [vp, C.c_uint32, C.c_uint32, vp]
+    L.doapp_plan_profile.argtypes = [vp, C.c_uint32, vp, vp, vp]
     L.doapp_comm_unique_id.argtypes = [vp]
     L.doapp_comm_init.argtypes = [vp, vp, C.c_int32, C.c_int32]
     L.doapp_grid_broadcast.argtypes = [vp, C.c_int32]
@@ -294,6 +295,13 @@ class Context:
         ms = C.c_float()
         self._ck(self.L.doapp_plan_bench(self.h, iters, repeats, C.addressof(ms)))
         return ms.value
+
+    def plan_profile(self, iters):
+        """(summed cost-kernel ms, launches, loop ms) of one event-instrumented pass."""
+        tot, lp, cnt = C.c_float(), C.c_float(), C.c_uint32()
+        self._ck(self.L.doapp_plan_profile(self.h, iters, C.addressof(tot), C.addressof(cnt),
+                                           C.addressof(lp)))
+        return tot.value, cnt.value, lp.value
 
     def replan_dynamic(self, start, goal, init_traj, clouds):
         start, goal, init_traj, clouds = _f32(start), _f32(goal), _f32(init_traj), _f32(clouds)

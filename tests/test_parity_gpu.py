@@ -1,0 +1,128 @@
+"""GPU parity: the CUDA path (through the C ABI) against the CPU oracle on the
+same seeded inputs.  Bit-exact for voxel indices, occupancy, collision counts,
+argmin; scores are expected bit-equal too (same summation tree) and are
+additionally checked to 1e-5 relative (north_star tolerance)."""
+import numpy as np
+import pytest
+
+from tests import synth
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-5
+
+
+def _mk(capi, oracle_mod, k, m, n, d=5, n_noise=1, **kw):
+    ctx = capi.Context(k=k, m=m, n=n, d=d, n_noise=n_noise, **kw)
+    okw = {a: b for a, b in kw.items() if a not in ("update_mode", "update_gain")}
+    orc = oracle_mod.Oracle(k=k, m=m, n=n, d=d, n_noise=n_noise, **okw)
+    return ctx, orc
+
+
+def test_sincos_bit_exact(capi, oracle_mod):
+    rng = np.random.default_rng(0)
+    x = np.concatenate([rng.uniform(-8, 8, 20000), rng.uniform(-1e5, 1e5, 2000),
+                        [0.0, -0.0, 1e6, -3e7, np.pi / 2, -np.pi / 2]]).astype(np.float32)
+    with capi.Context(k=1, m=1, n=1) as ctx:
+        s, c = ctx.debug_sincos(x)
+    so, co = oracle_mod.sincos(x)
+    assert np.array_equal(s.view(np.uint32), so.view(np.uint32))
+    assert np.array_equal(c.view(np.uint32), co.view(np.uint32))
+
+
+@pytest.mark.parametrize("d", [5, 4])
+def test_fk_bit_exact(capi, oracle_mod, d):
+    rng = np.random.default_rng(1)
+    wp = rng.uniform(-3.2, 3.2, (4096, d)).astype(np.float32)
+    with capi.Context(k=1, m=1, n=1, d=d) as ctx:
+        pts = ctx.debug_fk(wp)
+    ref = oracle_mod.fk_points(wp)
+    assert np.array_equal(pts.view(np.uint32), ref.view(np.uint32))
+
+
+def test_noise_philox_bit_exact(capi, oracle_mod):
+    ctx, orc = _mk(capi, oracle_mod, 3, 257, 16, sigma=0.1, seed=1234)
+    for it in (0, 5):
+        a, b = ctx.noise(it), orc.noise(it)
+        assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
+    ctx.close()
+
+
+@pytest.mark.parametrize("frame", [0, 1])
+def test_grid_lookup_indices(capi, oracle_mod, frame):
+    g = synth.box_grid(64, 0.02)
+    rng = np.random.default_rng(2)
+    pts = rng.uniform(-0.7, 1.4, (20000, 3)).astype(np.float32)
+    # points on cell boundaries and the frame edges
+    edge = np.array([[0.64, 0, 0.5], [-0.64, 0, 0.5], [0, 0.64, 0.5], [0, 0, 1.28], [0, 0, 0],
+                     [0.1, -0.1, 0.1], [0.3, 0.1, 0.3], [0.02, 0.04, 0.06]], np.float32)
+    pts = np.concatenate([pts, edge])
+    ctx, orc = _mk(capi, oracle_mod, 1, 1, 1)
+    ctx.set_grid(g, 0.02, frame)
+    orc.set_grid(g, 0.02, frame)
+    idx, col = ctx.grid_lookup(pts)
+    assert np.array_equal(idx, orc.grid_index(pts))
+    assert np.array_equal(col, orc.grid_collides(pts))
+    assert (idx >= 0).sum() > 1000 and col.sum() > 0
+    ctx.close()
+
+
+CASES = [  # (k, m, n, d, n_noise, grid, sigma)
+    (1, 64, 32, 5, 1, "u8", 0.1),      # BASELINE config 1
+    (1, 64, 32, 5, 1, "f32", 0.1),
+    (3, 37, 50, 4, 1, "u8", 0.3),      # ragged m, d = 4 (reference's shipped d), n = 50
+    (2, 33, 33, 5, 33, "u8", 0.2),     # per-waypoint noise, n not a multiple of 32
+    (1, 1024, 64, 5, 1, "u8", 0.5),    # BASELINE config 2 shape
+    (1, 5, 1, 5, 1, "u8", 0.5),        # single waypoint
+    (1, 8, 128, 5, 1, "none", 0.1),    # no grid
+]
+
+
+@pytest.mark.parametrize("k,m,n,d,n_noise,grid,sigma", CASES)
+def test_cost_eval_parity(capi, oracle_mod, k, m, n, d, n_noise, grid, sigma):
+    ctx, orc = _mk(capi, oracle_mod, k, m, n, d, n_noise, sigma=sigma)
+    if grid == "u8":
+        g = synth.box_grid(64, 0.02)
+    elif grid == "f32":
+        g = synth.box_distance_grid(64, 0.02)
+    if grid != "none":
+        ctx.set_grid(g, 0.02)
+        orc.set_grid(g, 0.02)
+    start = synth.START[:d]
+    base = np.stack([capi.plan_lerp(start, synth.GOALS[c % 2][:d], n) for c in range(k)])
+    nz = synth.noise(k, m, n_noise, d, sigma)
+    for noise in (nz, None):  # external noise, then in-kernel Philox
+        a = ctx.cost_eval(base, start, noise, iteration=3)
+        b = orc.cost_eval(base, start, noise, iteration=3)
+        assert np.array_equal(a["collisions"], b["collisions"])
+        assert a["argmin"] == b["argmin"]
+        np.testing.assert_allclose(a["scores"], b["scores"], rtol=RTOL, atol=0)
+        assert np.array_equal(a["scores"].view(np.uint32), b["scores"].view(np.uint32))
+        assert a["min_score"] == b["min_score"]
+    if grid == "u8":
+        assert b["collisions"].sum() > 0  # the obstacle is actually hit
+    ctx.close()
+
+
+def test_as_shipped_mode(capi, oracle_mod):
+    ctx, orc = _mk(capi, oracle_mod, 2, 16, 25, 5, collision_mode=0, sigma=1.0)
+    g = synth.box_grid(64, 0.02)
+    ctx.set_grid(g, 0.02)
+    orc.set_grid(g, 0.02)
+    base = np.stack([capi.plan_lerp(synth.START, synth.GOALS[c], 25) for c in range(2)])
+    nz = synth.noise(2, 16, 1, 5, 1.0)
+    a, b = ctx.cost_eval(base, synth.START, nz), orc.cost_eval(base, synth.START, nz)
+    assert a["collisions"].sum() == 0 and b["collisions"].sum() == 0
+    assert np.array_equal(a["scores"].view(np.uint32), b["scores"].view(np.uint32))
+    ctx.close()
+
+
+def test_limits_cost(capi, oracle_mod):
+    lo, hi = -0.3 * np.ones(5, np.float32), 0.6 * np.ones(5, np.float32)
+    ctx, orc = _mk(capi, oracle_mod, 1, 64, 32, 5, limit_weight=2.0, sigma=0.3)
+    ctx.set_limits(lo, hi)
+    orc.set_limits(lo, hi)
+    base = capi.plan_lerp(synth.START, synth.GOALS[0], 32)[None]
+    nz = synth.noise(1, 64, 1, 5, 0.3)
+    a, b = ctx.cost_eval(base, synth.START, nz), orc.cost_eval(base, synth.START, nz)
+    assert np.array_equal(a["scores"].view(np.uint32), b["scores"].view(np.uint32))
+    ctx.close()
