@@ -126,3 +126,37 @@ def test_limits_cost(capi, oracle_mod):
     a, b = ctx.cost_eval(base, synth.START, nz), orc.cost_eval(base, synth.START, nz)
     assert np.array_equal(a["scores"].view(np.uint32), b["scores"].view(np.uint32))
     ctx.close()
+
+
+def test_against_reference_kernel_golden(capi):
+    """CUDA path vs the REFERENCE kernel's own outputs (optimize_trajectories run on a B200 by
+    oracle/_ref/ref_harness, tests/golden/ref_outputs.npz): AS_SHIPPED scores from the reference's
+    noise, to the float-atomicAdd order of the reference (D17)."""
+    import os
+    G = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_outputs.npz"))
+    f = lambda k: G[k].astype(np.uint32).view(np.float32)
+    k, m, n, d = (int(v) for v in G["kernel_shape_kmnd"])
+    init = f("kernel_initial_trajectory").reshape(n, d)
+    base = np.repeat(init[None], k, 0)
+    with capi.Context(k=k, m=m, n=n, d=d, collision_mode=0) as ctx:
+        r = ctx.cost_eval(base, f("kernel_start"), f("kernel_noise").reshape(k, m, 1, d))
+    ref = f("kernel_scores").reshape(k, m + 1)[:, 1:]
+    np.testing.assert_allclose(r["scores"], ref, rtol=2e-6)
+    assert r["argmin"] == int(np.argmin(ref))
+
+
+def test_c1_golden_kat(capi):
+    """BASELINE config 1 against the committed known-answer hashes (tests/golden/c1_kat.json)."""
+    import hashlib
+    import json
+    import os
+    kat = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "c1_kat.json")))
+    with capi.Context(k=1, m=64, n=32, sigma=0.1) as ctx:
+        ctx.set_grid(synth.box_grid(64, 0.02), 0.02)
+        base = capi.plan_lerp(synth.START, synth.GOALS[0], 32)[None]
+        r = ctx.cost_eval(base, synth.START, None, iteration=0)
+        nz = ctx.noise(0)
+    assert hashlib.sha256(r["scores"].tobytes()).hexdigest() == kat["scores_sha256"]
+    assert hashlib.sha256(r["collisions"].tobytes()).hexdigest() == kat["collisions_sha256"]
+    assert hashlib.sha256(nz.tobytes()).hexdigest() == kat["noise_sha256"]
+    assert r["argmin"] == kat["argmin"] and int(r["collisions"].sum()) == kat["collisions_total"]
