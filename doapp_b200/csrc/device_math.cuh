@@ -63,6 +63,32 @@ DM_HD float div_(float a, float b) {
 #endif
 }
 
+// ---------------------------------------------------------------------------
+// Division by a loop-invariant divisor b with a precomputed r = RN(1/b):
+//   q0 = RN(a*r); e = fma(-b, q0, a) (exact); q = fma(e, r, q0)
+// (Markstein).  For b, r normal and |a| in [2^-60, 2^60] (or a == 0) no
+// intermediate is subnormal or overflows and q == RN(a/b); the C ABI verifies
+// this EXHAUSTIVELY on the device for each divisor it is given
+// (doapp_capi.cu: verify_fast_div) and the kernels fall back to the IEEE
+// divide outside that interval, so every quotient is bit-identical to a / b.
+struct FastDiv {
+  float b, r;
+  float lo, hi; // |a| in [lo, hi) (or a == 0) takes the fast path; lo = +inf disables it
+};
+constexpr float kFastDivLo = 0x1p-60f, kFastDivHi = 0x1p+60f;
+
+DM_HD float div_fast_unguarded(float a, FastDiv d) {
+  float q0 = mul_(a, d.r);
+  float e = fma_(-d.b, q0, a);
+  return fma_(e, d.r, q0);
+}
+DM_HD float div_fast(float a, FastDiv d) {
+  float q = div_fast_unguarded(a, d);
+  float aa = fabsf(a);
+  if (!(aa == 0.0f || (aa >= d.lo && aa < d.hi))) q = div_(a, d.b);
+  return q;
+}
+
 constexpr float kTwoOverPi = 0x1.45f306p-1f;
 constexpr float kP1 = 0x1.921fb6p+0f;   // RN(pi/2)
 constexpr float kP2 = -0x1.777a5cp-25f; // RN(pi/2 - P1)
@@ -205,6 +231,22 @@ DM_HD float noise_at(uint32_t seed_lo, uint32_t seed_hi, float sigma, uint32_t i
   uint32_t a = (j & 2u) ? r.z : r.x;
   uint32_t b = (j & 2u) ? r.w : r.y;
   return box_muller(a, b, (j & 1u) != 0, sigma);
+}
+
+// all D noise elements of one (sample, noise waypoint): joints 0-3 share one Philox
+// call, joint 4 takes the second (same values as noise_at element by element)
+template <int D>
+DM_HD void noise_vec(uint32_t seed_lo, uint32_t seed_hi, float sigma, uint32_t iteration,
+                     uint32_t c, uint32_t t_global, uint32_t wn, float (&out)[D]) {
+  u4 r = philox4x32_10(t_global, c, wn, 2u * iteration, seed_lo, seed_hi);
+  out[0] = box_muller(r.x, r.y, false, sigma);
+  out[1] = box_muller(r.x, r.y, true, sigma);
+  out[2] = box_muller(r.z, r.w, false, sigma);
+  out[3] = box_muller(r.z, r.w, true, sigma);
+  if (D > 4) {
+    u4 q = philox4x32_10(t_global, c, wn, 2u * iteration + 1u, seed_lo, seed_hi);
+    out[D > 4 ? 4 : 0] = box_muller(q.x, q.y, false, sigma);
+  }
 }
 
 } // namespace dm

@@ -98,6 +98,9 @@ struct doapp_ctx {
   float lim_min[kMaxJoints]{}, lim_max[kMaxJoints]{};
   int use_limits = 0;
   float rpy_s = 0.0f, rpy_c = 0.0f;
+  dm::FastDiv dt_div{};            // verified at create (verify_fast_div)
+  DevBuf<unsigned long long> vbad; // mismatch counter of the verification kernels
+  bool fast_math_ok = true;        // DOAPP_EXACT_DIV=1 forces the IEEE divides
 
   // staged planner inputs
   bool plan_staged = false, plan_pending = false;
@@ -179,6 +182,31 @@ void invalidate_graph(doapp_ctx *ctx) {
   }
 }
 
+uint32_t f2u(float f) {
+  uint32_t u;
+  memcpy(&u, &f, 4);
+  return u;
+}
+
+// Runs the exhaustive device check of dm::div_fast_unguarded against __fdiv_rn for divisor b
+// over the floats with bit patterns [lo_bits, hi_bits]; *ok = no mismatch.
+doapp_status verify_fast_div(doapp_ctx *ctx, float b, uint32_t lo_bits, uint32_t hi_bits, int mode,
+                             bool *ok) {
+  *ok = false;
+  volatile float rcp = 1.0f / b;
+  if (!ctx->fast_math_ok || !(b > 0x1p-60f && b < 0x1p+60f)) return DOAPP_OK;
+  ST(ensure(ctx, ctx->vbad, 1));
+  CU(cudaMemsetAsync(ctx->vbad.p, 0, sizeof(unsigned long long), ctx->stream));
+  dm::FastDiv d{b, rcp, 0.0f, 0.0f};
+  CU(launch_verify_div(d, lo_bits, hi_bits, mode, ctx->vbad.p, ctx->sm_count, ctx->stream));
+  ctx->launches += 1;
+  unsigned long long bad = 1;
+  CU(cudaMemcpyAsync(&bad, ctx->vbad.p, sizeof(bad), cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  *ok = bad == 0;
+  return DOAPP_OK;
+}
+
 CostParams base_cost_params(doapp_ctx *ctx) {
   const doapp_config &c = ctx->cfg;
   CostParams p{};
@@ -208,7 +236,7 @@ CostParams base_cost_params(doapp_ctx *ctx) {
   p.rpy_s = ctx->rpy_s;
   p.rpy_c = ctx->rpy_c;
   p.grid = ctx->grid;
-  p.total_samples = ctx->S;
+  p.dt_div = ctx->dt_div;
   return p;
 }
 
@@ -222,7 +250,6 @@ CostParams climber_cost_params(doapp_ctx *ctx) {
   p.n_noise = 1;
   p.sample_offset = 0;
   p.m_global = 1;
-  p.total_samples = ctx->cfg.num_climbers;
   return p;
 }
 
@@ -441,6 +468,8 @@ doapp_status doapp_create(const doapp_config *cfg, doapp_ctx **out) {
                 cfg->struct_size, sizeof(doapp_config));
   if (cfg->num_climbers == 0 || cfg->samples_per_climber == 0)
     return fail(nullptr, DOAPP_INVALID_ARG, "doapp_create: k and m must be > 0");
+  if (cfg->num_climbers > 65535)
+    return fail(nullptr, DOAPP_INVALID_ARG, "doapp_create: num_climbers must be <= 65535");
   if (cfg->num_waypoints == 0 || cfg->num_waypoints > 1024)
     return fail(nullptr, DOAPP_INVALID_ARG, "doapp_create: num_waypoints must be in 1..1024");
   if (cfg->waypoint_dim != 4 && cfg->waypoint_dim != 5)
@@ -475,6 +504,8 @@ doapp_status doapp_create(const doapp_config *cfg, doapp_ctx **out) {
   ctx->S = (uint64_t)cfg->num_climbers * cfg->samples_per_climber;
   const char *ng = getenv("DOAPP_NO_GRAPH");
   ctx->use_graph = !(ng && ng[0] == '1');
+  const char *xd = getenv("DOAPP_EXACT_DIV");
+  ctx->fast_math_ok = !(xd && xd[0] == '1');
   host_sincos(-1.5707963267948966f, &ctx->rpy_s, &ctx->rpy_c);
   doapp_status st = [&]() -> doapp_status {
     cudaDeviceProp prop;
@@ -500,6 +531,13 @@ doapp_status doapp_create(const doapp_config *cfg, doapp_ctx **out) {
     CU(cudaMemsetAsync(ctx->start.p, 0, sizeof(float) * 8, ctx->stream));
     CU(cudaMemsetAsync(ctx->found.p, 0, k, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
+    // velocity / acceleration divides: reciprocal-multiply path, proven against the IEEE
+    // divide for EVERY dividend in [2^-60, 2^60) for this delta_t, else disabled
+    bool ok = false;
+    ST(verify_fast_div(ctx, cfg->delta_t, f2u(dm::kFastDivLo), f2u(dm::kFastDivHi) - 1, 0, &ok));
+    volatile float rcp = 1.0f / cfg->delta_t;
+    ctx->dt_div = dm::FastDiv{cfg->delta_t, rcp, ok ? dm::kFastDivLo : INFINITY,
+                              ok ? dm::kFastDivHi : INFINITY};
     return DOAPP_OK;
   }();
   if (st != DOAPP_OK) {
@@ -526,7 +564,7 @@ void doapp_destroy(doapp_ctx *ctx) {
   release(ctx->pts); release(ctx->coll); release(ctx->final_coll); release(ctx->keys);
   release(ctx->keys_float); release(ctx->cur_hi); release(ctx->found); release(ctx->grid_cells);
   release(ctx->lookup_coll); release(ctx->lookup_idx); release(ctx->dbg_a); release(ctx->dbg_b);
-  release(ctx->dbg_c);
+  release(ctx->dbg_c); release(ctx->vbad);
   for (cudaEvent_t e : ctx->prof_events) cudaEventDestroy(e);
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->ev1) cudaEventDestroy(ctx->ev1);
@@ -549,6 +587,8 @@ doapp_status doapp_grid_alloc(doapp_ctx *ctx, int32_t kind, int32_t frame, uint3
     return fail(ctx, DOAPP_INVALID_ARG, "doapp_grid_alloc: FRAME_OG grids are cubes");
   CU(cudaSetDevice(ctx->cfg.device));
   const size_t cells = (size_t)nx * ny * nz;
+  if (cells >= (1ull << 32))
+    return fail(ctx, DOAPP_INVALID_ARG, "doapp_grid_alloc: %zu cells (limit 2^32 - 1)", cells);
   const size_t bytes = cells * (kind == DOAPP_GRID_F32 ? 4 : 1);
   ST(ensure(ctx, ctx->grid_cells, bytes));
   if (kind == DOAPP_GRID_U8) {
@@ -572,6 +612,18 @@ doapp_status doapp_grid_alloc(doapp_ctx *ctx, int32_t kind, int32_t frame, uint3
   g.z_max = (float)((double)nz * resolution);                 // :81-82
   g.res_d = resolution;
   g.half_d = ((double)nx * resolution) / 2.0;                 // occupancy_grid.cpp:31
+  {
+    // voxel-index divides (cpu_distance_grid.cu:120-122): every dividend the CDG frame can
+    // produce lies in [0, max(2*x_off, 2*y_off, z_max)]; check the truncated quotient of the
+    // reciprocal-multiply path against the IEEE divide for ALL of them
+    volatile float rr = 1.0f / g.res;
+    g.res_rcp = rr;
+    float top = fmaxf(fmaxf(2.0f * g.x_off, 2.0f * g.y_off), g.z_max);
+    bool ok = false;
+    if (frame == DOAPP_FRAME_CDG && top < dm::kFastDivHi)
+      ST(verify_fast_div(ctx, g.res, 0u, f2u(top), 1, &ok));
+    g.fast_idx = ok ? 1 : 0;
+  }
   ctx->grid = g;
   ctx->grid_bytes = bytes;
   ctx->grid_generation++;

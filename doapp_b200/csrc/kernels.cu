@@ -153,123 +153,220 @@ __device__ __forceinline__ uint32_t key_hi_float(float score) {
 }
 
 // ---------------------------------------------------------------- cost kernel
-template <int D>
-__global__ void __launch_bounds__(kCostThreads)
-    cost_kernel(const __grid_constant__ CostParams P) {
-  const int lane = threadIdx.x & 31;
-  const uint64_t warp = (uint64_t)blockIdx.x * (kCostThreads / 32) + (threadIdx.x >> 5);
-  const uint64_t s_begin = warp * P.samples_per_warp;
-  if (s_begin >= P.total_samples) return;
-  uint64_t s_end = s_begin + P.samples_per_warp;
-  if (s_end > P.total_samples) s_end = P.total_samples;
+// One thread = one sample x one run of waypoint segments.  The 32 lanes of a
+// warp are 32 consecutive samples of one climber walking the SAME waypoints, so
+// the base-trajectory reads are warp-uniform shared-memory broadcasts, the
+// neighbouring link points of the 32 perturbed copies gather from neighbouring
+// voxels, and xprev / vprev stay in registers (no shuffles, no scratch arrays:
+// the reference materialises noisy trajectories, velocities and accelerations
+// in global memory, generate_trajectories.cu:202-210).
+//
+// Sum order (fixed, independent of the launch geometry; oracle ORC_SUM_SEG4):
+// per-waypoint sums folded left to right inside segments of kSeg waypoints,
+// segment partials folded left to right.  With T > 1 threads per sample each
+// thread owns whole segments and leaves its partials in shared memory; thread 0
+// of the sample folds them.
+constexpr int kSeg = 4;
+constexpr int kMaxCostThreads = 512;
 
+// Grid modes the kernel is specialised for.
+enum : int { GM_NONE = 0, GM_U8_CDG = 1, GM_F32_CDG = 2, GM_GENERIC = 3 };
+
+template <int GM, bool FIDX>
+__device__ __forceinline__ int collides(const CostParams &P, P3 p) {
+  if (GM == GM_NONE) return 0;
+  if (GM == GM_GENERIC) return grid_collides(P.grid, p.x, p.y, p.z, P.coll_dist);
+  const GridDev &g = P.grid;
+  // cpu_distance_grid.cu:115-117 (half-open), branch-free
+  bool in = (p.x >= -g.x_off) & (p.x < g.x_off) & (p.y >= -g.y_off) & (p.y < g.y_off) &
+            (p.z >= 0.0f) & (p.z < g.z_max);
+  const float ax = dm::add_(p.x, g.x_off), ay = dm::add_(p.y, g.y_off);
+  float fx, fy, fz; // :120-122, IEEE quotients (verified-exact fast path when FIDX)
+  if (FIDX) {
+    fx = dm::div_fast_unguarded(ax, P.res_div);
+    fy = dm::div_fast_unguarded(ay, P.res_div);
+    fz = dm::div_fast_unguarded(p.z, P.res_div);
+  } else {
+    fx = dm::div_(ax, g.res);
+    fy = dm::div_(ay, g.res);
+    fz = dm::div_(p.z, g.res);
+  }
+  const uint32_t ix = __float2uint_rz(fx), iy = __float2uint_rz(fy), iz = __float2uint_rz(fz);
+  in = in & (ix < g.nx) & (iy < g.ny) & (iz < g.nz);
+  const uint32_t lin = in ? (iz * g.ny + iy) * g.nx + ix : 0u; // < 2^32 cells (grid_alloc)
+  if (GM == GM_U8_CDG) return in & (__ldg((const uint8_t *)g.cells + lin) != 0);
+  return in & (__ldg((const float *)g.cells + lin) <= P.coll_dist); // generate_trajectories.cu:412
+}
+
+template <int D, int GM, bool FIDX>
+__device__ __forceinline__ int num_collisions_v2(const CostParams &P, const float (&x)[D]) {
+  P3 pts[5];
+  fk_points<D>(x, P.rpy_s, P.rpy_c, pts);
+  int cnt = 0;
+#pragma unroll
+  for (int l = 0; l < 5; ++l) cnt += collides<GM, FIDX>(P, pts[l]);
+  return cnt;
+}
+
+__device__ __forceinline__ unsigned long long warp_min_u64(unsigned long long v) {
+#pragma unroll
+  for (int off = 16; off >= 1; off >>= 1) {
+    unsigned long long o = __shfl_xor_sync(kFull, v, off);
+    v = o < v ? o : v;
+  }
+  return v;
+}
+
+template <int D, int GM, bool NPW, bool FIDX>
+__global__ void __launch_bounds__(kMaxCostThreads)
+    cost_kernel(const __grid_constant__ CostParams P) {
+  constexpr int DP = D == 4 ? 4 : 8; // padded joints per waypoint in shared memory
+  extern __shared__ __align__(16) float smem[];
+  float *sbase = smem;                               // [n][DP]
+  float *spart = sbase + (size_t)P.n * DP;           // [nseg][samples/block]   (T > 1)
+  const uint32_t T = 1u << P.parts_log2;
+  const uint32_t spb = (blockDim.x >> 5 >> P.parts_log2) * 32; // samples per block
+  float *slim = spart + (size_t)P.nseg * spb;        // [nseg][samples/block]   (T > 1, limits)
+  int *scoll = (int *)(slim + (P.use_limits ? (size_t)P.nseg * spb : 0)); // [T][samples/block]
+
+  const uint32_t c = blockIdx.y;
+  const int lane = threadIdx.x & 31;
+  const uint32_t warp = threadIdx.x >> 5;
+  const uint32_t part = warp & (T - 1), sw = warp >> P.parts_log2;
+  const uint32_t si = sw * 32 + lane; // sample slot inside the block
+  uint32_t t = blockIdx.x * spb + si;
+  const bool active = t < P.m;
+  t = active ? t : P.m - 1; // idle lanes shadow the last sample (no divergence, no stores)
+  const uint32_t tg = (uint32_t)(P.sample_offset + t);
+
+  // stage the climber's trajectory: SoA [j][npad] in global -> AoS [w][DP] in shared
+  {
+    const float *traj = P.traj + (size_t)c * D * P.npad;
+    for (uint32_t i = threadIdx.x; i < P.n * D; i += blockDim.x) {
+      const uint32_t j = i / P.n, w = i - j * P.n;
+      sbase[w * DP + j] = __ldg(traj + (size_t)j * P.npad + w);
+    }
+  }
   float start[D];
 #pragma unroll
   for (int j = 0; j < D; ++j) start[j] = __ldg(P.start + j);
 
-  unsigned long long run_key = kKeyNone, run_keyf = kKeyNone;
-  uint32_t run_c = 0xFFFFFFFFu;
-
-  for (uint64_t s = s_begin; s < s_end; ++s) {
-    const uint32_t c = (uint32_t)(s / P.m);
-    const uint32_t t = (uint32_t)(s - (uint64_t)c * P.m);
-    const uint32_t tg = (uint32_t)(P.sample_offset + t);
-    if (c != run_c) {
-      if (lane == 0 && run_c != 0xFFFFFFFFu) {
-        if (P.keys) atomicMin(P.keys + run_c, run_key);
-        if (P.keys_float) atomicMin(P.keys_float + run_c, run_keyf);
-      }
-      run_c = c;
-      run_key = kKeyNone;
-      run_keyf = kKeyNone;
+  const float *nz = nullptr;
+  if (P.noise_mode == NOISE_EXTERNAL)
+    nz = P.noise + ((size_t)c * P.noise_m + (size_t)(tg - P.noise_t0)) * P.n_noise * D;
+  float eps[D];
+#pragma unroll
+  for (int j = 0; j < D; ++j) eps[j] = 0.0f;
+  if (!NPW) {
+    if (P.noise_mode == NOISE_EXTERNAL) {
+#pragma unroll
+      for (int j = 0; j < D; ++j) eps[j] = __ldg(nz + j);
+    } else if (P.noise_mode == NOISE_PHILOX) {
+      dm::noise_vec<D>(P.seed_lo, P.seed_hi, P.sigma, P.iteration, c, tg, 0, eps);
     }
-    const float *traj = P.traj + (size_t)c * D * P.npad;
-    const float *nz = nullptr;
-    if (P.noise_mode == NOISE_EXTERNAL)
-      nz = P.noise + ((size_t)c * P.noise_m + (size_t)(tg - P.noise_t0)) * P.n_noise * D;
+  }
+  __syncthreads();
 
-    float eps[D];
-#pragma unroll
-    for (int j = 0; j < D; ++j) eps[j] = 0.0f;
-    if (P.n_noise == 1) {
-      if (P.noise_mode == NOISE_EXTERNAL) {
-#pragma unroll
-        for (int j = 0; j < D; ++j) eps[j] = __ldg(nz + j);
-      } else if (P.noise_mode == NOISE_PHILOX) {
-#pragma unroll
-        for (int j = 0; j < D; ++j)
-          eps[j] = dm::noise_at(P.seed_lo, P.seed_hi, P.sigma, P.iteration, c, tg, 0, j);
-      }
+  // noisy position of joint j at waypoint w (generate_trajectories.cu:53-57)
+  auto noisy = [&](uint32_t w, int j) -> float {
+    float e = eps[j];
+    if (NPW) {
+      if (P.noise_mode == NOISE_EXTERNAL)
+        e = __ldg(nz + (size_t)w * D + j);
+      else if (P.noise_mode == NOISE_PHILOX)
+        e = dm::noise_at(P.seed_lo, P.seed_hi, P.sigma, P.iteration, c, tg, w, j);
     }
+    return dm::add_(sbase[w * DP + j], e);
+  };
 
-    float carry_x[D], carry_v[D];
+  const uint32_t seg0 = part * P.segs_per_part;
+  uint32_t seg1 = seg0 + P.segs_per_part;
+  seg1 = seg1 < P.nseg ? seg1 : P.nseg;
+  uint32_t w = seg0 * kSeg;
+
+  // priors of the first owned waypoint: the initial waypoint for BOTH derivative
+  // passes at w = 0 (generate_trajectories.cu:285), else recomputed
+  float xprev[D], vprev[D];
+  if (w == 0) {
+#pragma unroll
+    for (int j = 0; j < D; ++j) xprev[j] = vprev[j] = start[j];
+  } else if (seg0 < P.nseg) {
 #pragma unroll
     for (int j = 0; j < D; ++j) {
-      carry_x[j] = start[j];
-      carry_v[j] = start[j];
+      const float x1 = noisy(w - 1, j);
+      const float x2 = w >= 2 ? noisy(w - 2, j) : start[j];
+      xprev[j] = x1;
+      vprev[j] = dm::div_fast(dm::sub_(x1, x2), P.dt_div);
     }
-    float part = 0.0f, lpart = 0.0f;
-    int coll = 0;
-
-    for (uint32_t w0 = 0; w0 < P.n; w0 += 32) {
-      const uint32_t w = w0 + lane;
-      const bool valid = w < P.n;
-      float x[D];
-      float a2 = 0.0f, l2 = 0.0f;
-#pragma unroll
-      for (int j = 0; j < D; ++j) {
-        float b = valid ? __ldg(traj + (size_t)j * P.npad + w) : 0.0f;
-        float e = eps[j];
-        if (P.n_noise != 1 && valid) {
-          if (P.noise_mode == NOISE_EXTERNAL)
-            e = __ldg(nz + (size_t)w * D + j);
-          else if (P.noise_mode == NOISE_PHILOX)
-            e = dm::noise_at(P.seed_lo, P.seed_hi, P.sigma, P.iteration, c, tg, w, j);
-        }
-        x[j] = dm::add_(b, e); // generate_trajectories.cu:53-57
-        // prior position: lane-1, or the previous chunk's lane 31, or the
-        // initial waypoint for waypoint 0 (generate_trajectories.cu:285)
-        float xp = __shfl_up_sync(kFull, x[j], 1);
-        float cx = __shfl_sync(kFull, carry_x[j], 31);
-        if (lane == 0) xp = cx;
-        float v = dm::div_(dm::sub_(x[j], xp), P.dt); // :288
-        float vp = __shfl_up_sync(kFull, v, 1);
-        float cv = __shfl_sync(kFull, carry_v[j], 31);
-        if (lane == 0) vp = cv;
-        float a = dm::div_(dm::sub_(v, vp), P.dt);
-        a2 = dm::add_(a2, dm::mul_(a, a)); // :76
-        carry_x[j] = x[j];
-        carry_v[j] = v;
-        if (P.use_limits) {
-          float h = fmaxf(0.0f, fmaxf(dm::sub_(x[j], P.lim_max[j]), dm::sub_(P.lim_min[j], x[j])));
-          l2 = dm::add_(l2, dm::mul_(h, h));
-        }
-      }
-      if (valid) {
-        part = dm::add_(part, a2);
-        lpart = dm::add_(lpart, l2);
-        if (P.collision_mode != 0 && P.grid.kind != 0) coll += num_collisions<D>(P, x);
-      }
-    }
-    const float sum = butterfly_sum(part);
-    const int coll_all = __reduce_add_sync(kFull, coll);
-    float score = dm::add_((float)coll_all, dm::mul_(P.smooth_scale, sum)); // :81,100,107-108
-    if (P.use_limits && P.limit_weight != 0.0f) {
-      const float lsum = butterfly_sum(lpart);
-      score = dm::add_(score, dm::mul_(P.limit_weight, lsum));
-    }
-    if (lane == 0) {
-      if (P.scores) P.scores[s] = score;
-      if (P.collisions) P.collisions[s] = coll_all;
-    }
-    unsigned long long key = ((unsigned long long)key_hi(P.select_mode, score) << 32) | tg;
-    unsigned long long keyf = ((unsigned long long)key_hi_float(score) << 32) | tg;
-    run_key = key < run_key ? key : run_key;
-    run_keyf = keyf < run_keyf ? keyf : run_keyf;
   }
-  if (lane == 0 && run_c != 0xFFFFFFFFu) {
-    if (P.keys) atomicMin(P.keys + run_c, run_key);
-    if (P.keys_float) atomicMin(P.keys_float + run_c, run_keyf);
+
+  float total = 0.0f, ltotal = 0.0f;
+  int coll = 0;
+  for (uint32_t seg = seg0; seg < seg1; ++seg) {
+    float ps = 0.0f, pl = 0.0f;
+#pragma unroll
+    for (int u = 0; u < kSeg; ++u, ++w) {
+      if (w < P.n) {
+        float x[D];
+        float a2 = 0.0f, l2 = 0.0f;
+#pragma unroll
+        for (int j = 0; j < D; ++j) {
+          x[j] = noisy(w, j);
+          const float v = dm::div_fast(dm::sub_(x[j], xprev[j]), P.dt_div);  // :288
+          const float a = dm::div_fast(dm::sub_(v, vprev[j]), P.dt_div);
+          a2 = dm::add_(a2, dm::mul_(a, a));                                  // :76
+          xprev[j] = x[j];
+          vprev[j] = v;
+          if (P.use_limits) {
+            const float h =
+                fmaxf(0.0f, fmaxf(dm::sub_(x[j], P.lim_max[j]), dm::sub_(P.lim_min[j], x[j])));
+            l2 = dm::add_(l2, dm::mul_(h, h));
+          }
+        }
+        ps = dm::add_(ps, a2);
+        pl = dm::add_(pl, l2);
+        if (GM != GM_NONE && P.collision_mode != 0) coll += num_collisions_v2<D, GM, FIDX>(P, x);
+      }
+    }
+    if (T == 1) {
+      total = dm::add_(total, ps);
+      ltotal = dm::add_(ltotal, pl);
+    } else {
+      spart[seg * spb + si] = ps;
+      if (P.use_limits) slim[seg * spb + si] = pl;
+    }
+  }
+  if (T > 1) {
+    scoll[part * spb + si] = coll;
+    __syncthreads();
+    if (part != 0) return;
+    coll = 0;
+    for (uint32_t q = 0; q < T; ++q) coll += scoll[q * spb + si];
+    for (uint32_t seg = 0; seg < P.nseg; ++seg) {
+      total = dm::add_(total, spart[seg * spb + si]);
+      if (P.use_limits) ltotal = dm::add_(ltotal, slim[seg * spb + si]);
+    }
+  }
+
+  float score = dm::add_((float)coll, dm::mul_(P.smooth_scale, total)); // :81,100,107-108
+  if (P.use_limits && P.limit_weight != 0.0f)
+    score = dm::add_(score, dm::mul_(P.limit_weight, ltotal));
+  if (active) {
+    const size_t s = (size_t)c * P.m + t;
+    if (P.scores) P.scores[s] = score;
+    if (P.collisions) P.collisions[s] = coll;
+  }
+  if (P.keys) {
+    unsigned long long key =
+        active ? ((unsigned long long)key_hi(P.select_mode, score) << 32) | tg : kKeyNone;
+    key = warp_min_u64(key);
+    if (lane == 0) atomicMin(P.keys + c, key);
+  }
+  if (P.keys_float) {
+    unsigned long long key =
+        active ? ((unsigned long long)key_hi_float(score) << 32) | tg : kKeyNone;
+    key = warp_min_u64(key);
+    if (lane == 0) atomicMin(P.keys_float + c, key);
   }
 }
 
@@ -432,6 +529,26 @@ __global__ void debug_fk_kernel(const float *wp, uint64_t count, float rpy_s, fl
   }
 }
 
+// Exhaustive check of the reciprocal-multiply division against the IEEE divide for every
+// float whose bit pattern lies in [lo_bits, hi_bits].  mode 0: quotient bits must match;
+// mode 1: the truncated quotient (voxel index) must match.
+__global__ void verify_div_kernel(dm::FastDiv d, uint32_t lo_bits, uint32_t hi_bits, int mode,
+                                  unsigned long long *bad) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  unsigned long long mine = 0;
+  for (uint64_t u = (uint64_t)lo_bits + blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+       u <= hi_bits; u += stride) {
+    const float a = __uint_as_float((uint32_t)u);
+    const float f = dm::div_fast_unguarded(a, d), e = __fdiv_rn(a, d.b);
+    if (mode == 0)
+      mine += __float_as_uint(f) != __float_as_uint(e);
+    else
+      mine += __float2uint_rz(f) != __float2uint_rz(e);
+  }
+  mine = __reduce_add_sync(kFull, (unsigned)mine);
+  if ((threadIdx.x & 31) == 0 && mine) atomicAdd(bad, mine);
+}
+
 inline unsigned blocks_for(uint64_t total, unsigned threads) {
   return (unsigned)((total + threads - 1) / threads);
 }
@@ -440,23 +557,72 @@ inline unsigned blocks_for(uint64_t total, unsigned threads) {
 
 void host_sincos(float x, float *s, float *c) { dm::sincos(x, s, c); }
 
+template <int D, int GM, bool NPW>
+static cudaError_t launch_cost_t(const CostParams &p, dim3 grid, unsigned threads, size_t smem,
+                                 bool fidx, cudaStream_t st) {
+  auto go = [&](auto kern) -> cudaError_t {
+    if (smem > 48 * 1024) {
+      cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           (int)smem);
+      if (e != cudaSuccess) return e;
+    }
+    kern<<<grid, threads, smem, st>>>(p);
+    return cudaGetLastError();
+  };
+  if (fidx && (GM == GM_U8_CDG || GM == GM_F32_CDG)) return go(cost_kernel<D, GM, NPW, true>);
+  return go(cost_kernel<D, GM, NPW, false>);
+}
+
+template <int D>
+static cudaError_t launch_cost_d(const CostParams &p, dim3 grid, unsigned threads, size_t smem,
+                                 cudaStream_t st) {
+  int gm = GM_NONE;
+  if (p.collision_mode != 0 && p.grid.kind != 0 && p.grid.cells)
+    gm = p.grid.frame != 0 ? GM_GENERIC : (p.grid.kind == 1 ? GM_U8_CDG : GM_F32_CDG);
+  const bool npw = p.n_noise != 1 && p.noise_mode != NOISE_ZERO;
+  const bool fidx = p.grid.fast_idx != 0;
+#define DOAPP_GO(GMV)                                                                 \
+  return npw ? launch_cost_t<D, GMV, true>(p, grid, threads, smem, fidx, st)          \
+             : launch_cost_t<D, GMV, false>(p, grid, threads, smem, fidx, st)
+  switch (gm) {
+  case GM_U8_CDG: DOAPP_GO(GM_U8_CDG);
+  case GM_F32_CDG: DOAPP_GO(GM_F32_CDG);
+  case GM_GENERIC: DOAPP_GO(GM_GENERIC);
+  default: DOAPP_GO(GM_NONE);
+  }
+#undef DOAPP_GO
+}
+
 cudaError_t launch_cost(const CostParams &p_in, int d, int sm_count, cudaStream_t st) {
   CostParams p = p_in;
-  if (p.total_samples == 0) return cudaSuccess;
-  // One warp per sample while that fits the resident warps of the chip, else
-  // a contiguous run of samples per warp (blocked, so a warp's per-climber
-  // running argmin needs one atomic per climber it touches).
-  const uint64_t warps_per_block = kCostThreads / 32;
-  const uint64_t resident_warps = (uint64_t)sm_count * 64; // 2048 threads / SM
-  uint64_t spw = (p.total_samples + resident_warps - 1) / resident_warps;
-  if (spw < 1) spw = 1;
-  p.samples_per_warp = (uint32_t)spw;
-  const uint64_t warps = (p.total_samples + spw - 1) / spw;
-  const unsigned blocks = (unsigned)((warps + warps_per_block - 1) / warps_per_block);
-  if (d == 5)
-    cost_kernel<5><<<blocks, kCostThreads, 0, st>>>(p);
-  else
-    cost_kernel<4><<<blocks, kCostThreads, 0, st>>>(p);
+  if (p.k == 0 || p.m == 0) return cudaSuccess;
+  p.nseg = (p.n + kSeg - 1) / kSeg;
+  p.res_div = dm::FastDiv{p.grid.res, p.grid.res_rcp, 0.0f, 0.0f};
+  // Threads per sample: 1 when the samples alone fill the chip, else split each sample's
+  // segments over up to 16 warps so that small problems (config 2: 1024 samples) still
+  // put ~16 warps on every SM and the dependent chain per thread is a few waypoints.
+  const uint64_t sample_warps = (uint64_t)p.k * ((p.m + 31) / 32);
+  const uint64_t target_warps = (uint64_t)sm_count * 16;
+  uint32_t lg = 0;
+  while (lg < 4 && (2u << lg) <= p.nseg && sample_warps * (1u << lg) < target_warps) ++lg;
+  p.parts_log2 = lg;
+  const uint32_t T = 1u << lg;
+  p.segs_per_part = (p.nseg + T - 1) / T;
+  const uint32_t sw = T >= 4 ? 1 : 4 / T; // sample-warps per block (>= 4 warps per block)
+  const unsigned threads = 32 * T * sw;
+  const uint32_t spb = 32 * sw;
+  const dim3 grid((p.m + spb - 1) / spb, p.k);
+  const int dp = d == 4 ? 4 : 8;
+  size_t smem = (size_t)p.n * dp * sizeof(float);
+  if (T > 1)
+    smem += ((size_t)p.nseg * spb * (p.use_limits ? 2 : 1) + (size_t)T * spb) * sizeof(float);
+  return d == 5 ? launch_cost_d<5>(p, grid, threads, smem, st)
+                : launch_cost_d<4>(p, grid, threads, smem, st);
+}
+
+cudaError_t launch_verify_div(dm::FastDiv d, uint32_t lo_bits, uint32_t hi_bits, int mode,
+                              unsigned long long *bad, int sm_count, cudaStream_t st) {
+  verify_div_kernel<<<sm_count * 8, 256, 0, st>>>(d, lo_bits, hi_bits, mode, bad);
   return cudaGetLastError();
 }
 

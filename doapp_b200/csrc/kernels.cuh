@@ -5,6 +5,8 @@
 #include <cstdint>
 #include <cuda_runtime.h>
 
+#include "device_math.cuh"
+
 namespace doapp {
 
 constexpr int kMaxJoints = 5;
@@ -22,6 +24,10 @@ struct GridDev {
   float res, x_off, y_off, z_max;
   // OG frame (occupancy_grid.cpp:29-40), fp64
   double res_d, half_d;
+  // 1: the reciprocal-multiply index quotient was verified equal to the IEEE one for
+  // every dividend this frame can produce (doapp_capi.cu: verify_fast_index)
+  int fast_idx;
+  float res_rcp;
 };
 
 struct CostParams {
@@ -46,8 +52,10 @@ struct CostParams {
   int32_t *collisions;           // [k*m] or nullptr
   unsigned long long *keys;      // [k] packed argmin keys for the update rule, or nullptr
   unsigned long long *keys_float; // [k] packed (float bits, t) keys for the host-style argmin
-  uint32_t samples_per_warp;
-  uint64_t total_samples;
+  dm::FastDiv dt_div, res_div; // divisor + RN(1/divisor)
+  // launch geometry (filled by launch_cost): 2^parts_log2 threads per sample, each owning
+  // segs_per_part segments of 4 waypoints; nseg = ceil(n / 4)
+  uint32_t parts_log2, segs_per_part, nseg;
 };
 
 struct UpdateParams {
@@ -84,6 +92,8 @@ struct ScatterParams {
 };
 
 cudaError_t launch_cost(const CostParams &p, int d, int sm_count, cudaStream_t st);
+cudaError_t launch_verify_div(dm::FastDiv d, uint32_t lo_bits, uint32_t hi_bits, int mode,
+                              unsigned long long *bad, int sm_count, cudaStream_t st);
 cudaError_t launch_update(const UpdateParams &p, cudaStream_t st);
 cudaError_t launch_final(const FinalParams &p, cudaStream_t st);
 cudaError_t launch_scatter(const ScatterParams &p, int sm_count, cudaStream_t st);

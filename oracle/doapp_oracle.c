@@ -24,7 +24,7 @@ void orc_params_init(orc_params *p) {
   p->collision_distance = 0.05f; /* gt.cu:389 */
   p->collision_mode = ORC_COLLISION_INTENDED;
   p->select_mode = ORC_SELECT_CEIL_INT;
-  p->sum_order = ORC_SUM_TREE32;
+  p->sum_order = ORC_SUM_SEG4;
   p->sigma = 1.0f;
   p->seed = 1234; /* gt.cu:23 */
 }
@@ -376,6 +376,20 @@ static float orc_tree32(const float *per_waypoint, uint32_t n) {
   return part[0];
 }
 
+/* SEG4: per-waypoint sums are folded left to right inside segments of 4 consecutive
+ * waypoints, then the segment partials are folded left to right.  This is the fixed order
+ * of the CUDA kernels (one thread walks whole segments; any number of threads per sample
+ * produces the same partials), replacing the reference's unordered atomicAdd (gt.cu:73-77). */
+static float orc_seg4(const float *per_waypoint, uint32_t n) {
+  float total = 0.0f;
+  for (uint32_t w0 = 0; w0 < n; w0 += 4) {
+    float part = 0.0f;
+    for (uint32_t w = w0; w < n && w < w0 + 4; ++w) part = part + per_waypoint[w];
+    total = total + part;
+  }
+  return total;
+}
+
 float orc_cost_sample(const orc_params *p, const orc_grid *g, const float *base,
                       const float *start, const float *noise, int32_t *collisions,
                       float *noisy_out, float *vel_out, float *acc_out, float *smooth_out,
@@ -424,9 +438,12 @@ float orc_cost_sample(const orc_params *p, const orc_grid *g, const float *base,
   if (p->sum_order == ORC_SUM_SEQUENTIAL) { /* gt.test.cu:187-195 */
     sum = seq_sum;
     lsum = seq_lim;
-  } else {
+  } else if (p->sum_order == ORC_SUM_TREE32) {
     sum = orc_tree32(acc2, n);
     lsum = orc_tree32(lim2, n);
+  } else {
+    sum = orc_seg4(acc2, n);
+    lsum = orc_seg4(lim2, n);
   }
   float smooth = p->smooth_scale * sum; /* gt.cu:81,107 */
   float score = (float)coll + smooth;   /* gt.cu:100,108 */

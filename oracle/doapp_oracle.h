@@ -39,7 +39,9 @@ enum { ORC_FRAME_CDG = 0, ORC_FRAME_OG = 1 };
  * SEQUENTIAL = the host loop of gt.test.cu:187-195;
  * TREE32 = lane-strided partials + xor butterfly (the fixed order the CUDA
  * kernels use in place of the reference's unordered float atomicAdd, gt.cu:73-77). */
-enum { ORC_SUM_SEQUENTIAL = 0, ORC_SUM_TREE32 = 1 };
+/* SEG4 (default) = left folds inside segments of 4 waypoints, then a left fold of the segment
+ * partials: the fixed order of the current CUDA kernels (independent of launch geometry). */
+enum { ORC_SUM_SEQUENTIAL = 0, ORC_SUM_TREE32 = 1, ORC_SUM_SEG4 = 2 };
 
 typedef struct orc_grid {
   int32_t kind;  /* ORC_GRID_* */
