@@ -32,11 +32,28 @@ def _nvcc() -> str:
     return nvcc
 
 
-def _stale(target: str, sources: list[str]) -> bool:
-    if not os.path.exists(target):
+def _digest(sources: list[str], flags: list[str]) -> str:
+    import hashlib
+    h = hashlib.sha256(" ".join(flags).encode())
+    for s in sources:
+        h.update(os.path.basename(s).encode())
+        h.update(open(s, "rb").read())
+    return h.hexdigest()
+
+
+def _stale(target: str, sources: list[str], flags: list[str] | None = None) -> bool:
+    """Content-hash staleness (a stamp file beside the target): file mtimes do not survive the
+    copy to the GPU box, and a spurious rebuild there must not happen."""
+    stamp = target + ".stamp"
+    if not os.path.exists(target) or not os.path.exists(stamp):
         return True
-    t = os.path.getmtime(target)
-    return any(os.path.getmtime(s) > t for s in sources)
+    return open(stamp).read().strip() != _digest([s for s in sources if not s.endswith(".so")],
+                                                 flags or [])
+
+
+def _stamp(target: str, sources: list[str], flags: list[str] | None = None) -> None:
+    with open(target + ".stamp", "w") as f:
+        f.write(_digest([s for s in sources if not s.endswith(".so")], flags or []))
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
@@ -44,12 +61,15 @@ def build(force: bool = False, verbose: bool = False) -> str:
     cu = [os.path.join(CSRC, f) for f in ("kernels.cu", "doapp_capi.cu")]
     deps = cu + [os.path.join(CSRC, f) for f in ("kernels.cuh", "device_math.cuh")] + \
         [os.path.join(ROOT, "include", "doapp", "doapp.h")]
-    if force or _stale(LIB, deps):
+    if force or _stale(LIB, deps, NVCC_FLAGS):
         cmd = [_nvcc(), *NVCC_FLAGS, "-shared", "-I", os.path.join(ROOT, "include"), "-I", CSRC,
                *cu, "-o", LIB, "-ldl"]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
-        subprocess.run(cmd, check=True)
+        r = subprocess.run(cmd, capture_output=not verbose, text=True)
+        if r.returncode != 0:
+            raise RuntimeError(f"nvcc failed ({r.returncode}):\n{r.stdout}\n{r.stderr}")
+        _stamp(LIB, deps, NVCC_FLAGS)
     host_dir = os.path.join(PKG, "host")
     host_src = os.path.join(host_dir, "planning_state.cpp")
     if os.path.exists(host_src):
@@ -60,11 +80,13 @@ def build(force: bool = False, verbose: bool = False) -> str:
         if force or _stale(HOST_LIB, hdeps):
             subprocess.run([cxx, *common, "-shared", host_src, "-o", HOST_LIB, "-L", LIB_DIR,
                             "-ldoapp_b200", "-Wl,-rpath,$ORIGIN"], check=True)
+            _stamp(HOST_LIB, hdeps)
         test_src = os.path.join(host_dir, "planning_state_test.cpp")
         if os.path.exists(test_src) and (force or _stale(HOST_TEST, hdeps + [test_src, HOST_LIB])):
             subprocess.run([cxx, *common, test_src, "-o", HOST_TEST, "-L", LIB_DIR,
                             "-ldoapp_planning_state", "-ldoapp_b200", "-Wl,-rpath,$ORIGIN"],
                            check=True)
+            _stamp(HOST_TEST, hdeps + [test_src, HOST_LIB])
     return LIB
 
 

@@ -103,7 +103,7 @@ constexpr float kC1 = 4.166664568298827e-2f, kC2 = -1.388731625493765e-3f,
 
 // Cold path: |x| >= 2^17, inf or nan.
 #if defined(__CUDACC__)
-__host__ __device__ __noinline__
+inline __host__ __device__ __noinline__
 #else
 inline
 #endif

@@ -26,7 +26,6 @@ namespace doapp {
 namespace {
 
 constexpr unsigned kFull = 0xFFFFFFFFu;
-constexpr int kCostThreads = 256;
 
 // ---------------------------------------------------------------- grid lookup
 // Flat cell index of a world point or -1 (outside).  CDG: cpu_distance_grid.cu:113-126
@@ -125,22 +124,6 @@ __device__ __forceinline__ void fk_points(const float (&th)[D], float rpy_s, flo
   p = rot_y(rpy_s, rpy_c, p);
   p = P3{p.x, dm::add_(p.y, -0.005f), dm::add_(p.z, 0.07f)};
   out[4] = p;
-}
-
-template <int D>
-__device__ __forceinline__ int num_collisions(const CostParams &P, const float (&x)[D]) {
-  P3 pts[5];
-  fk_points<D>(x, P.rpy_s, P.rpy_c, pts);
-  int cnt = 0;
-#pragma unroll
-  for (int l = 0; l < 5; ++l) cnt += grid_collides(P.grid, pts[l].x, pts[l].y, pts[l].z, P.coll_dist);
-  return cnt;
-}
-
-__device__ __forceinline__ float butterfly_sum(float v) {
-#pragma unroll
-  for (int off = 16; off >= 1; off >>= 1) v = dm::add_(v, __shfl_xor_sync(kFull, v, off));
-  return v;
 }
 
 __device__ __forceinline__ uint32_t key_hi(int select_mode, float score) {

@@ -35,15 +35,25 @@ class Params(C.Structure):
                 ("seed", C.c_uint64), ("sample_offset", C.c_uint64), ("m_global", C.c_uint64)]
 
 
+def _digest() -> str:
+    import hashlib
+    h = hashlib.sha256()
+    for f in ("doapp_oracle.c", "doapp_oracle.h", "Makefile"):
+        h.update(open(os.path.join(_HERE, f), "rb").read())
+    return h.hexdigest()
+
+
 def build(force: bool = False) -> str:
-    """Compile the oracle with gcc (oracle/Makefile)."""
-    src = os.path.join(_HERE, "doapp_oracle.c")
-    hdr = os.path.join(_HERE, "doapp_oracle.h")
-    stale = (not os.path.exists(_LIB_PATH)
-             or os.path.getmtime(_LIB_PATH) < max(os.path.getmtime(src), os.path.getmtime(hdr)))
-    if force or stale:
-        subprocess.run(["make", "-C", _HERE, "-B" if force else "-s", "all"], check=True,
+    """Compile the oracle with gcc (oracle/Makefile).  Staleness is a content hash: file
+    mtimes do not survive the copy to the GPU box."""
+    stamp = _LIB_PATH + ".stamp"
+    fresh = (os.path.exists(_LIB_PATH) and os.path.exists(stamp)
+             and open(stamp).read().strip() == _digest())
+    if force or not fresh:
+        subprocess.run(["make", "-C", _HERE, "-B", "-s", "all"], check=True,
                        stdout=subprocess.DEVNULL)
+        with open(stamp, "w") as f:
+            f.write(_digest())
     return _LIB_PATH
 
 
