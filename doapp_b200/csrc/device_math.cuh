@@ -249,4 +249,15 @@ DM_HD void noise_vec(uint32_t seed_lo, uint32_t seed_hi, float sigma, uint32_t i
   }
 }
 
+// Box-Muller pair `pair` of one (sample, noise waypoint): pair 0 = joints (0,1), pair 1 =
+// joints (2,3), pair 2 = joint 4 (second Philox call; *b unused).  Same values as noise_at.
+DM_HD void noise_pair(uint32_t seed_lo, uint32_t seed_hi, float sigma, uint32_t iteration,
+                      uint32_t c, uint32_t t_global, uint32_t wn, uint32_t pair, float *a,
+                      float *b) {
+  u4 r = philox4x32_10(t_global, c, wn, 2u * iteration + (pair >> 1), seed_lo, seed_hi);
+  const uint32_t u = (pair & 1u) ? r.z : r.x, v = (pair & 1u) ? r.w : r.y;
+  *a = box_muller(u, v, false, sigma);
+  *b = box_muller(u, v, true, sigma);
+}
+
 } // namespace dm

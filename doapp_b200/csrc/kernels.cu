@@ -17,6 +17,8 @@
 // scores and the argmin are reproducible bit for bit.
 #include "kernels.cuh"
 
+#include <cooperative_groups.h>
+
 #include <cstring>
 
 #include "device_math.cuh"
@@ -144,12 +146,12 @@ __device__ __forceinline__ uint32_t key_hi_float(float score) {
 // the reference materialises noisy trajectories, velocities and accelerations
 // in global memory, generate_trajectories.cu:202-210).
 //
-// Sum order (fixed, independent of the launch geometry; oracle ORC_SUM_SEG4):
-// per-waypoint sums folded left to right inside segments of kSeg waypoints,
-// segment partials folded left to right.  With T > 1 threads per sample each
-// thread owns whole segments and leaves its partials in shared memory; thread 0
-// of the sample folds them.
-constexpr int kSeg = 4;
+// Sum order (fixed, independent of the launch geometry; oracle ORC_SUM_WAYPOINT):
+// the d squares of a waypoint are summed joint 0 first, then the per-waypoint
+// sums are folded left to right, waypoint 0 first.  With T > 1 threads per
+// sample each thread owns a run of consecutive waypoints and leaves its
+// per-waypoint sums in the shared memory of the cluster's rank-0 CTA
+// (distributed shared memory); one thread per sample folds them in order.
 constexpr int kMaxCostThreads = 512;
 
 // Grid modes the kernel is specialised for.
@@ -203,21 +205,30 @@ __device__ __forceinline__ unsigned long long warp_min_u64(unsigned long long v)
 template <int D, int GM, bool NPW, bool FIDX>
 __global__ void __launch_bounds__(kMaxCostThreads)
     cost_kernel(const __grid_constant__ CostParams P) {
+  namespace cg = cooperative_groups;
   constexpr int DP = D == 4 ? 4 : 8; // padded joints per waypoint in shared memory
   extern __shared__ __align__(16) float smem[];
-  float *sbase = smem;                               // [n][DP]
-  float *spart = sbase + (size_t)P.n * DP;           // [nseg][samples/block]   (T > 1)
-  const uint32_t T = 1u << P.parts_log2;
-  const uint32_t spb = (blockDim.x >> 5 >> P.parts_log2) * 32; // samples per block
-  float *slim = spart + (size_t)P.nseg * spb;        // [nseg][samples/block]   (T > 1, limits)
-  int *scoll = (int *)(slim + (P.use_limits ? (size_t)P.nseg * spb : 0)); // [T][samples/block]
+  const uint32_t T = 1u << P.parts_log2;   // threads (parts) per sample
+  const uint32_t PW = 1u << P.pw_log2;     // parts per CTA; cluster size = T / PW
+  const uint32_t cs_log2 = P.parts_log2 - P.pw_log2;
+  const uint32_t spb = (blockDim.x >> 5 >> P.pw_log2) * 32; // samples per block (32 if T > 1)
+  float *sbase = smem;                                 // [n][DP]
+  float *seps = sbase + (size_t)P.n * DP;              // [D][32]      (shared noise, PW >= 4)
+  float *spart = seps + (PW >= 4 ? D * 32 : 0);        // [n][32]      (T > 1; rank-0 CTA's is used)
+  float *slim = spart + (T > 1 ? (size_t)P.n * 32 : 0); // [n][32]     (T > 1 and limits)
+  int *scoll = (int *)(slim + ((T > 1 && P.use_limits) ? (size_t)P.n * 32 : 0)); // [T][32]
+
+  const bool clustered = cs_log2 != 0;
+  cg::cluster_group cluster = cg::this_cluster();
+  const uint32_t crank = clustered ? cluster.block_rank() : 0u;
+  if (clustered) cluster.barrier_arrive(); // every CTA of the cluster is running before DSMEM use
 
   const uint32_t c = blockIdx.y;
   const int lane = threadIdx.x & 31;
   const uint32_t warp = threadIdx.x >> 5;
-  const uint32_t part = warp & (T - 1), sw = warp >> P.parts_log2;
-  const uint32_t si = sw * 32 + lane; // sample slot inside the block
-  uint32_t t = blockIdx.x * spb + si;
+  const uint32_t part = T > 1 ? crank * PW + warp : 0u;
+  const uint32_t si = T > 1 ? (uint32_t)lane : warp * 32 + lane; // sample slot inside the block
+  uint32_t t = (blockIdx.x >> cs_log2) * spb + si;
   const bool active = t < P.m;
   t = active ? t : P.m - 1; // idle lanes shadow the last sample (no divergence, no stores)
   const uint32_t tg = (uint32_t)(P.sample_offset + t);
@@ -240,15 +251,29 @@ __global__ void __launch_bounds__(kMaxCostThreads)
   float eps[D];
 #pragma unroll
   for (int j = 0; j < D; ++j) eps[j] = 0.0f;
+  const bool share_noise = !NPW && PW >= 4 && P.noise_mode == NOISE_PHILOX;
   if (!NPW) {
     if (P.noise_mode == NOISE_EXTERNAL) {
 #pragma unroll
       for (int j = 0; j < D; ++j) eps[j] = __ldg(nz + j);
     } else if (P.noise_mode == NOISE_PHILOX) {
-      dm::noise_vec<D>(P.seed_lo, P.seed_hi, P.sigma, P.iteration, c, tg, 0, eps);
+      if (!share_noise) {
+        dm::noise_vec<D>(P.seed_lo, P.seed_hi, P.sigma, P.iteration, c, tg, 0, eps);
+      } else if (warp < 3) {
+        // the CTA's warps all serve the same 32 samples: warps 0/1/2 draw the Box-Muller
+        // pairs (joints 0,1), (2,3) and joint 4 once and share them through shared memory
+        float a, b;
+        dm::noise_pair(P.seed_lo, P.seed_hi, P.sigma, P.iteration, c, tg, 0, warp, &a, &b);
+        if (2 * warp < D) seps[(2 * warp) * 32 + lane] = a;
+        if (2 * warp + 1 < D && warp < 2) seps[(2 * warp + 1) * 32 + lane] = b;
+      }
     }
   }
   __syncthreads();
+  if (share_noise) {
+#pragma unroll
+    for (int j = 0; j < D; ++j) eps[j] = seps[j * 32 + lane];
+  }
 
   // noisy position of joint j at waypoint w (generate_trajectories.cu:53-57)
   auto noisy = [&](uint32_t w, int j) -> float {
@@ -262,10 +287,9 @@ __global__ void __launch_bounds__(kMaxCostThreads)
     return dm::add_(sbase[w * DP + j], e);
   };
 
-  const uint32_t seg0 = part * P.segs_per_part;
-  uint32_t seg1 = seg0 + P.segs_per_part;
-  seg1 = seg1 < P.nseg ? seg1 : P.nseg;
-  uint32_t w = seg0 * kSeg;
+  uint32_t w = part * P.wpp;
+  uint32_t w_end = w + P.wpp;
+  w_end = w_end < P.n ? w_end : P.n;
 
   // priors of the first owned waypoint: the initial waypoint for BOTH derivative
   // passes at w = 0 (generate_trajectories.cu:285), else recomputed
@@ -273,7 +297,7 @@ __global__ void __launch_bounds__(kMaxCostThreads)
   if (w == 0) {
 #pragma unroll
     for (int j = 0; j < D; ++j) xprev[j] = vprev[j] = start[j];
-  } else if (seg0 < P.nseg) {
+  } else if (w < P.n) {
 #pragma unroll
     for (int j = 0; j < D; ++j) {
       const float x1 = noisy(w - 1, j);
@@ -283,51 +307,56 @@ __global__ void __launch_bounds__(kMaxCostThreads)
     }
   }
 
+  // partial sums of the other CTAs of the cluster land in rank 0's shared memory (DSMEM)
+  float *spart0 = spart, *slim0 = slim;
+  int *scoll0 = scoll;
+  if (clustered) {
+    spart0 = cluster.map_shared_rank(spart, 0);
+    slim0 = cluster.map_shared_rank(slim, 0);
+    scoll0 = cluster.map_shared_rank(scoll, 0);
+    cluster.barrier_wait();
+  }
+
   float total = 0.0f, ltotal = 0.0f;
   int coll = 0;
-  for (uint32_t seg = seg0; seg < seg1; ++seg) {
-    float ps = 0.0f, pl = 0.0f;
+  for (; w < w_end; ++w) {
+    float x[D];
+    float a2 = 0.0f, l2 = 0.0f;
 #pragma unroll
-    for (int u = 0; u < kSeg; ++u, ++w) {
-      if (w < P.n) {
-        float x[D];
-        float a2 = 0.0f, l2 = 0.0f;
-#pragma unroll
-        for (int j = 0; j < D; ++j) {
-          x[j] = noisy(w, j);
-          const float v = dm::div_fast(dm::sub_(x[j], xprev[j]), P.dt_div);  // :288
-          const float a = dm::div_fast(dm::sub_(v, vprev[j]), P.dt_div);
-          a2 = dm::add_(a2, dm::mul_(a, a));                                  // :76
-          xprev[j] = x[j];
-          vprev[j] = v;
-          if (P.use_limits) {
-            const float h =
-                fmaxf(0.0f, fmaxf(dm::sub_(x[j], P.lim_max[j]), dm::sub_(P.lim_min[j], x[j])));
-            l2 = dm::add_(l2, dm::mul_(h, h));
-          }
-        }
-        ps = dm::add_(ps, a2);
-        pl = dm::add_(pl, l2);
-        if (GM != GM_NONE && P.collision_mode != 0) coll += num_collisions_v2<D, GM, FIDX>(P, x);
+    for (int j = 0; j < D; ++j) {
+      x[j] = noisy(w, j);
+      const float v = dm::div_fast(dm::sub_(x[j], xprev[j]), P.dt_div); // :288
+      const float a = dm::div_fast(dm::sub_(v, vprev[j]), P.dt_div);
+      a2 = dm::add_(a2, dm::mul_(a, a));                                 // :76
+      xprev[j] = x[j];
+      vprev[j] = v;
+      if (P.use_limits) {
+        const float h =
+            fmaxf(0.0f, fmaxf(dm::sub_(x[j], P.lim_max[j]), dm::sub_(P.lim_min[j], x[j])));
+        l2 = dm::add_(l2, dm::mul_(h, h));
       }
     }
-    if (T == 1) {
-      total = dm::add_(total, ps);
-      ltotal = dm::add_(ltotal, pl);
+    if (GM != GM_NONE && P.collision_mode != 0) coll += num_collisions_v2<D, GM, FIDX>(P, x);
+    if (T == 1) { // fixed order: left fold over the waypoints (oracle ORC_SUM_WAYPOINT)
+      total = dm::add_(total, a2);
+      ltotal = dm::add_(ltotal, l2);
     } else {
-      spart[seg * spb + si] = ps;
-      if (P.use_limits) slim[seg * spb + si] = pl;
+      spart0[w * 32 + lane] = a2;
+      if (P.use_limits) slim0[w * 32 + lane] = l2;
     }
   }
   if (T > 1) {
-    scoll[part * spb + si] = coll;
-    __syncthreads();
+    scoll0[part * 32 + lane] = coll;
+    if (clustered)
+      cluster.sync();
+    else
+      __syncthreads();
     if (part != 0) return;
     coll = 0;
-    for (uint32_t q = 0; q < T; ++q) coll += scoll[q * spb + si];
-    for (uint32_t seg = 0; seg < P.nseg; ++seg) {
-      total = dm::add_(total, spart[seg * spb + si]);
-      if (P.use_limits) ltotal = dm::add_(ltotal, slim[seg * spb + si]);
+    for (uint32_t q = 0; q < T; ++q) coll += scoll[q * 32 + lane];
+    for (uint32_t ww = 0; ww < P.n; ++ww) {
+      total = dm::add_(total, spart[ww * 32 + lane]);
+      if (P.use_limits) ltotal = dm::add_(ltotal, slim[ww * 32 + lane]);
     }
   }
 
@@ -352,6 +381,7 @@ __global__ void __launch_bounds__(kMaxCostThreads)
     if (lane == 0) atomicMin(P.keys_float + c, key);
   }
 }
+
 
 // -------------------------------------------------------------- update kernel
 // One block per climber: keep-best of generate_trajectories.cu:225-241 (the
@@ -542,36 +572,47 @@ void host_sincos(float x, float *s, float *c) { dm::sincos(x, s, c); }
 
 template <int D, int GM, bool NPW>
 static cudaError_t launch_cost_t(const CostParams &p, dim3 grid, unsigned threads, size_t smem,
-                                 bool fidx, cudaStream_t st) {
+                                 unsigned cluster, bool fidx, cudaStream_t st) {
   auto go = [&](auto kern) -> cudaError_t {
     if (smem > 48 * 1024) {
       cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            (int)smem);
       if (e != cudaSuccess) return e;
     }
-    kern<<<grid, threads, smem, st>>>(p);
-    return cudaGetLastError();
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(threads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = cluster;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = cluster > 1 ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, p);
   };
-  if (fidx && (GM == GM_U8_CDG || GM == GM_F32_CDG)) return go(cost_kernel<D, GM, NPW, true>);
+  if (fidx) return go(cost_kernel<D, GM, NPW, true>);
   return go(cost_kernel<D, GM, NPW, false>);
 }
 
 template <int D>
 static cudaError_t launch_cost_d(const CostParams &p, dim3 grid, unsigned threads, size_t smem,
-                                 cudaStream_t st) {
+                                 unsigned cluster, cudaStream_t st) {
   int gm = GM_NONE;
   if (p.collision_mode != 0 && p.grid.kind != 0 && p.grid.cells)
     gm = p.grid.frame != 0 ? GM_GENERIC : (p.grid.kind == 1 ? GM_U8_CDG : GM_F32_CDG);
   const bool npw = p.n_noise != 1 && p.noise_mode != NOISE_ZERO;
   const bool fidx = p.grid.fast_idx != 0;
-#define DOAPP_GO(GMV)                                                                 \
-  return npw ? launch_cost_t<D, GMV, true>(p, grid, threads, smem, fidx, st)          \
-             : launch_cost_t<D, GMV, false>(p, grid, threads, smem, fidx, st)
+#define DOAPP_GO(GMV, F)                                                                  \
+  return npw ? launch_cost_t<D, GMV, true>(p, grid, threads, smem, cluster, F, st)        \
+             : launch_cost_t<D, GMV, false>(p, grid, threads, smem, cluster, F, st)
   switch (gm) {
-  case GM_U8_CDG: DOAPP_GO(GM_U8_CDG);
-  case GM_F32_CDG: DOAPP_GO(GM_F32_CDG);
-  case GM_GENERIC: DOAPP_GO(GM_GENERIC);
-  default: DOAPP_GO(GM_NONE);
+  case GM_U8_CDG: DOAPP_GO(GM_U8_CDG, fidx);
+  case GM_F32_CDG: DOAPP_GO(GM_F32_CDG, fidx);
+  case GM_GENERIC: DOAPP_GO(GM_GENERIC, false);
+  default: DOAPP_GO(GM_NONE, false);
   }
 #undef DOAPP_GO
 }
@@ -579,28 +620,36 @@ static cudaError_t launch_cost_d(const CostParams &p, dim3 grid, unsigned thread
 cudaError_t launch_cost(const CostParams &p_in, int d, int sm_count, cudaStream_t st) {
   CostParams p = p_in;
   if (p.k == 0 || p.m == 0) return cudaSuccess;
-  p.nseg = (p.n + kSeg - 1) / kSeg;
   p.res_div = dm::FastDiv{p.grid.res, p.grid.res_rcp, 0.0f, 0.0f};
-  // Threads per sample: 1 when the samples alone fill the chip, else split each sample's
-  // segments over up to 16 warps so that small problems (config 2: 1024 samples) still
-  // put ~16 warps on every SM and the dependent chain per thread is a few waypoints.
+  // Threads per sample: 1 when the samples alone fill the chip; otherwise each sample's
+  // waypoints are split over T = 2..32 threads (4 warps per CTA, T/4 CTAs per cluster) so
+  // that a small problem (config 2: 1024 samples x 64 waypoints) still spreads over every
+  // SM and the dependent chain per thread is a couple of waypoints.
+  const int dp = d == 4 ? 4 : 8;
   const uint64_t sample_warps = (uint64_t)p.k * ((p.m + 31) / 32);
-  const uint64_t target_warps = (uint64_t)sm_count * 16;
+  const uint64_t target_warps = (uint64_t)sm_count * 12;
+  auto smem_for = [&](uint32_t T) -> size_t {
+    size_t f = (size_t)p.n * dp;
+    if (T >= 4) f += (size_t)d * 32;
+    if (T > 1) f += (size_t)p.n * 32 * (p.use_limits ? 2 : 1) + (size_t)T * 32;
+    return f * sizeof(float);
+  };
   uint32_t lg = 0;
-  while (lg < 4 && (2u << lg) <= p.nseg && sample_warps * (1u << lg) < target_warps) ++lg;
+  while (lg < 5 && (2u << lg) <= p.n && sample_warps * (1u << lg) < target_warps &&
+         smem_for(2u << lg) <= 200 * 1024)
+    ++lg;
   p.parts_log2 = lg;
   const uint32_t T = 1u << lg;
-  p.segs_per_part = (p.nseg + T - 1) / T;
-  const uint32_t sw = T >= 4 ? 1 : 4 / T; // sample-warps per block (>= 4 warps per block)
-  const unsigned threads = 32 * T * sw;
+  p.pw_log2 = lg < 2 ? lg : 2;
+  const uint32_t PW = 1u << p.pw_log2, cs = T / PW;
+  p.wpp = (p.n + T - 1) / T;
+  const uint32_t sw = T > 1 ? 1 : 4; // sample-warps per CTA
+  const unsigned threads = 32 * PW * sw;
   const uint32_t spb = 32 * sw;
-  const dim3 grid((p.m + spb - 1) / spb, p.k);
-  const int dp = d == 4 ? 4 : 8;
-  size_t smem = (size_t)p.n * dp * sizeof(float);
-  if (T > 1)
-    smem += ((size_t)p.nseg * spb * (p.use_limits ? 2 : 1) + (size_t)T * spb) * sizeof(float);
-  return d == 5 ? launch_cost_d<5>(p, grid, threads, smem, st)
-                : launch_cost_d<4>(p, grid, threads, smem, st);
+  const dim3 grid(((p.m + spb - 1) / spb) * cs, p.k);
+  const size_t smem = smem_for(T);
+  return d == 5 ? launch_cost_d<5>(p, grid, threads, smem, cs, st)
+                : launch_cost_d<4>(p, grid, threads, smem, cs, st);
 }
 
 cudaError_t launch_verify_div(dm::FastDiv d, uint32_t lo_bits, uint32_t hi_bits, int mode,

@@ -54,8 +54,8 @@ struct CostParams {
   unsigned long long *keys_float; // [k] packed (float bits, t) keys for the host-style argmin
   dm::FastDiv dt_div, res_div; // divisor + RN(1/divisor)
   // launch geometry (filled by launch_cost): 2^parts_log2 threads per sample, each owning
-  // segs_per_part segments of 4 waypoints; nseg = ceil(n / 4)
-  uint32_t parts_log2, segs_per_part, nseg;
+  // wpp consecutive waypoints; 2^pw_log2 of them per CTA, the rest across a cluster
+  uint32_t parts_log2, pw_log2, wpp;
 };
 
 struct UpdateParams {

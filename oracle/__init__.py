@@ -18,7 +18,7 @@ COLLISION_AS_SHIPPED, COLLISION_INTENDED = 0, 1
 SELECT_CEIL_INT, SELECT_FLOAT = 0, 1
 GRID_NONE, GRID_U8, GRID_F32 = 0, 1, 2
 FRAME_CDG, FRAME_OG = 0, 1
-SUM_SEQUENTIAL, SUM_TREE32, SUM_SEG4 = 0, 1, 2
+SUM_SEQUENTIAL, SUM_TREE32, SUM_SEG4, SUM_WAYPOINT = 0, 1, 2, 3
 
 
 class Grid(C.Structure):

@@ -24,7 +24,7 @@ void orc_params_init(orc_params *p) {
   p->collision_distance = 0.05f; /* gt.cu:389 */
   p->collision_mode = ORC_COLLISION_INTENDED;
   p->select_mode = ORC_SELECT_CEIL_INT;
-  p->sum_order = ORC_SUM_SEG4;
+  p->sum_order = ORC_SUM_WAYPOINT;
   p->sigma = 1.0f;
   p->seed = 1234; /* gt.cu:23 */
 }
@@ -441,9 +441,16 @@ float orc_cost_sample(const orc_params *p, const orc_grid *g, const float *base,
   } else if (p->sum_order == ORC_SUM_TREE32) {
     sum = orc_tree32(acc2, n);
     lsum = orc_tree32(lim2, n);
-  } else {
+  } else if (p->sum_order == ORC_SUM_SEG4) {
     sum = orc_seg4(acc2, n);
     lsum = orc_seg4(lim2, n);
+  } else { /* ORC_SUM_WAYPOINT: left fold of the per-waypoint sums, waypoint 0 first */
+    sum = 0.0f;
+    lsum = 0.0f;
+    for (uint32_t w = 0; w < n; ++w) {
+      sum = sum + acc2[w];
+      lsum = lsum + lim2[w];
+    }
   }
   float smooth = p->smooth_scale * sum; /* gt.cu:81,107 */
   float score = (float)coll + smooth;   /* gt.cu:100,108 */

@@ -39,9 +39,12 @@ enum { ORC_FRAME_CDG = 0, ORC_FRAME_OG = 1 };
  * SEQUENTIAL = the host loop of gt.test.cu:187-195;
  * TREE32 = lane-strided partials + xor butterfly (the fixed order the CUDA
  * kernels use in place of the reference's unordered float atomicAdd, gt.cu:73-77). */
-/* SEG4 (default) = left folds inside segments of 4 waypoints, then a left fold of the segment
- * partials: the fixed order of the current CUDA kernels (independent of launch geometry). */
-enum { ORC_SUM_SEQUENTIAL = 0, ORC_SUM_TREE32 = 1, ORC_SUM_SEG4 = 2 };
+/* SEG4 = left folds inside segments of 4 waypoints, then a left fold of the segment partials.
+ * WAYPOINT (default) = per-waypoint sums over the joints (joint 0 first), then one left fold
+ * over the waypoints (waypoint 0 first): the fixed order of the CUDA kernels, independent of
+ * how many threads share a sample.  It differs from SEQUENTIAL only in that the d squares of
+ * a waypoint are summed before they join the running total. */
+enum { ORC_SUM_SEQUENTIAL = 0, ORC_SUM_TREE32 = 1, ORC_SUM_SEG4 = 2, ORC_SUM_WAYPOINT = 3 };
 
 typedef struct orc_grid {
   int32_t kind;  /* ORC_GRID_* */
