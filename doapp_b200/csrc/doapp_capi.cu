@@ -87,6 +87,8 @@ struct doapp_ctx {
   DevBuf<int32_t> coll, final_coll;
   DevBuf<unsigned long long> keys, keys_float;
   DevBuf<uint32_t> cur_hi;
+  DevBuf<unsigned int> done;
+  bool fuse_update = true; // DOAPP_NO_FUSE=1: separate update_kernel launches
   DevBuf<uint8_t> found, grid_cells, lookup_coll;
   DevBuf<long long> lookup_idx;
   DevBuf<float> dbg_a, dbg_b, dbg_c;
@@ -240,6 +242,14 @@ CostParams base_cost_params(doapp_ctx *ctx) {
   return p;
 }
 
+void set_fuse(doapp_ctx *ctx, CostParams &p, int mode) {
+  p.fuse_mode = mode;
+  p.traj_rw = ctx->traj.p;
+  p.cur_hi = ctx->cur_hi.p;
+  p.found_better = ctx->found.p;
+  p.done = ctx->done.p;
+}
+
 // cost pass over the k kept trajectories themselves (zero noise, one "sample"
 // per climber): generate_trajectories.cu:180-191.
 CostParams climber_cost_params(doapp_ctx *ctx) {
@@ -279,22 +289,28 @@ doapp_status enqueue_plan(doapp_ctx *ctx, uint32_t iters, int noise_mode, uint64
   uint64_t nk = 0;
   NcclApi *nccl = ctx->comm ? nccl_api(nullptr) : nullptr;
   CU(cudaMemsetAsync(ctx->keys.p, 0xFF, sizeof(unsigned long long) * c.num_climbers, ctx->stream));
+  CU(cudaMemsetAsync(ctx->done.p, 0, sizeof(unsigned int) * c.num_climbers, ctx->stream));
   // score the unperturbed trajectories -> cur_hi
   {
     CostParams p = climber_cost_params(ctx);
     p.keys = ctx->keys.p;
+    const bool fuse = ctx->fuse_update;
+    if (fuse) set_fuse(ctx, p, 2);
     CU(launch_cost(p, c.waypoint_dim, ctx->sm_count, ctx->stream));
-    UpdateParams u{};
-    u.k = c.num_climbers;
-    u.n = c.num_waypoints;
-    u.npad = ctx->npad;
-    u.d = c.waypoint_dim;
-    u.keys = ctx->keys.p;
-    u.cur_hi = ctx->cur_hi.p;
-    u.found_better = ctx->found.p;
-    u.init = 1;
-    CU(launch_update(u, ctx->stream));
-    nk += 2;
+    nk += 1;
+    if (!fuse) {
+      UpdateParams u{};
+      u.k = c.num_climbers;
+      u.n = c.num_waypoints;
+      u.npad = ctx->npad;
+      u.d = c.waypoint_dim;
+      u.keys = ctx->keys.p;
+      u.cur_hi = ctx->cur_hi.p;
+      u.found_better = ctx->found.p;
+      u.init = 1;
+      CU(launch_update(u, ctx->stream));
+      nk += 1;
+    }
   }
   const size_t noise_iter_stride =
       (size_t)c.num_climbers * ctx->m_global * c.noise_waypoints * c.waypoint_dim;
@@ -308,9 +324,15 @@ doapp_status enqueue_plan(doapp_ctx *ctx, uint32_t iters, int noise_mode, uint64
       p.noise_t0 = 0;
     }
     p.keys = ctx->keys.p;
+    // single GPU: the cost kernel's last warp applies the keep-best itself; with ranks to
+    // merge, the all-reduce sits between the cost kernel and a separate update kernel
+    const bool fuse = ctx->fuse_update && !nccl;
+    if (fuse) set_fuse(ctx, p, 1);
     if (ctx->profiling) CU(cudaEventRecord(ctx->prof_events[2 * it], ctx->stream));
     CU(launch_cost(p, c.waypoint_dim, ctx->sm_count, ctx->stream));
     if (ctx->profiling) CU(cudaEventRecord(ctx->prof_events[2 * it + 1], ctx->stream));
+    nk += 1;
+    if (fuse) continue;
     if (nccl) {
       ncclResult_t r = nccl->AllReduce(ctx->keys.p, ctx->keys.p, c.num_climbers, ncclUint64,
                                        ncclMin, ctx->comm, ctx->stream);
@@ -338,7 +360,7 @@ doapp_status enqueue_plan(doapp_ctx *ctx, uint32_t iters, int noise_mode, uint64
     u.found_better = ctx->found.p;
     u.init = 0;
     CU(launch_update(u, ctx->stream));
-    nk += 2;
+    nk += 1;
   }
   // final float score of every kept trajectory, then the host-style argmin
   {
@@ -504,6 +526,8 @@ doapp_status doapp_create(const doapp_config *cfg, doapp_ctx **out) {
   ctx->S = (uint64_t)cfg->num_climbers * cfg->samples_per_climber;
   const char *ng = getenv("DOAPP_NO_GRAPH");
   ctx->use_graph = !(ng && ng[0] == '1');
+  const char *nf = getenv("DOAPP_NO_FUSE");
+  ctx->fuse_update = !(nf && nf[0] == '1');
   const char *xd = getenv("DOAPP_EXACT_DIV");
   ctx->fast_math_ok = !(xd && xd[0] == '1');
   host_sincos(-1.5707963267948966f, &ctx->rpy_s, &ctx->rpy_c);
@@ -525,6 +549,8 @@ doapp_status doapp_create(const doapp_config *cfg, doapp_ctx **out) {
     ST(ensure(ctx, ctx->keys, k));
     ST(ensure(ctx, ctx->keys_float, k));
     ST(ensure(ctx, ctx->cur_hi, k));
+    ST(ensure(ctx, ctx->done, k));
+    CU(cudaMemsetAsync(ctx->done.p, 0, sizeof(unsigned int) * k, ctx->stream));
     ST(ensure(ctx, ctx->found, k));
     ST(ensure(ctx, ctx->out, 4 + 2 * n * d));
     CU(cudaMemsetAsync(ctx->traj.p, 0, sizeof(float) * k * d * ctx->npad, ctx->stream));
@@ -562,7 +588,7 @@ void doapp_destroy(doapp_ctx *ctx) {
   release(ctx->traj); release(ctx->aos_tmp); release(ctx->start); release(ctx->noise);
   release(ctx->scores); release(ctx->final_scores); release(ctx->out); release(ctx->cloud);
   release(ctx->pts); release(ctx->coll); release(ctx->final_coll); release(ctx->keys);
-  release(ctx->keys_float); release(ctx->cur_hi); release(ctx->found); release(ctx->grid_cells);
+  release(ctx->keys_float); release(ctx->cur_hi); release(ctx->done); release(ctx->found); release(ctx->grid_cells);
   release(ctx->lookup_coll); release(ctx->lookup_idx); release(ctx->dbg_a); release(ctx->dbg_b);
   release(ctx->dbg_c); release(ctx->vbad);
   for (cudaEvent_t e : ctx->prof_events) cudaEventDestroy(e);
@@ -1022,6 +1048,7 @@ doapp_status doapp_replan_dynamic(doapp_ctx *ctx, const float *start, const floa
   CU(cudaStreamSynchronize(ctx->stream));
   CU(cudaEventRecord(ctx->ev0, ctx->stream));
   CU(cudaMemsetAsync(ctx->keys.p, 0xFF, sizeof(unsigned long long) * c.num_climbers, ctx->stream));
+  CU(cudaMemsetAsync(ctx->done.p, 0, sizeof(unsigned int) * c.num_climbers, ctx->stream));
   // the initial score is taken against the first cloud's grid
   auto rebuild = [&](uint32_t it) -> doapp_status {
     CU(cudaMemsetAsync(ctx->grid_cells.p, 0, ctx->grid_bytes, ctx->stream));
@@ -1052,22 +1079,29 @@ doapp_status doapp_replan_dynamic(doapp_ctx *ctx, const float *start, const floa
   for (uint32_t it = 0; it < iters; ++it) {
     ST(rebuild(it));
     // the world moved: re-score the kept trajectories against the new grid
+    const bool fuse = ctx->fuse_update && !ctx->comm;
     CostParams p0 = climber_cost_params(ctx);
     p0.keys = ctx->keys.p;
+    if (fuse) set_fuse(ctx, p0, 2);
     CU(launch_cost(p0, c.waypoint_dim, ctx->sm_count, ctx->stream));
-    UpdateParams ui = u;
-    ui.init = 1;
-    CU(launch_update(ui, ctx->stream));
+    if (!fuse) {
+      UpdateParams ui = u;
+      ui.init = 1;
+      CU(launch_update(ui, ctx->stream));
+    }
     CostParams p = base_cost_params(ctx);
     p.noise_mode = NOISE_PHILOX;
     p.iteration = it;
     p.keys = ctx->keys.p;
+    if (fuse) set_fuse(ctx, p, 1);
     CU(launch_cost(p, c.waypoint_dim, ctx->sm_count, ctx->stream));
-    UpdateParams uu = u;
-    uu.iteration = it;
-    uu.init = 0;
-    CU(launch_update(uu, ctx->stream));
-    ctx->launches += 4;
+    if (!fuse) {
+      UpdateParams uu = u;
+      uu.iteration = it;
+      uu.init = 0;
+      CU(launch_update(uu, ctx->stream));
+    }
+    ctx->launches += fuse ? 2 : 4;
   }
   {
     CostParams p = climber_cost_params(ctx);

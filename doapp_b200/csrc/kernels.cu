@@ -202,6 +202,61 @@ __device__ __forceinline__ unsigned long long warp_min_u64(unsigned long long v)
   return v;
 }
 
+// Keep-best of generate_trajectories.cu:225-241 (D5/D6 fixed) executed by the LAST warp that
+// reports for climber c (all of the climber's keys are merged by then): same rule as
+// update_kernel, fused into the cost kernel so that an iteration is one launch.
+template <int D>
+__device__ __noinline__ void fused_update(const CostParams &P, uint32_t c, int lane) {
+  __threadfence();
+  const unsigned long long key = __ldcg(P.keys + c);
+  const uint32_t hi = (uint32_t)(key >> 32), tg = (uint32_t)key;
+  const uint32_t cur = __ldcg(P.cur_hi + c);
+  if (P.fuse_mode == 2) { // seed the current score from the unperturbed trajectory (:180-191)
+    if (lane == 0) {
+      P.cur_hi[c] = hi;
+      P.found_better[c] = 0;
+    }
+  } else if (hi < cur) {
+    float *traj = P.traj_rw + (size_t)c * D * P.npad;
+    const float *nz = nullptr;
+    if (P.noise_mode == NOISE_EXTERNAL)
+      nz = P.noise + ((size_t)c * P.noise_m + (size_t)(tg - P.noise_t0)) * P.n_noise * D;
+    float eps[D];
+#pragma unroll
+    for (int j = 0; j < D; ++j) eps[j] = 0.0f;
+    if (P.n_noise == 1) {
+      if (P.noise_mode == NOISE_EXTERNAL) {
+#pragma unroll
+        for (int j = 0; j < D; ++j) eps[j] = nz[j];
+      } else if (P.noise_mode == NOISE_PHILOX) {
+        dm::noise_vec<D>(P.seed_lo, P.seed_hi, P.sigma, P.iteration, c, tg, 0, eps);
+      }
+    }
+    for (uint32_t w = lane; w < P.n; w += 32) {
+#pragma unroll
+      for (int j = 0; j < D; ++j) {
+        float e = eps[j];
+        if (P.n_noise != 1) {
+          if (P.noise_mode == NOISE_EXTERNAL)
+            e = nz[(size_t)w * D + j];
+          else if (P.noise_mode == NOISE_PHILOX)
+            e = dm::noise_at(P.seed_lo, P.seed_hi, P.sigma, P.iteration, c, tg, w, j);
+        }
+        float *q = traj + (size_t)j * P.npad + w;
+        *q = dm::add_(*q, e);
+      }
+    }
+    if (lane == 0) {
+      P.cur_hi[c] = hi;
+      P.found_better[c] = 1;
+    }
+  }
+  if (lane == 0) { // re-arm for the next launch
+    P.keys[c] = kKeyNone;
+    P.done[c] = 0u;
+  }
+}
+
 template <int D, int GM, bool NPW, bool FIDX>
 __global__ void __launch_bounds__(kMaxCostThreads)
     cost_kernel(const __grid_constant__ CostParams P) {
@@ -238,7 +293,7 @@ __global__ void __launch_bounds__(kMaxCostThreads)
     const float *traj = P.traj + (size_t)c * D * P.npad;
     for (uint32_t i = threadIdx.x; i < P.n * D; i += blockDim.x) {
       const uint32_t j = i / P.n, w = i - j * P.n;
-      sbase[w * DP + j] = __ldg(traj + (size_t)j * P.npad + w);
+      sbase[w * DP + j] = __ldcg(traj + (size_t)j * P.npad + w); // rewritten by fused_update
     }
   }
   float start[D];
@@ -368,17 +423,28 @@ __global__ void __launch_bounds__(kMaxCostThreads)
     if (P.scores) P.scores[s] = score;
     if (P.collisions) P.collisions[s] = coll;
   }
-  if (P.keys) {
-    unsigned long long key =
-        active ? ((unsigned long long)key_hi(P.select_mode, score) << 32) | tg : kKeyNone;
-    key = warp_min_u64(key);
-    if (lane == 0) atomicMin(P.keys + c, key);
-  }
   if (P.keys_float) {
     unsigned long long key =
         active ? ((unsigned long long)key_hi_float(score) << 32) | tg : kKeyNone;
     key = warp_min_u64(key);
     if (lane == 0) atomicMin(P.keys_float + c, key);
+  }
+  if (P.keys) {
+    unsigned long long key =
+        active ? ((unsigned long long)key_hi(P.select_mode, score) << 32) | tg : kKeyNone;
+    key = warp_min_u64(key);
+    unsigned int prior = 0;
+    if (lane == 0) {
+      atomicMin(P.keys + c, key);
+      if (P.fuse_mode) {
+        __threadfence();
+        prior = atomicAdd(P.done + c, 1u);
+      }
+    }
+    if (P.fuse_mode) {
+      prior = __shfl_sync(kFull, prior, 0);
+      if (prior == P.units_per_climber - 1) fused_update<D>(P, c, lane);
+    }
   }
 }
 
@@ -648,6 +714,7 @@ cudaError_t launch_cost(const CostParams &p_in, int d, int sm_count, cudaStream_
   const uint32_t spb = 32 * sw;
   const dim3 grid(((p.m + spb - 1) / spb) * cs, p.k);
   const size_t smem = smem_for(T);
+  p.units_per_climber = T > 1 ? grid.x / cs : grid.x * sw; // warps that fold + report
   return d == 5 ? launch_cost_d<5>(p, grid, threads, smem, cs, st)
                 : launch_cost_d<4>(p, grid, threads, smem, cs, st);
 }

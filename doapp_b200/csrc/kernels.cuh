@@ -53,6 +53,14 @@ struct CostParams {
   unsigned long long *keys;      // [k] packed argmin keys for the update rule, or nullptr
   unsigned long long *keys_float; // [k] packed (float bits, t) keys for the host-style argmin
   dm::FastDiv dt_div, res_div; // divisor + RN(1/divisor)
+  // fused keep-best (single-GPU path): the last warp to finish a climber applies
+  // update_kernel's rule itself.  fuse_mode 0 = off, 1 = keep-best, 2 = seed cur_hi
+  int fuse_mode;
+  float *traj_rw;          // same buffer as traj, writable
+  uint32_t *cur_hi;        // [k]
+  uint8_t *found_better;   // [k]
+  unsigned int *done;      // [k] finished-warp counters, self-resetting
+  uint32_t units_per_climber; // warps that report per climber (filled by launch_cost)
   // launch geometry (filled by launch_cost): 2^parts_log2 threads per sample, each owning
   // wpp consecutive waypoints; 2^pw_log2 of them per CTA, the rest across a cluster
   uint32_t parts_log2, pw_log2, wpp;
