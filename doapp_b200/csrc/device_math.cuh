@@ -117,23 +117,27 @@ inline
   *q_out = (int)kd & 3;
 }
 
-DM_HD void sincos(float x, float *s, float *c) {
-  float r;
-  int q;
-  if (fabsf(x) < 131072.0f) {
-    float t = mul_(x, kTwoOverPi);
-    float kf = rintf(t);
-    r = fma_(-kf, kP1, x);
-    r = fma_(-kf, kP2, r);
-    r = fma_(-kf, kP3, r);
-    q = (int)kf & 3;
-  } else if (x != x || fabsf(x) == INFINITY) {
-    *s = NAN;
-    *c = NAN;
-    return;
-  } else {
-    sincos_slow(x, &r, &q);
-  }
+DM_HD uint32_t f2u_(float f) {
+#if defined(__CUDA_ARCH__)
+  return __float_as_uint(f);
+#else
+  uint32_t u;
+  memcpy(&u, &f, 4);
+  return u;
+#endif
+}
+DM_HD float u2f_(uint32_t u) {
+#if defined(__CUDA_ARCH__)
+  return __uint_as_float(u);
+#else
+  float f;
+  memcpy(&f, &u, 4);
+  return f;
+#endif
+}
+
+// polynomial core + quadrant fix-up shared by both argument ranges; q = k mod 4
+DM_HD void sincos_core(float r, uint32_t q, float *s, float *c) {
   float z = mul_(r, r);
   float ps = fma_(kS3, z, kS2);
   ps = fma_(ps, z, kS1);
@@ -143,10 +147,40 @@ DM_HD void sincos(float x, float *s, float *c) {
   pc = fma_(pc, z, kC1);
   pc = fma_(pc, z, -0.5f);
   float cos_r = fma_(pc, z, 1.0f);
-  float sa = (q & 1) ? cos_r : sin_r;
-  float ca = (q & 1) ? sin_r : cos_r;
-  *s = (q & 2) ? -sa : sa;
-  *c = ((q + 1) & 2) ? -ca : ca;
+  // (s,c) = (sin,cos), (cos,-sin), (-sin,-cos), (-cos,sin) for q = 0..3, as sign-bit flips
+  const bool swap = (q & 1u) != 0;
+  const float sa = swap ? cos_r : sin_r, ca = swap ? sin_r : cos_r;
+  const uint32_t qs = q << 30; // bit 31 = bit 1 of q
+  *s = u2f_(f2u_(sa) ^ (qs & 0x80000000u));
+  *c = u2f_(f2u_(ca) ^ ((qs + 0x40000000u) & 0x80000000u)); // bit 1 of q + 1
+}
+
+// |x| < 2^17 only (the caller checks): straight-line code, no conversions.  kf = rintf(t) is
+// taken with the 1.5*2^23 trick (t + M rounds to an integer, ties to even, exactly as rintf
+// does for |t| < 2^22) and k mod 4 is read from the low mantissa bits of t + M.
+DM_HD void sincos_small(float x, float *s, float *c) {
+  const float kMagic = 12582912.0f; // 1.5 * 2^23
+  float t = mul_(x, kTwoOverPi);
+  float tm = add_(t, kMagic);
+  float kf = sub_(tm, kMagic);
+  float r = fma_(-kf, kP1, x);
+  r = fma_(-kf, kP2, r);
+  r = fma_(-kf, kP3, r);
+  sincos_core(r, f2u_(tm) & 3u, s, c);
+}
+
+DM_HD void sincos(float x, float *s, float *c) {
+  if (fabsf(x) < 131072.0f) {
+    sincos_small(x, s, c);
+  } else if (x != x || fabsf(x) == INFINITY) {
+    *s = NAN;
+    *c = NAN;
+  } else {
+    float r;
+    int q;
+    sincos_slow(x, &r, &q);
+    sincos_core(r, (uint32_t)q & 3u, s, c);
+  }
 }
 
 // natural log on (0, 1]

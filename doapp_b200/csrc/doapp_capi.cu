@@ -87,8 +87,11 @@ struct doapp_ctx {
   DevBuf<int32_t> coll, final_coll;
   DevBuf<unsigned long long> keys, keys_float;
   DevBuf<uint32_t> cur_hi;
-  DevBuf<unsigned int> done;
-  bool fuse_update = true; // DOAPP_NO_FUSE=1: separate update_kernel launches
+  // Ping-pong state of the planner: traj holds two [k][d][npad] halves, cur_hi two [k]
+  // halves, keys three [k] buffers (read / write / being re-armed).  Every launch that
+  // applies a pending keep-best reads half traj_s and writes the other (kernels.cuh).
+  int traj_s = 0, cur_s = 0, key_w = -1;
+  size_t traj_half = 0; // elements per trajectory half
   DevBuf<uint8_t> found, grid_cells, lookup_coll;
   DevBuf<long long> lookup_idx;
   DevBuf<float> dbg_a, dbg_b, dbg_c;
@@ -116,6 +119,7 @@ struct doapp_ctx {
   const float *graph_noise_ptr = nullptr;
   uint64_t graph_grid_generation = ~0ull;
   uint64_t graph_kernels = 0;
+  int graph_end_traj_s = 0, graph_end_cur_s = 0, graph_end_key_w = -1;
   bool use_graph = true;
 
   ncclComm_t comm = nullptr;
@@ -212,7 +216,7 @@ doapp_status verify_fast_div(doapp_ctx *ctx, float b, uint32_t lo_bits, uint32_t
 CostParams base_cost_params(doapp_ctx *ctx) {
   const doapp_config &c = ctx->cfg;
   CostParams p{};
-  p.traj = ctx->traj.p;
+  p.traj = ctx->traj.p + (size_t)ctx->traj_s * ctx->traj_half;
   p.start = ctx->start.p;
   p.k = c.num_climbers;
   p.m = c.samples_per_climber;
@@ -242,12 +246,49 @@ CostParams base_cost_params(doapp_ctx *ctx) {
   return p;
 }
 
-void set_fuse(doapp_ctx *ctx, CostParams &p, int mode) {
-  p.fuse_mode = mode;
-  p.traj_rw = ctx->traj.p;
-  p.cur_hi = ctx->cur_hi.p;
-  p.found_better = ctx->found.p;
-  p.done = ctx->done.p;
+float *traj_half_ptr(doapp_ctx *ctx, int half) {
+  return ctx->traj.p + (size_t)half * ctx->traj_half;
+}
+
+void reset_plan_state(doapp_ctx *ctx) {
+  ctx->traj_s = 0;
+  ctx->cur_s = 0;
+  ctx->key_w = -1;
+}
+
+// One cost launch of the planner sequence.  pend_mode != PEND_NONE: the launch first applies
+// the keep-best decided by the key buffer the previous launch wrote (noise of `pend_iteration`
+// / `pend_noise`), flipping the trajectory and cur_hi halves.  write_keys: the launch leaves
+// its own per-climber winner in the next key buffer and re-arms the one after it.
+doapp_status launch_pass(doapp_ctx *ctx, CostParams p, int pend_mode, uint32_t pend_iteration,
+                         int pend_noise_mode, const float *pend_noise, bool write_keys) {
+  const size_t k = ctx->cfg.num_climbers;
+  p.traj = traj_half_ptr(ctx, ctx->traj_s);
+  p.pend_mode = pend_mode;
+  if (pend_mode != PEND_NONE) {
+    if (ctx->key_w < 0) return fail(ctx, DOAPP_NOT_READY, "launch_pass: no pending keys");
+    p.pend_keys = ctx->keys.p + (size_t)ctx->key_w * k;
+    p.pend_iteration = pend_iteration;
+    p.pend_noise_mode = pend_noise_mode;
+    p.pend_noise = pend_noise;
+    p.cur_hi_in = ctx->cur_hi.p + (size_t)ctx->cur_s * k;
+    p.cur_hi_out = ctx->cur_hi.p + (size_t)(1 - ctx->cur_s) * k;
+    p.found_better = ctx->found.p;
+    p.traj_next = traj_half_ptr(ctx, 1 - ctx->traj_s);
+  }
+  int kw = -1;
+  if (write_keys) {
+    kw = (ctx->key_w + 1) % 3;
+    p.keys = ctx->keys.p + (size_t)kw * k;
+    p.keys_reset = ctx->keys.p + (size_t)((kw + 1) % 3) * k;
+  }
+  CU(launch_cost(p, ctx->cfg.waypoint_dim, ctx->sm_count, ctx->stream));
+  if (pend_mode != PEND_NONE) {
+    ctx->traj_s ^= 1;
+    ctx->cur_s ^= 1;
+  }
+  if (write_keys) ctx->key_w = kw;
+  return DOAPP_OK;
 }
 
 // cost pass over the k kept trajectories themselves (zero noise, one "sample"
@@ -257,7 +298,7 @@ CostParams climber_cost_params(doapp_ctx *ctx) {
   p.m = 1;
   p.noise_mode = NOISE_ZERO;
   p.noise = nullptr;
-  p.n_noise = 1;
+  p.n_noise = ctx->cfg.noise_waypoints; // layout of a PENDING winner's noise; own noise is zero
   p.sample_offset = 0;
   p.m_global = 1;
   return p;
@@ -270,6 +311,7 @@ doapp_status upload_traj(doapp_ctx *ctx, const float *host_aos, bool broadcast_f
   ST(ensure(ctx, ctx->aos_tmp, (size_t)c.num_climbers * c.num_waypoints * c.waypoint_dim));
   CU(cudaMemcpyAsync(ctx->aos_tmp.p, host_aos, elems * sizeof(float), cudaMemcpyHostToDevice,
                      ctx->stream));
+  reset_plan_state(ctx); // the uploaded trajectories live in half 0
   CU(launch_aos_to_soa(ctx->aos_tmp.p, ctx->traj.p, c.num_climbers, c.num_waypoints, ctx->npad,
                        c.waypoint_dim, broadcast_first ? 1 : 0, ctx->stream));
   ctx->launches += 1;
@@ -282,94 +324,58 @@ doapp_status upload_start(doapp_ctx *ctx, const float *start) {
   return DOAPP_OK;
 }
 
-// Enqueue the planner loop (no host synchronisation inside): initial scoring,
-// `iters` x (cost -> [all-reduce] -> update), final scoring and selection.
+// Enqueue the planner loop (no host synchronisation inside).  One launch per stage:
+//   seed pass   scores the k unperturbed trajectories                      (gt.cu:180-191)
+//   iteration i costs the samples; while staging it first applies the keep-best of
+//               iteration i-1 (or seeds cur_hi from the seed pass)          (gt.cu:197-241)
+//   [ranks > 1: one MIN all-reduce of the k keys after every iteration      ]
+//   final pass  applies the last keep-best and scores the kept trajectories in float
+//   selection   host-style argmin + velocities                              (ps.cu:113-166)
 doapp_status enqueue_plan(doapp_ctx *ctx, uint32_t iters, int noise_mode, uint64_t *kernels) {
   const doapp_config &c = ctx->cfg;
+  const size_t k = c.num_climbers;
   uint64_t nk = 0;
   NcclApi *nccl = ctx->comm ? nccl_api(nullptr) : nullptr;
-  CU(cudaMemsetAsync(ctx->keys.p, 0xFF, sizeof(unsigned long long) * c.num_climbers, ctx->stream));
-  CU(cudaMemsetAsync(ctx->done.p, 0, sizeof(unsigned int) * c.num_climbers, ctx->stream));
-  // score the unperturbed trajectories -> cur_hi
-  {
-    CostParams p = climber_cost_params(ctx);
-    p.keys = ctx->keys.p;
-    const bool fuse = ctx->fuse_update;
-    if (fuse) set_fuse(ctx, p, 2);
-    CU(launch_cost(p, c.waypoint_dim, ctx->sm_count, ctx->stream));
-    nk += 1;
-    if (!fuse) {
-      UpdateParams u{};
-      u.k = c.num_climbers;
-      u.n = c.num_waypoints;
-      u.npad = ctx->npad;
-      u.d = c.waypoint_dim;
-      u.keys = ctx->keys.p;
-      u.cur_hi = ctx->cur_hi.p;
-      u.found_better = ctx->found.p;
-      u.init = 1;
-      CU(launch_update(u, ctx->stream));
-      nk += 1;
-    }
-  }
+  reset_plan_state(ctx);
+  CU(cudaMemsetAsync(ctx->keys.p, 0xFF, sizeof(unsigned long long) * 3 * k, ctx->stream));
+  ST(launch_pass(ctx, climber_cost_params(ctx), PEND_NONE, 0, NOISE_ZERO, nullptr, true));
+  nk += 1;
   const size_t noise_iter_stride =
       (size_t)c.num_climbers * ctx->m_global * c.noise_waypoints * c.waypoint_dim;
+  auto noise_of = [&](uint32_t it) -> const float * {
+    return noise_mode == NOISE_EXTERNAL ? ctx->noise.p + (size_t)it * noise_iter_stride : nullptr;
+  };
   for (uint32_t it = 0; it < iters; ++it) {
     CostParams p = base_cost_params(ctx);
     p.noise_mode = noise_mode;
     p.iteration = it;
-    if (noise_mode == NOISE_EXTERNAL) {
-      p.noise = ctx->noise.p + (size_t)it * noise_iter_stride;
-      p.noise_m = ctx->m_global;
-      p.noise_t0 = 0;
-    }
-    p.keys = ctx->keys.p;
-    // single GPU: the cost kernel's last warp applies the keep-best itself; with ranks to
-    // merge, the all-reduce sits between the cost kernel and a separate update kernel
-    const bool fuse = ctx->fuse_update && !nccl;
-    if (fuse) set_fuse(ctx, p, 1);
+    p.noise = noise_of(it);
+    p.noise_m = ctx->m_global;
+    p.noise_t0 = 0;
     if (ctx->profiling) CU(cudaEventRecord(ctx->prof_events[2 * it], ctx->stream));
-    CU(launch_cost(p, c.waypoint_dim, ctx->sm_count, ctx->stream));
+    ST(launch_pass(ctx, p, it == 0 ? PEND_SEED : PEND_KEEP_BEST, it ? it - 1 : 0, noise_mode,
+                   it ? noise_of(it - 1) : nullptr, true));
     if (ctx->profiling) CU(cudaEventRecord(ctx->prof_events[2 * it + 1], ctx->stream));
     nk += 1;
-    if (fuse) continue;
     if (nccl) {
-      ncclResult_t r = nccl->AllReduce(ctx->keys.p, ctx->keys.p, c.num_climbers, ncclUint64,
-                                       ncclMin, ctx->comm, ctx->stream);
+      unsigned long long *kb = ctx->keys.p + (size_t)ctx->key_w * k;
+      ncclResult_t r = nccl->AllReduce(kb, kb, k, ncclUint64, ncclMin, ctx->comm, ctx->stream);
       if (r != ncclSuccess)
         return fail(ctx, DOAPP_NCCL_ERROR, "ncclAllReduce: %s",
                     nccl->GetErrorString ? nccl->GetErrorString(r) : "error");
     }
-    UpdateParams u{};
-    u.traj = ctx->traj.p;
-    u.noise = p.noise;
-    u.noise_m = p.noise_m;
-    u.noise_t0 = p.noise_t0;
-    u.noise_mode = noise_mode;
-    u.k = c.num_climbers;
-    u.n = c.num_waypoints;
-    u.npad = ctx->npad;
-    u.d = c.waypoint_dim;
-    u.n_noise = c.noise_waypoints;
-    u.iteration = it;
-    u.seed_lo = (uint32_t)c.seed;
-    u.seed_hi = (uint32_t)(c.seed >> 32);
-    u.sigma = c.sigma;
-    u.keys = ctx->keys.p;
-    u.cur_hi = ctx->cur_hi.p;
-    u.found_better = ctx->found.p;
-    u.init = 0;
-    CU(launch_update(u, ctx->stream));
-    nk += 1;
   }
-  // final float score of every kept trajectory, then the host-style argmin
   {
     CostParams p = climber_cost_params(ctx);
     p.scores = ctx->final_scores.p;
     p.collisions = ctx->final_coll.p;
-    CU(launch_cost(p, c.waypoint_dim, ctx->sm_count, ctx->stream));
+    // the winner's noise of the last iteration is still needed to apply its keep-best
+    p.noise_m = ctx->m_global;
+    p.noise_t0 = 0;
+    ST(launch_pass(ctx, p, iters == 0 ? PEND_SEED : PEND_KEEP_BEST, iters ? iters - 1 : 0,
+                   noise_mode, iters ? noise_of(iters - 1) : nullptr, false));
     FinalParams f{};
-    f.traj = ctx->traj.p;
+    f.traj = traj_half_ptr(ctx, ctx->traj_s);
     f.start = ctx->start.p;
     f.scores = ctx->final_scores.p;
     f.found_better = ctx->found.p;
@@ -389,6 +395,7 @@ doapp_status enqueue_plan(doapp_ctx *ctx, uint32_t iters, int noise_mode, uint64
 // restore every climber to the staged initial trajectory (device copy kept in aos_tmp)
 doapp_status reset_climbers(doapp_ctx *ctx) {
   const doapp_config &c = ctx->cfg;
+  reset_plan_state(ctx);
   CU(launch_aos_to_soa(ctx->aos_tmp.p, ctx->traj.p, c.num_climbers, c.num_waypoints, ctx->npad,
                        c.waypoint_dim, 1, ctx->stream));
   ctx->launches += 1;
@@ -427,8 +434,14 @@ doapp_status run_plan(doapp_ctx *ctx, uint32_t iters, int noise_mode) {
     ctx->graph_noise_ptr = nptr;
     ctx->graph_grid_generation = ctx->grid_generation;
     ctx->graph_kernels = nk;
+    ctx->graph_end_traj_s = ctx->traj_s;
+    ctx->graph_end_cur_s = ctx->cur_s;
+    ctx->graph_end_key_w = ctx->key_w;
   }
   CU(cudaGraphLaunch(ctx->graph_exec, ctx->stream));
+  ctx->traj_s = ctx->graph_end_traj_s; // where the replayed sequence leaves the ping-pong state
+  ctx->cur_s = ctx->graph_end_cur_s;
+  ctx->key_w = ctx->graph_end_key_w;
   ctx->launches += ctx->graph_kernels;
   return DOAPP_OK;
 }
@@ -526,8 +539,6 @@ doapp_status doapp_create(const doapp_config *cfg, doapp_ctx **out) {
   ctx->S = (uint64_t)cfg->num_climbers * cfg->samples_per_climber;
   const char *ng = getenv("DOAPP_NO_GRAPH");
   ctx->use_graph = !(ng && ng[0] == '1');
-  const char *nf = getenv("DOAPP_NO_FUSE");
-  ctx->fuse_update = !(nf && nf[0] == '1');
   const char *xd = getenv("DOAPP_EXACT_DIV");
   ctx->fast_math_ok = !(xd && xd[0] == '1');
   host_sincos(-1.5707963267948966f, &ctx->rpy_s, &ctx->rpy_c);
@@ -539,21 +550,20 @@ doapp_status doapp_create(const doapp_config *cfg, doapp_ctx **out) {
     CU(cudaEventCreate(&ctx->ev0));
     CU(cudaEventCreate(&ctx->ev1));
     const size_t k = cfg->num_climbers, n = cfg->num_waypoints, d = cfg->waypoint_dim;
-    ST(ensure(ctx, ctx->traj, k * d * ctx->npad));
+    ctx->traj_half = k * d * ctx->npad;
+    ST(ensure(ctx, ctx->traj, 2 * ctx->traj_half));
     ST(ensure(ctx, ctx->aos_tmp, k * n * d));
     ST(ensure(ctx, ctx->start, 8));
     ST(ensure(ctx, ctx->scores, ctx->S));
     ST(ensure(ctx, ctx->coll, ctx->S));
     ST(ensure(ctx, ctx->final_scores, k));
     ST(ensure(ctx, ctx->final_coll, k));
-    ST(ensure(ctx, ctx->keys, k));
+    ST(ensure(ctx, ctx->keys, 3 * k));
     ST(ensure(ctx, ctx->keys_float, k));
-    ST(ensure(ctx, ctx->cur_hi, k));
-    ST(ensure(ctx, ctx->done, k));
-    CU(cudaMemsetAsync(ctx->done.p, 0, sizeof(unsigned int) * k, ctx->stream));
+    ST(ensure(ctx, ctx->cur_hi, 2 * k));
     ST(ensure(ctx, ctx->found, k));
     ST(ensure(ctx, ctx->out, 4 + 2 * n * d));
-    CU(cudaMemsetAsync(ctx->traj.p, 0, sizeof(float) * k * d * ctx->npad, ctx->stream));
+    CU(cudaMemsetAsync(ctx->traj.p, 0, sizeof(float) * 2 * ctx->traj_half, ctx->stream));
     CU(cudaMemsetAsync(ctx->start.p, 0, sizeof(float) * 8, ctx->stream));
     CU(cudaMemsetAsync(ctx->found.p, 0, k, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
@@ -588,7 +598,7 @@ void doapp_destroy(doapp_ctx *ctx) {
   release(ctx->traj); release(ctx->aos_tmp); release(ctx->start); release(ctx->noise);
   release(ctx->scores); release(ctx->final_scores); release(ctx->out); release(ctx->cloud);
   release(ctx->pts); release(ctx->coll); release(ctx->final_coll); release(ctx->keys);
-  release(ctx->keys_float); release(ctx->cur_hi); release(ctx->done); release(ctx->found); release(ctx->grid_cells);
+  release(ctx->keys_float); release(ctx->cur_hi); release(ctx->found); release(ctx->grid_cells);
   release(ctx->lookup_coll); release(ctx->lookup_idx); release(ctx->dbg_a); release(ctx->dbg_b);
   release(ctx->dbg_c); release(ctx->vbad);
   for (cudaEvent_t e : ctx->prof_events) cudaEventDestroy(e);
@@ -971,7 +981,8 @@ doapp_status doapp_plan_state(doapp_ctx *ctx, float *trajectories, float *scores
   CU(cudaStreamSynchronize(ctx->stream));
   if (trajectories) {
     std::vector<float> soa(k * d * npad);
-    CU(cudaMemcpy(soa.data(), ctx->traj.p, soa.size() * sizeof(float), cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(soa.data(), traj_half_ptr(ctx, ctx->traj_s), soa.size() * sizeof(float),
+                  cudaMemcpyDeviceToHost));
     for (size_t cl = 0; cl < k; ++cl)
       for (size_t w = 0; w < n; ++w)
         for (size_t j = 0; j < d; ++j)
@@ -1047,9 +1058,9 @@ doapp_status doapp_replan_dynamic(doapp_ctx *ctx, const float *start, const floa
                        ctx->stream));
   CU(cudaStreamSynchronize(ctx->stream));
   CU(cudaEventRecord(ctx->ev0, ctx->stream));
-  CU(cudaMemsetAsync(ctx->keys.p, 0xFF, sizeof(unsigned long long) * c.num_climbers, ctx->stream));
-  CU(cudaMemsetAsync(ctx->done.p, 0, sizeof(unsigned int) * c.num_climbers, ctx->stream));
-  // the initial score is taken against the first cloud's grid
+  const size_t k = c.num_climbers;
+  reset_plan_state(ctx);
+  CU(cudaMemsetAsync(ctx->keys.p, 0xFF, sizeof(unsigned long long) * 3 * k, ctx->stream));
   auto rebuild = [&](uint32_t it) -> doapp_status {
     CU(cudaMemsetAsync(ctx->grid_cells.p, 0, ctx->grid_bytes, ctx->stream));
     ScatterParams sp{};
@@ -1062,54 +1073,28 @@ doapp_status doapp_replan_dynamic(doapp_ctx *ctx, const float *start, const floa
     if (num_points) ctx->launches += 1;
     return DOAPP_OK;
   };
-  UpdateParams u{};
-  u.traj = ctx->traj.p;
-  u.noise_mode = NOISE_PHILOX;
-  u.k = c.num_climbers;
-  u.n = c.num_waypoints;
-  u.npad = ctx->npad;
-  u.d = c.waypoint_dim;
-  u.n_noise = c.noise_waypoints;
-  u.seed_lo = (uint32_t)c.seed;
-  u.seed_hi = (uint32_t)(c.seed >> 32);
-  u.sigma = c.sigma;
-  u.keys = ctx->keys.p;
-  u.cur_hi = ctx->cur_hi.p;
-  u.found_better = ctx->found.p;
   for (uint32_t it = 0; it < iters; ++it) {
     ST(rebuild(it));
-    // the world moved: re-score the kept trajectories against the new grid
-    const bool fuse = ctx->fuse_update && !ctx->comm;
-    CostParams p0 = climber_cost_params(ctx);
-    p0.keys = ctx->keys.p;
-    if (fuse) set_fuse(ctx, p0, 2);
-    CU(launch_cost(p0, c.waypoint_dim, ctx->sm_count, ctx->stream));
-    if (!fuse) {
-      UpdateParams ui = u;
-      ui.init = 1;
-      CU(launch_update(ui, ctx->stream));
-    }
+    // the world moved: apply the previous iteration's keep-best, then re-score the kept
+    // trajectories against the new grid (their key seeds cur_hi for this iteration)
+    ST(launch_pass(ctx, climber_cost_params(ctx), it ? PEND_KEEP_BEST : PEND_NONE, it ? it - 1 : 0,
+                   NOISE_PHILOX, nullptr, true));
     CostParams p = base_cost_params(ctx);
     p.noise_mode = NOISE_PHILOX;
     p.iteration = it;
-    p.keys = ctx->keys.p;
-    if (fuse) set_fuse(ctx, p, 1);
-    CU(launch_cost(p, c.waypoint_dim, ctx->sm_count, ctx->stream));
-    if (!fuse) {
-      UpdateParams uu = u;
-      uu.iteration = it;
-      uu.init = 0;
-      CU(launch_update(uu, ctx->stream));
-    }
-    ctx->launches += fuse ? 2 : 4;
+    ST(launch_pass(ctx, p, PEND_SEED, 0, NOISE_PHILOX, nullptr, true));
+    ctx->launches += 2;
   }
   {
     CostParams p = climber_cost_params(ctx);
     p.scores = ctx->final_scores.p;
     p.collisions = ctx->final_coll.p;
-    CU(launch_cost(p, c.waypoint_dim, ctx->sm_count, ctx->stream));
+    if (iters)
+      ST(launch_pass(ctx, p, PEND_KEEP_BEST, iters - 1, NOISE_PHILOX, nullptr, false));
+    else
+      ST(launch_pass(ctx, p, PEND_NONE, 0, NOISE_ZERO, nullptr, false));
     FinalParams f{};
-    f.traj = ctx->traj.p;
+    f.traj = traj_half_ptr(ctx, ctx->traj_s);
     f.start = ctx->start.p;
     f.scores = ctx->final_scores.p;
     f.found_better = ctx->found.p;

@@ -3,7 +3,8 @@
 // Stage map:
 //   cost_kernel     a1 (Philox noise, fused) + a2 perturb + a3 derivatives +
 //                   a4 FK + a5 grid gathers + a6 score + a7 per-climber argmin keys
-//   update_kernel   a7 keep-best (generate_trajectories.cu:225-241, D5/D6 fixed)
+//                   + a7 keep-best of the previous launch, applied while staging
+//                   (generate_trajectories.cu:225-241, D5/D6 fixed)
 //   final_kernel    host argmin of planning_state.cu:113-127 + velocities
 //   scatter_kernel  a10 point cloud -> voxel occupancy (occupancy_grid.cpp:42-58)
 //
@@ -19,6 +20,7 @@
 
 #include <cooperative_groups.h>
 
+#include <cstdlib>
 #include <cstring>
 
 #include "device_math.cuh"
@@ -89,35 +91,45 @@ __device__ __forceinline__ P3 rot_z(float s, float c, P3 q) {
   return u;
 }
 
-template <int D>
+// FAST: straight-line small-argument sin/cos (dm::sincos_small); *ok is cleared when an angle
+// is outside its range and the caller must redo the waypoint through the general path.
+template <int D, bool FAST>
 __device__ __forceinline__ void fk_points(const float (&th)[D], float rpy_s, float rpy_c,
-                                          P3 (&out)[5]) {
+                                          P3 (&out)[5], bool *ok) {
   float s, c;
   P3 p, q;
+  auto sc = [&](float a) {
+    if (FAST) {
+      *ok = *ok & (fabsf(a) < 131072.0f);
+      dm::sincos_small(a, &s, &c);
+    } else {
+      dm::sincos(a, &s, &c);
+    }
+  };
   // base: t = (0, -0.0015, 0.0715), roty(theta0)            gt.cu:405-410
-  dm::sincos(th[0], &s, &c);
+  sc(th[0]);
   q = P3{0.0f, -0.0015f, 0.0715f};
   p = rot_y(s, c, q);
   out[0] = p;
   // shoulder: t = (0, 0, 0.045), rotz(theta1)                gt.cu:416-421
-  dm::sincos(th[1], &s, &c);
+  sc(th[1]);
   q = P3{p.x, p.y, dm::add_(p.z, 0.045f)};
   p = rot_z(s, c, q);
   out[1] = p;
   // elbow: t = (0, 0, 0.1), roty(theta2)                     gt.cu:427-432
-  dm::sincos(th[2], &s, &c);
+  sc(th[2]);
   q = P3{p.x, p.y, dm::add_(p.z, 0.1f)};
   p = rot_y(s, c, q);
   out[2] = p;
   // wrist: t = (0, 0, 0.1), roty(theta3)                     gt.cu:438-443
-  dm::sincos(th[3], &s, &c);
+  sc(th[3]);
   q = P3{p.x, p.y, dm::add_(p.z, 0.1f)};
   p = rot_y(s, c, q);
   out[3] = p;
   // wrist rotate: t = (0, -0.0125, 0.08), roty(theta4)       gt.cu:449-454
   q = P3{p.x, dm::add_(p.y, -0.0125f), dm::add_(p.z, 0.08f)};
   if (D >= 5) {
-    dm::sincos(th[D >= 5 ? 4 : 0], &s, &c);
+    sc(th[D >= 5 ? 4 : 0]);
     p = rot_y(s, c, q);
   } else {
     p = q; // theta4 := 0 -> identity
@@ -183,14 +195,66 @@ __device__ __forceinline__ int collides(const CostParams &P, P3 p) {
   return in & (__ldg((const float *)g.cells + lin) <= P.coll_dist); // generate_trajectories.cu:412
 }
 
-template <int D, int GM, bool FIDX>
-__device__ __forceinline__ int num_collisions_v2(const CostParams &P, const float (&x)[D]) {
-  P3 pts[5];
-  fk_points<D>(x, P.rpy_s, P.rpy_c, pts);
-  int cnt = 0;
+// One waypoint of one sample: derivatives, smoothness / limit terms and the collision count
+// (generate_trajectories.cu:86-103,276-291,391-466).  FAST = straight-line code: reciprocal
+// divides and small-argument sin/cos computed unconditionally, one flag says whether every
+// operand was inside the verified ranges; the caller redoes the waypoint with FAST = false
+// (IEEE divides, full-range sin/cos) in the rare case it was not.  Both produce the same bits
+// wherever FAST is valid.  vnew = this waypoint's velocities (the caller commits them).
+template <int D, int GM, bool FIDX, bool LIM, bool FAST>
+__device__ __forceinline__ bool waypoint_cost(const CostParams &P, const float (&x)[D],
+                                              const float (&xprev)[D], const float (&vprev)[D],
+                                              float (&vnew)[D], float *a2_out, float *l2_out,
+                                              int *coll_out) {
+  bool ok = true;
+  float a2 = 0.0f, l2 = 0.0f;
+  auto dv = [&](float a) -> float {
+    if (FAST) {
+      const float aa = fabsf(a);
+      ok = ok & ((aa == 0.0f) | ((aa >= P.dt_div.lo) & (aa < P.dt_div.hi)));
+      return dm::div_fast_unguarded(a, P.dt_div);
+    }
+    return dm::div_(a, P.dt_div.b);
+  };
 #pragma unroll
-  for (int l = 0; l < 5; ++l) cnt += collides<GM, FIDX>(P, pts[l]);
-  return cnt;
+  for (int j = 0; j < D; ++j) {
+    const float v = dv(dm::sub_(x[j], xprev[j])); // :288
+    const float a = dv(dm::sub_(v, vprev[j]));
+    a2 = dm::add_(a2, dm::mul_(a, a)); // :76
+    vnew[j] = v;
+    if (LIM) {
+      const float h =
+          fmaxf(0.0f, fmaxf(dm::sub_(x[j], P.lim_max[j]), dm::sub_(P.lim_min[j], x[j])));
+      l2 = dm::add_(l2, dm::mul_(h, h));
+    }
+  }
+  int cnt = 0;
+  if (GM != GM_NONE) {
+    P3 pts[5];
+    fk_points<D, FAST>(x, P.rpy_s, P.rpy_c, pts, &ok);
+#pragma unroll
+    for (int l = 0; l < 5; ++l) cnt += collides<GM, FIDX>(P, pts[l]);
+  }
+  *a2_out = a2;
+  *l2_out = l2;
+  *coll_out = cnt;
+  return ok;
+}
+
+// by-value interface of the out-of-line general path: keeps the hot loop's arrays in registers
+template <int D> struct WpIn {
+  float x[D], xprev[D], vprev[D];
+};
+template <int D> struct WpOut {
+  float vnew[D], a2, l2;
+  int coll;
+};
+template <int D, int GM, bool FIDX, bool LIM>
+__device__ __noinline__ WpOut<D> waypoint_cost_general(const CostParams &P, WpIn<D> in) {
+  WpOut<D> o;
+  waypoint_cost<D, GM, FIDX, LIM, false>(P, in.x, in.xprev, in.vprev, o.vnew, &o.a2, &o.l2,
+                                         &o.coll);
+  return o;
 }
 
 __device__ __forceinline__ unsigned long long warp_min_u64(unsigned long long v) {
@@ -202,62 +266,7 @@ __device__ __forceinline__ unsigned long long warp_min_u64(unsigned long long v)
   return v;
 }
 
-// Keep-best of generate_trajectories.cu:225-241 (D5/D6 fixed) executed by the LAST warp that
-// reports for climber c (all of the climber's keys are merged by then): same rule as
-// update_kernel, fused into the cost kernel so that an iteration is one launch.
-template <int D>
-__device__ __noinline__ void fused_update(const CostParams &P, uint32_t c, int lane) {
-  __threadfence();
-  const unsigned long long key = __ldcg(P.keys + c);
-  const uint32_t hi = (uint32_t)(key >> 32), tg = (uint32_t)key;
-  const uint32_t cur = __ldcg(P.cur_hi + c);
-  if (P.fuse_mode == 2) { // seed the current score from the unperturbed trajectory (:180-191)
-    if (lane == 0) {
-      P.cur_hi[c] = hi;
-      P.found_better[c] = 0;
-    }
-  } else if (hi < cur) {
-    float *traj = P.traj_rw + (size_t)c * D * P.npad;
-    const float *nz = nullptr;
-    if (P.noise_mode == NOISE_EXTERNAL)
-      nz = P.noise + ((size_t)c * P.noise_m + (size_t)(tg - P.noise_t0)) * P.n_noise * D;
-    float eps[D];
-#pragma unroll
-    for (int j = 0; j < D; ++j) eps[j] = 0.0f;
-    if (P.n_noise == 1) {
-      if (P.noise_mode == NOISE_EXTERNAL) {
-#pragma unroll
-        for (int j = 0; j < D; ++j) eps[j] = nz[j];
-      } else if (P.noise_mode == NOISE_PHILOX) {
-        dm::noise_vec<D>(P.seed_lo, P.seed_hi, P.sigma, P.iteration, c, tg, 0, eps);
-      }
-    }
-    for (uint32_t w = lane; w < P.n; w += 32) {
-#pragma unroll
-      for (int j = 0; j < D; ++j) {
-        float e = eps[j];
-        if (P.n_noise != 1) {
-          if (P.noise_mode == NOISE_EXTERNAL)
-            e = nz[(size_t)w * D + j];
-          else if (P.noise_mode == NOISE_PHILOX)
-            e = dm::noise_at(P.seed_lo, P.seed_hi, P.sigma, P.iteration, c, tg, w, j);
-        }
-        float *q = traj + (size_t)j * P.npad + w;
-        *q = dm::add_(*q, e);
-      }
-    }
-    if (lane == 0) {
-      P.cur_hi[c] = hi;
-      P.found_better[c] = 1;
-    }
-  }
-  if (lane == 0) { // re-arm for the next launch
-    P.keys[c] = kKeyNone;
-    P.done[c] = 0u;
-  }
-}
-
-template <int D, int GM, bool NPW, bool FIDX>
+template <int D, int GM, bool NPW, bool FIDX, bool LIM>
 __global__ void __launch_bounds__(kMaxCostThreads)
     cost_kernel(const __grid_constant__ CostParams P) {
   namespace cg = cooperative_groups;
@@ -269,9 +278,10 @@ __global__ void __launch_bounds__(kMaxCostThreads)
   const uint32_t spb = (blockDim.x >> 5 >> P.pw_log2) * 32; // samples per block (32 if T > 1)
   float *sbase = smem;                                 // [n][DP]
   float *seps = sbase + (size_t)P.n * DP;              // [D][32]      (shared noise, PW >= 4)
-  float *spart = seps + (PW >= 4 ? D * 32 : 0);        // [n][32]      (T > 1; rank-0 CTA's is used)
+  float *swin = seps + (PW >= 4 ? D * 32 : 0);         // [8]          pending winner's noise
+  float *spart = swin + 8;                             // [n][32]      (T > 1; rank-0 CTA's is used)
   float *slim = spart + (T > 1 ? (size_t)P.n * 32 : 0); // [n][32]     (T > 1 and limits)
-  int *scoll = (int *)(slim + ((T > 1 && P.use_limits) ? (size_t)P.n * 32 : 0)); // [T][32]
+  int *scoll = (int *)(slim + ((T > 1 && LIM) ? (size_t)P.n * 32 : 0)); // [T][32]
 
   const bool clustered = cs_log2 != 0;
   cg::cluster_group cluster = cg::this_cluster();
@@ -288,17 +298,38 @@ __global__ void __launch_bounds__(kMaxCostThreads)
   t = active ? t : P.m - 1; // idle lanes shadow the last sample (no divergence, no stores)
   const uint32_t tg = (uint32_t)(P.sample_offset + t);
 
-  // stage the climber's trajectory: SoA [j][npad] in global -> AoS [w][DP] in shared
-  {
-    const float *traj = P.traj + (size_t)c * D * P.npad;
-    for (uint32_t i = threadIdx.x; i < P.n * D; i += blockDim.x) {
-      const uint32_t j = i / P.n, w = i - j * P.n;
-      sbase[w * DP + j] = __ldcg(traj + (size_t)j * P.npad + w); // rewritten by fused_update
-    }
-  }
   float start[D];
 #pragma unroll
   for (int j = 0; j < D; ++j) start[j] = __ldg(P.start + j);
+
+  // ---- pending keep-best of the PREVIOUS launch (generate_trajectories.cu:225-241, D5/D6
+  // fixed).  The previous cost launch left the climber's winning key; instead of a separate
+  // update kernel every CTA applies the winner's noise while it stages the trajectory, and
+  // the climber's first CTA also writes the updated state for the launch after this one.
+  uint32_t pend_tg = 0;
+  bool improve = false;
+  if (P.pend_mode != PEND_NONE) {
+    const unsigned long long pk = __ldg(P.pend_keys + c);
+    const uint32_t hi = (uint32_t)(pk >> 32);
+    pend_tg = (uint32_t)pk;
+    uint32_t cur_new = hi;
+    if (P.pend_mode == PEND_KEEP_BEST) {
+      const uint32_t cur = __ldg(P.cur_hi_in + c);
+      improve = hi < cur;
+      cur_new = improve ? hi : cur;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+      P.cur_hi_out[c] = cur_new;
+      if (P.pend_mode == PEND_SEED)
+        P.found_better[c] = 0;
+      else if (improve)
+        P.found_better[c] = 1;
+    }
+  }
+  if (blockIdx.x == 0 && P.keys_reset && threadIdx.x == 0) P.keys_reset[c] = kKeyNone;
+  const float *pnz = nullptr; // the winner's noise row in the previous launch's external buffer
+  if (improve && P.pend_noise_mode == NOISE_EXTERNAL)
+    pnz = P.pend_noise + ((size_t)c * P.noise_m + (size_t)(pend_tg - P.noise_t0)) * P.n_noise * D;
 
   const float *nz = nullptr;
   if (P.noise_mode == NOISE_EXTERNAL)
@@ -322,6 +353,43 @@ __global__ void __launch_bounds__(kMaxCostThreads)
         if (2 * warp < D) seps[(2 * warp) * 32 + lane] = a;
         if (2 * warp + 1 < D && warp < 2) seps[(2 * warp + 1) * 32 + lane] = b;
       }
+    }
+    // the pending winner's noise vector (one d-vector per sample, D16): three lanes of the
+    // CTA's last warp redraw its Box-Muller pairs
+    if (improve && P.n_noise == 1 && warp == (blockDim.x >> 5) - 1 && lane < 3) {
+      float a = 0.0f, b = 0.0f;
+      if (P.pend_noise_mode == NOISE_PHILOX) {
+        dm::noise_pair(P.seed_lo, P.seed_hi, P.sigma, P.pend_iteration, c, pend_tg, 0, lane, &a, &b);
+      } else if (P.pend_noise_mode == NOISE_EXTERNAL) {
+        a = 2 * lane < D ? __ldg(pnz + 2 * lane) : 0.0f;
+        b = 2 * lane + 1 < D ? __ldg(pnz + 2 * lane + 1) : 0.0f;
+      }
+      if (2 * lane < D) swin[2 * lane] = a;
+      if (2 * lane + 1 < D) swin[2 * lane + 1] = b;
+    }
+  }
+  if (improve) __syncthreads(); // block-uniform
+
+  // stage the climber's trajectory (with the pending update applied): SoA [j][npad] in
+  // global -> AoS [w][DP] in shared
+  {
+    const float *traj = P.traj + (size_t)c * D * P.npad;
+    float *tnext = (blockIdx.x == 0 && P.traj_next) ? P.traj_next + (size_t)c * D * P.npad : nullptr;
+    for (uint32_t i = threadIdx.x; i < P.n * D; i += blockDim.x) {
+      const uint32_t j = i / P.n, w = i - j * P.n;
+      float b = __ldg(traj + (size_t)j * P.npad + w);
+      if (improve) {
+        float e;
+        if (P.n_noise == 1)
+          e = swin[j];
+        else if (P.pend_noise_mode == NOISE_EXTERNAL)
+          e = __ldg(pnz + (size_t)w * D + j);
+        else
+          e = dm::noise_at(P.seed_lo, P.seed_hi, P.sigma, P.pend_iteration, c, pend_tg, w, j);
+        b = dm::add_(b, e);
+      }
+      sbase[w * DP + j] = b;
+      if (tnext) tnext[(size_t)j * P.npad + w] = b;
     }
   }
   __syncthreads();
@@ -374,30 +442,40 @@ __global__ void __launch_bounds__(kMaxCostThreads)
 
   float total = 0.0f, ltotal = 0.0f;
   int coll = 0;
+#pragma unroll 2
   for (; w < w_end; ++w) {
-    float x[D];
-    float a2 = 0.0f, l2 = 0.0f;
+    float x[D], vnew[D];
+#pragma unroll
+    for (int j = 0; j < D; ++j) x[j] = noisy(w, j);
+    float a2, l2;
+    int cw;
+    if (!waypoint_cost<D, GM, FIDX, LIM, true>(P, x, xprev, vprev, vnew, &a2, &l2, &cw)) {
+      WpIn<D> in; // rare: an operand outside the verified ranges -> IEEE divides, full sin/cos
+#pragma unroll
+      for (int j = 0; j < D; ++j) {
+        in.x[j] = x[j];
+        in.xprev[j] = xprev[j];
+        in.vprev[j] = vprev[j];
+      }
+      const WpOut<D> o = waypoint_cost_general<D, GM, FIDX, LIM>(P, in);
+#pragma unroll
+      for (int j = 0; j < D; ++j) vnew[j] = o.vnew[j];
+      a2 = o.a2;
+      l2 = o.l2;
+      cw = o.coll;
+    }
 #pragma unroll
     for (int j = 0; j < D; ++j) {
-      x[j] = noisy(w, j);
-      const float v = dm::div_fast(dm::sub_(x[j], xprev[j]), P.dt_div); // :288
-      const float a = dm::div_fast(dm::sub_(v, vprev[j]), P.dt_div);
-      a2 = dm::add_(a2, dm::mul_(a, a));                                 // :76
       xprev[j] = x[j];
-      vprev[j] = v;
-      if (P.use_limits) {
-        const float h =
-            fmaxf(0.0f, fmaxf(dm::sub_(x[j], P.lim_max[j]), dm::sub_(P.lim_min[j], x[j])));
-        l2 = dm::add_(l2, dm::mul_(h, h));
-      }
+      vprev[j] = vnew[j];
     }
-    if (GM != GM_NONE && P.collision_mode != 0) coll += num_collisions_v2<D, GM, FIDX>(P, x);
+    coll += cw;
     if (T == 1) { // fixed order: left fold over the waypoints (oracle ORC_SUM_WAYPOINT)
       total = dm::add_(total, a2);
-      ltotal = dm::add_(ltotal, l2);
+      if (LIM) ltotal = dm::add_(ltotal, l2);
     } else {
       spart0[w * 32 + lane] = a2;
-      if (P.use_limits) slim0[w * 32 + lane] = l2;
+      if (LIM) slim0[w * 32 + lane] = l2;
     }
   }
   if (T > 1) {
@@ -411,13 +489,12 @@ __global__ void __launch_bounds__(kMaxCostThreads)
     for (uint32_t q = 0; q < T; ++q) coll += scoll[q * 32 + lane];
     for (uint32_t ww = 0; ww < P.n; ++ww) {
       total = dm::add_(total, spart[ww * 32 + lane]);
-      if (P.use_limits) ltotal = dm::add_(ltotal, slim[ww * 32 + lane]);
+      if (LIM) ltotal = dm::add_(ltotal, slim[ww * 32 + lane]);
     }
   }
 
   float score = dm::add_((float)coll, dm::mul_(P.smooth_scale, total)); // :81,100,107-108
-  if (P.use_limits && P.limit_weight != 0.0f)
-    score = dm::add_(score, dm::mul_(P.limit_weight, ltotal));
+  if (LIM && P.limit_weight != 0.0f) score = dm::add_(score, dm::mul_(P.limit_weight, ltotal));
   if (active) {
     const size_t s = (size_t)c * P.m + t;
     if (P.scores) P.scores[s] = score;
@@ -433,68 +510,7 @@ __global__ void __launch_bounds__(kMaxCostThreads)
     unsigned long long key =
         active ? ((unsigned long long)key_hi(P.select_mode, score) << 32) | tg : kKeyNone;
     key = warp_min_u64(key);
-    unsigned int prior = 0;
-    if (lane == 0) {
-      atomicMin(P.keys + c, key);
-      if (P.fuse_mode) {
-        __threadfence();
-        prior = atomicAdd(P.done + c, 1u);
-      }
-    }
-    if (P.fuse_mode) {
-      prior = __shfl_sync(kFull, prior, 0);
-      if (prior == P.units_per_climber - 1) fused_update<D>(P, c, lane);
-    }
-  }
-}
-
-
-// -------------------------------------------------------------- update kernel
-// One block per climber: keep-best of generate_trajectories.cu:225-241 (the
-// winning sample replaces the climber's trajectory when its key beats the
-// current one), then re-arm the key slot for the next iteration.
-__global__ void update_kernel(const __grid_constant__ UpdateParams P) {
-  const uint32_t c = blockIdx.x;
-  __shared__ unsigned long long s_key;
-  __shared__ uint32_t s_cur;
-  if (threadIdx.x == 0) {
-    s_key = P.keys[c];
-    s_cur = P.cur_hi[c];
-  }
-  __syncthreads();
-  const unsigned long long key = s_key;
-  const uint32_t hi = (uint32_t)(key >> 32), tg = (uint32_t)key;
-  if (P.init) {
-    if (threadIdx.x == 0) {
-      P.cur_hi[c] = hi;
-      P.found_better[c] = 0;
-      P.keys[c] = kKeyNone;
-    }
-    return;
-  }
-  const bool improve = hi < s_cur;
-  if (improve) {
-    float *traj = P.traj + (size_t)c * P.d * P.npad;
-    const float *nz = nullptr;
-    if (P.noise_mode == NOISE_EXTERNAL)
-      nz = P.noise + ((size_t)c * P.noise_m + (size_t)(tg - P.noise_t0)) * P.n_noise * P.d;
-    for (uint32_t i = threadIdx.x; i < P.n * P.d; i += blockDim.x) {
-      const uint32_t j = i / P.n, w = i - j * P.n;
-      const uint32_t wn = P.n_noise == 1 ? 0 : w;
-      float e = 0.0f;
-      if (P.noise_mode == NOISE_EXTERNAL)
-        e = nz[(size_t)wn * P.d + j];
-      else if (P.noise_mode == NOISE_PHILOX)
-        e = dm::noise_at(P.seed_lo, P.seed_hi, P.sigma, P.iteration, c, tg, wn, j);
-      traj[(size_t)j * P.npad + w] = dm::add_(traj[(size_t)j * P.npad + w], e);
-    }
-  }
-  if (threadIdx.x == 0) {
-    if (improve) {
-      P.cur_hi[c] = hi;
-      P.found_better[c] = 1;
-    }
-    P.keys[c] = kKeyNone;
+    if (lane == 0) atomicMin(P.keys + c, key);
   }
 }
 
@@ -600,7 +616,8 @@ __global__ void debug_fk_kernel(const float *wp, uint64_t count, float rpy_s, fl
 #pragma unroll
   for (int j = 0; j < D; ++j) th[j] = wp[i * D + j];
   P3 pts[5];
-  fk_points<D>(th, rpy_s, rpy_c, pts);
+  bool ok = true;
+  fk_points<D, false>(th, rpy_s, rpy_c, pts, &ok);
   for (int l = 0; l < 5; ++l) {
     out[(i * 5 + l) * 3 + 0] = pts[l].x;
     out[(i * 5 + l) * 3 + 1] = pts[l].y;
@@ -636,49 +653,53 @@ inline unsigned blocks_for(uint64_t total, unsigned threads) {
 
 void host_sincos(float x, float *s, float *c) { dm::sincos(x, s, c); }
 
-template <int D, int GM, bool NPW>
+template <int D, int GM, bool NPW, bool LIM>
 static cudaError_t launch_cost_t(const CostParams &p, dim3 grid, unsigned threads, size_t smem,
-                                 unsigned cluster, bool fidx, cudaStream_t st) {
-  auto go = [&](auto kern) -> cudaError_t {
-    if (smem > 48 * 1024) {
-      cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           (int)smem);
-      if (e != cudaSuccess) return e;
-    }
-    cudaLaunchConfig_t cfg{};
-    cfg.gridDim = grid;
-    cfg.blockDim = dim3(threads);
-    cfg.dynamicSmemBytes = smem;
-    cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = cluster;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = cluster > 1 ? 1 : 0;
-    return cudaLaunchKernelEx(&cfg, kern, p);
-  };
-  if (fidx) return go(cost_kernel<D, GM, NPW, true>);
-  return go(cost_kernel<D, GM, NPW, false>);
+                                 unsigned cluster, cudaStream_t st) {
+  // the specialised CDG kernels exist only with the verified reciprocal index divide; a grid
+  // whose verification failed (or DOAPP_EXACT_DIV=1) runs the generic kernel (IEEE divides)
+  constexpr bool FIDX = GM == GM_U8_CDG || GM == GM_F32_CDG;
+  auto kern = cost_kernel<D, GM, NPW, FIDX, LIM>;
+  if (smem > 48 * 1024) {
+    cudaError_t e =
+        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+  }
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = dim3(threads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = cluster;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = cluster > 1 ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, p);
 }
 
 template <int D>
 static cudaError_t launch_cost_d(const CostParams &p, dim3 grid, unsigned threads, size_t smem,
                                  unsigned cluster, cudaStream_t st) {
   int gm = GM_NONE;
-  if (p.collision_mode != 0 && p.grid.kind != 0 && p.grid.cells)
-    gm = p.grid.frame != 0 ? GM_GENERIC : (p.grid.kind == 1 ? GM_U8_CDG : GM_F32_CDG);
+  if (p.collision_mode != 0 && p.grid.kind != 0 && p.grid.cells) {
+    gm = GM_GENERIC;
+    if (p.grid.frame == 0 && p.grid.fast_idx) gm = p.grid.kind == 1 ? GM_U8_CDG : GM_F32_CDG;
+  }
   const bool npw = p.n_noise != 1 && p.noise_mode != NOISE_ZERO;
-  const bool fidx = p.grid.fast_idx != 0;
-#define DOAPP_GO(GMV, F)                                                                  \
-  return npw ? launch_cost_t<D, GMV, true>(p, grid, threads, smem, cluster, F, st)        \
-             : launch_cost_t<D, GMV, false>(p, grid, threads, smem, cluster, F, st)
+  const bool lim = p.use_limits != 0;
+#define DOAPP_GO(GMV)                                                                       \
+  return npw ? (lim ? launch_cost_t<D, GMV, true, true>(p, grid, threads, smem, cluster, st)  \
+                    : launch_cost_t<D, GMV, true, false>(p, grid, threads, smem, cluster, st)) \
+             : (lim ? launch_cost_t<D, GMV, false, true>(p, grid, threads, smem, cluster, st) \
+                    : launch_cost_t<D, GMV, false, false>(p, grid, threads, smem, cluster, st))
   switch (gm) {
-  case GM_U8_CDG: DOAPP_GO(GM_U8_CDG, fidx);
-  case GM_F32_CDG: DOAPP_GO(GM_F32_CDG, fidx);
-  case GM_GENERIC: DOAPP_GO(GM_GENERIC, false);
-  default: DOAPP_GO(GM_NONE, false);
+  case GM_U8_CDG: DOAPP_GO(GM_U8_CDG);
+  case GM_F32_CDG: DOAPP_GO(GM_F32_CDG);
+  case GM_GENERIC: DOAPP_GO(GM_GENERIC);
+  default: DOAPP_GO(GM_NONE);
   }
 #undef DOAPP_GO
 }
@@ -695,7 +716,7 @@ cudaError_t launch_cost(const CostParams &p_in, int d, int sm_count, cudaStream_
   const uint64_t sample_warps = (uint64_t)p.k * ((p.m + 31) / 32);
   const uint64_t target_warps = (uint64_t)sm_count * 12;
   auto smem_for = [&](uint32_t T) -> size_t {
-    size_t f = (size_t)p.n * dp;
+    size_t f = (size_t)p.n * dp + 8;
     if (T >= 4) f += (size_t)d * 32;
     if (T > 1) f += (size_t)p.n * 32 * (p.use_limits ? 2 : 1) + (size_t)T * 32;
     return f * sizeof(float);
@@ -704,6 +725,11 @@ cudaError_t launch_cost(const CostParams &p_in, int d, int sm_count, cudaStream_
   while (lg < 5 && (2u << lg) <= p.n && sample_warps * (1u << lg) < target_warps &&
          smem_for(2u << lg) <= 200 * 1024)
     ++lg;
+  {
+    // tuning override: DOAPP_PARTS_LOG2 caps the threads per sample (profiling only)
+    static const char *env = getenv("DOAPP_PARTS_LOG2");
+    if (env && env[0] >= '0' && env[0] <= '5' && (uint32_t)(env[0] - '0') < lg) lg = env[0] - '0';
+  }
   p.parts_log2 = lg;
   const uint32_t T = 1u << lg;
   p.pw_log2 = lg < 2 ? lg : 2;
@@ -714,7 +740,6 @@ cudaError_t launch_cost(const CostParams &p_in, int d, int sm_count, cudaStream_
   const uint32_t spb = 32 * sw;
   const dim3 grid(((p.m + spb - 1) / spb) * cs, p.k);
   const size_t smem = smem_for(T);
-  p.units_per_climber = T > 1 ? grid.x / cs : grid.x * sw; // warps that fold + report
   return d == 5 ? launch_cost_d<5>(p, grid, threads, smem, cs, st)
                 : launch_cost_d<4>(p, grid, threads, smem, cs, st);
 }
@@ -722,13 +747,6 @@ cudaError_t launch_cost(const CostParams &p_in, int d, int sm_count, cudaStream_
 cudaError_t launch_verify_div(dm::FastDiv d, uint32_t lo_bits, uint32_t hi_bits, int mode,
                               unsigned long long *bad, int sm_count, cudaStream_t st) {
   verify_div_kernel<<<sm_count * 8, 256, 0, st>>>(d, lo_bits, hi_bits, mode, bad);
-  return cudaGetLastError();
-}
-
-cudaError_t launch_update(const UpdateParams &p, cudaStream_t st) {
-  if (p.k == 0) return cudaSuccess;
-  unsigned threads = p.n * p.d < 128 ? 64 : (p.n * p.d < 512 ? 128 : 256);
-  update_kernel<<<p.k, threads, 0, st>>>(p);
   return cudaGetLastError();
 }
 

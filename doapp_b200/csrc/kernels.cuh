@@ -13,6 +13,9 @@ constexpr int kMaxJoints = 5;
 constexpr uint64_t kKeyNone = 0xFFFFFFFFFFFFFFFFull;
 
 enum NoiseMode : int { NOISE_ZERO = 0, NOISE_EXTERNAL = 1, NOISE_PHILOX = 2 };
+// PEND_SEED: the previous launch scored the unperturbed trajectories, its key seeds cur_hi
+// (generate_trajectories.cu:180-191); PEND_KEEP_BEST: the winner replaces the trajectory if better
+enum PendMode : int { PEND_NONE = 0, PEND_KEEP_BEST = 1, PEND_SEED = 2 };
 
 // Device view of the voxel grid (dense, index ix + nx*iy + nx*ny*iz).
 struct GridDev {
@@ -53,31 +56,22 @@ struct CostParams {
   unsigned long long *keys;      // [k] packed argmin keys for the update rule, or nullptr
   unsigned long long *keys_float; // [k] packed (float bits, t) keys for the host-style argmin
   dm::FastDiv dt_div, res_div; // divisor + RN(1/divisor)
-  // fused keep-best (single-GPU path): the last warp to finish a climber applies
-  // update_kernel's rule itself.  fuse_mode 0 = off, 1 = keep-best, 2 = seed cur_hi
-  int fuse_mode;
-  float *traj_rw;          // same buffer as traj, writable
-  uint32_t *cur_hi;        // [k]
-  uint8_t *found_better;   // [k]
-  unsigned int *done;      // [k] finished-warp counters, self-resetting
-  uint32_t units_per_climber; // warps that report per climber (filled by launch_cost)
+  // pending keep-best of the previous launch, applied by this one while it stages the
+  // trajectory (see cost_kernel): winner key per climber, the noise that launch drew, the
+  // climber's current rounded score in / out, and the other trajectory buffer to write
+  int pend_mode;                        // PendMode
+  const unsigned long long *pend_keys;  // [k]
+  uint32_t pend_iteration;
+  int pend_noise_mode;
+  const float *pend_noise;              // external buffer of that launch (same layout as noise)
+  const uint32_t *cur_hi_in;            // [k]
+  uint32_t *cur_hi_out;                 // [k]
+  uint8_t *found_better;                // [k]
+  float *traj_next;                     // [k][d][npad] or nullptr
+  unsigned long long *keys_reset;       // [k] key buffer to re-arm for a later launch, or nullptr
   // launch geometry (filled by launch_cost): 2^parts_log2 threads per sample, each owning
   // wpp consecutive waypoints; 2^pw_log2 of them per CTA, the rest across a cluster
   uint32_t parts_log2, pw_log2, wpp;
-};
-
-struct UpdateParams {
-  float *traj; // [k][d][npad]
-  const float *noise;
-  uint64_t noise_m, noise_t0;
-  int noise_mode;
-  uint32_t k, n, npad, d, n_noise;
-  uint32_t iteration, seed_lo, seed_hi;
-  float sigma;
-  unsigned long long *keys; // [k], consumed and reset
-  uint32_t *cur_hi;         // [k]
-  uint8_t *found_better;    // [k]
-  int init;                 // 1: seed cur_hi from keys, no trajectory change
 };
 
 struct FinalParams {
@@ -102,7 +96,6 @@ struct ScatterParams {
 cudaError_t launch_cost(const CostParams &p, int d, int sm_count, cudaStream_t st);
 cudaError_t launch_verify_div(dm::FastDiv d, uint32_t lo_bits, uint32_t hi_bits, int mode,
                               unsigned long long *bad, int sm_count, cudaStream_t st);
-cudaError_t launch_update(const UpdateParams &p, cudaStream_t st);
 cudaError_t launch_final(const FinalParams &p, cudaStream_t st);
 cudaError_t launch_scatter(const ScatterParams &p, int sm_count, cudaStream_t st);
 cudaError_t launch_lookup(const GridDev &g, const float *xyz, uint64_t count, float coll_dist,
