@@ -1,0 +1,65 @@
+// planning_state_test.cpp — drives PlanningState the way perturbator/src/main.cu:24-43 does
+// (joint_state + goal_state callbacks, plan(), publish_trajectory()) without ROS, and prints the
+// published JointTrajectory as JSON for tests/test_host_gpu.py to check against the oracle.
+//   planning_state_test k m n d grid_n resolution iterations cloud.bin|- 
+#include <cstdio>
+#include <cstdlib>
+#include <memory>
+#include <vector>
+
+#include "planning_state.hpp"
+
+int main(int argc, char **argv) {
+  if (argc < 9) {
+    std::fprintf(stderr, "usage: %s k m n d grid_n resolution iterations cloud.bin|-\n", argv[0]);
+    return 2;
+  }
+  const unsigned k = std::atoi(argv[1]), m = std::atoi(argv[2]), n = std::atoi(argv[3]),
+                 d = std::atoi(argv[4]), gn = std::atoi(argv[5]), iters = std::atoi(argv[7]);
+  const double res = std::atof(argv[6]);
+  const doapp::cpu_distance_grid::Dimensions dims = {gn, gn, gn, res};
+  PlanningState planning_state(k, m, n, d, dims);
+  planning_state.setIterations(iters);
+
+  if (argv[8][0] != '-') { // the grid feed: an xyz cloud scattered into the grid
+    FILE *f = std::fopen(argv[8], "rb");
+    if (!f) return 3;
+    std::fseek(f, 0, SEEK_END);
+    long bytes = std::ftell(f);
+    std::fseek(f, 0, SEEK_SET);
+    doapp_host::PointCloudXYZ cloud;
+    cloud.xyz.resize(bytes / sizeof(float));
+    if (std::fread(cloud.xyz.data(), 1, bytes, f) != (size_t)bytes) return 3;
+    std::fclose(f);
+    planning_state.updatePointCloud(cloud);
+  }
+
+  auto state = std::make_shared<doapp_host::JointState>();
+  state->position = {0.0, 0.0, 0.0, 0.0, 0.0, 0.7}; // 6 servos reported, truncated to d
+  auto goal = std::make_shared<doapp_host::JointState>();
+  goal->position = {0.0, -1.0, 1.5, -1.5, 0.0}; // task/src/main.cpp:39 + wrist_rotate
+  planning_state.updateArmState(state);
+  planning_state.updateGoalState(goal);
+  doapp_host::Publisher pub;
+  if (!planning_state.have_goal()) return 4;
+  planning_state.plan();
+  planning_state.publish_trajectory(pub); // main.cu:40-43
+  if (planning_state.have_goal() || pub.published.size() != 1) return 5;
+  planning_state.updateGoalState(goal); // unchanged goal: no replanning (planning_state.cuh:39)
+  if (planning_state.have_goal()) return 6;
+
+  const doapp_host::JointTrajectory &msg = pub.published[0];
+  std::printf("{\"cost\": %.9g, \"points\": [", planning_state.last_cost());
+  for (size_t i = 0; i < msg.points.size(); ++i) {
+    const auto &p = msg.points[i];
+    std::printf("%s{\"t\": %.9g, \"positions\": [", i ? ", " : "", p.time_from_start);
+    for (size_t j = 0; j < p.positions.size(); ++j)
+      std::printf("%s%.9g", j ? ", " : "", p.positions[j]);
+    std::printf("], \"velocities\": [");
+    for (size_t j = 0; j < p.velocities.size(); ++j)
+      std::printf("%s%.9g", j ? ", " : "", p.velocities[j]);
+    std::printf("]}");
+  }
+  std::printf("]}\n");
+  return 0;
+}
