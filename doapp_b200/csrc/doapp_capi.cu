@@ -87,6 +87,7 @@ struct doapp_ctx {
   DevBuf<int32_t> coll, final_coll;
   DevBuf<unsigned long long> keys, keys_float;
   DevBuf<uint32_t> cur_hi;
+  DevBuf<long long> usum; // weighted update: 2 x [k][8] integer sums (ping-pong)
   // Ping-pong state of the planner: traj holds two [k][d][npad] halves, cur_hi two [k]
   // halves, keys three [k] buffers (read / write / being re-armed).  Every launch that
   // applies a pending keep-best reads half traj_s and writes the other (kernels.cuh).
@@ -345,6 +346,10 @@ doapp_status enqueue_plan(doapp_ctx *ctx, uint32_t iters, int noise_mode, uint64
   auto noise_of = [&](uint32_t it) -> const float * {
     return noise_mode == NOISE_EXTERNAL ? ctx->noise.p + (size_t)it * noise_iter_stride : nullptr;
   };
+  const bool weighted = c.update_mode == DOAPP_UPDATE_WEIGHTED;
+  const int pend_it = weighted ? PEND_WEIGHTED : PEND_KEEP_BEST;
+  if (weighted)
+    CU(cudaMemsetAsync(ctx->usum.p, 0, sizeof(long long) * 2 * k * 8, ctx->stream));
   for (uint32_t it = 0; it < iters; ++it) {
     CostParams p = base_cost_params(ctx);
     p.noise_mode = noise_mode;
@@ -352,8 +357,16 @@ doapp_status enqueue_plan(doapp_ctx *ctx, uint32_t iters, int noise_mode, uint64
     p.noise = noise_of(it);
     p.noise_m = ctx->m_global;
     p.noise_t0 = 0;
+    if (weighted) {
+      // the update vector needs every sample's score and the block's int(ceilf(.)) minimum
+      p.scores = ctx->scores.p;
+      p.select_mode = DOAPP_SELECT_CEIL_INT;
+      p.update_gain = c.update_gain;
+      p.pend_usum = ctx->usum.p + (size_t)((it + 1) & 1) * k * 8; // sums of iteration it-1
+      p.usum_reset = ctx->usum.p + (size_t)(it & 1) * k * 8;      // zeroed for this iteration
+    }
     if (ctx->profiling) CU(cudaEventRecord(ctx->prof_events[2 * it], ctx->stream));
-    ST(launch_pass(ctx, p, it == 0 ? PEND_SEED : PEND_KEEP_BEST, it ? it - 1 : 0, noise_mode,
+    ST(launch_pass(ctx, p, it == 0 ? PEND_SEED : pend_it, it ? it - 1 : 0, noise_mode,
                    it ? noise_of(it - 1) : nullptr, true));
     if (ctx->profiling) CU(cudaEventRecord(ctx->prof_events[2 * it + 1], ctx->stream));
     nk += 1;
@@ -364,15 +377,47 @@ doapp_status enqueue_plan(doapp_ctx *ctx, uint32_t iters, int noise_mode, uint64
         return fail(ctx, DOAPP_NCCL_ERROR, "ncclAllReduce: %s",
                     nccl->GetErrorString ? nccl->GetErrorString(r) : "error");
     }
+    if (weighted) {
+      // compute_update_vector (gt.cu:117-133) over this rank's samples, integer sums
+      UpdateParams u{};
+      u.scores = ctx->scores.p;
+      u.keys = ctx->keys.p + (size_t)ctx->key_w * k;
+      u.noise = noise_of(it);
+      u.noise_m = ctx->m_global;
+      u.noise_t0 = 0;
+      u.noise_mode = noise_mode;
+      u.k = c.num_climbers;
+      u.m = c.samples_per_climber;
+      u.d = c.waypoint_dim;
+      u.iteration = it;
+      u.seed_lo = (uint32_t)c.seed;
+      u.seed_hi = (uint32_t)(c.seed >> 32);
+      u.sigma = c.sigma;
+      u.sample_offset = c.sample_offset;
+      u.usum = ctx->usum.p + (size_t)(it & 1) * k * 8;
+      CU(launch_update_vector(u, ctx->sm_count, ctx->stream));
+      nk += 1;
+      if (nccl) { // exact: integer sums commute
+        ncclResult_t r =
+            nccl->AllReduce(u.usum, u.usum, k * 8, ncclInt64, ncclSum, ctx->comm, ctx->stream);
+        if (r != ncclSuccess)
+          return fail(ctx, DOAPP_NCCL_ERROR, "ncclAllReduce(sum): %s",
+                      nccl->GetErrorString ? nccl->GetErrorString(r) : "error");
+      }
+    }
   }
   {
     CostParams p = climber_cost_params(ctx);
     p.scores = ctx->final_scores.p;
     p.collisions = ctx->final_coll.p;
+    if (weighted) {
+      p.update_gain = c.update_gain;
+      p.pend_usum = ctx->usum.p + (size_t)((iters + 1) & 1) * k * 8;
+    }
     // the winner's noise of the last iteration is still needed to apply its keep-best
     p.noise_m = ctx->m_global;
     p.noise_t0 = 0;
-    ST(launch_pass(ctx, p, iters == 0 ? PEND_SEED : PEND_KEEP_BEST, iters ? iters - 1 : 0,
+    ST(launch_pass(ctx, p, iters == 0 ? PEND_SEED : pend_it, iters ? iters - 1 : 0,
                    noise_mode, iters ? noise_of(iters - 1) : nullptr, false));
     FinalParams f{};
     f.traj = traj_half_ptr(ctx, ctx->traj_s);
@@ -513,11 +558,16 @@ doapp_status doapp_create(const doapp_config *cfg, doapp_ctx **out) {
     return fail(nullptr, DOAPP_INVALID_ARG, "doapp_create: noise_waypoints must be 1 or n");
   if (!(cfg->delta_t > 0.0f))
     return fail(nullptr, DOAPP_INVALID_ARG, "doapp_create: delta_t must be > 0");
-  if (cfg->update_mode != DOAPP_UPDATE_KEEP_BEST)
-    return fail(nullptr, DOAPP_INVALID_ARG,
-                "doapp_create: only DOAPP_UPDATE_KEEP_BEST is implemented");
+  if (cfg->update_mode != DOAPP_UPDATE_KEEP_BEST && cfg->update_mode != DOAPP_UPDATE_WEIGHTED)
+    return fail(nullptr, DOAPP_INVALID_ARG, "doapp_create: unknown update_mode %d",
+                cfg->update_mode);
   uint64_t mg = cfg->global_samples_per_climber ? cfg->global_samples_per_climber
                                                 : cfg->samples_per_climber;
+  // weighted update: one d-vector of noise per sample (generate_trajectories.cu:117-142), and the
+  // 64-bit fixed-point sums (terms < 2^12 scaled by 2^28) must not overflow
+  if (cfg->update_mode == DOAPP_UPDATE_WEIGHTED && (cfg->noise_waypoints != 1 || mg > (1ull << 22)))
+    return fail(nullptr, DOAPP_INVALID_ARG,
+                "doapp_create: DOAPP_UPDATE_WEIGHTED needs noise_waypoints == 1 and m_global <= 2^22");
   if (cfg->sample_offset + cfg->samples_per_climber > mg || mg > 0xFFFFFFFFull)
     return fail(nullptr, DOAPP_INVALID_ARG, "doapp_create: shard [%llu,+%u) outside m_global %llu",
                 (unsigned long long)cfg->sample_offset, cfg->samples_per_climber,
@@ -561,6 +611,7 @@ doapp_status doapp_create(const doapp_config *cfg, doapp_ctx **out) {
     ST(ensure(ctx, ctx->keys, 3 * k));
     ST(ensure(ctx, ctx->keys_float, k));
     ST(ensure(ctx, ctx->cur_hi, 2 * k));
+    ST(ensure(ctx, ctx->usum, 2 * k * 8));
     ST(ensure(ctx, ctx->found, k));
     ST(ensure(ctx, ctx->out, 4 + 2 * n * d));
     CU(cudaMemsetAsync(ctx->traj.p, 0, sizeof(float) * 2 * ctx->traj_half, ctx->stream));
@@ -600,7 +651,7 @@ void doapp_destroy(doapp_ctx *ctx) {
   release(ctx->pts); release(ctx->coll); release(ctx->final_coll); release(ctx->keys);
   release(ctx->keys_float); release(ctx->cur_hi); release(ctx->found); release(ctx->grid_cells);
   release(ctx->lookup_coll); release(ctx->lookup_idx); release(ctx->dbg_a); release(ctx->dbg_b);
-  release(ctx->dbg_c); release(ctx->vbad);
+  release(ctx->dbg_c); release(ctx->vbad); release(ctx->usum);
   for (cudaEvent_t e : ctx->prof_events) cudaEventDestroy(e);
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->ev1) cudaEventDestroy(ctx->ev1);

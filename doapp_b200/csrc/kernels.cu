@@ -307,8 +307,13 @@ __global__ void __launch_bounds__(kMaxCostThreads)
   // update kernel every CTA applies the winner's noise while it stages the trajectory, and
   // the climber's first CTA also writes the updated state for the launch after this one.
   uint32_t pend_tg = 0;
-  bool improve = false;
-  if (P.pend_mode != PEND_NONE) {
+  bool improve = false; // block-uniform: the staged trajectory gets swin[] / the winner's noise added
+  const bool weighted = P.pend_mode == PEND_WEIGHTED;
+  if (weighted) {
+    improve = true;
+    if (blockIdx.x == 0 && threadIdx.x == 0) P.found_better[c] = 1;
+    if (blockIdx.x == 0 && P.usum_reset && threadIdx.x < 8) P.usum_reset[(size_t)c * 8 + threadIdx.x] = 0;
+  } else if (P.pend_mode != PEND_NONE) {
     const unsigned long long pk = __ldg(P.pend_keys + c);
     const uint32_t hi = (uint32_t)(pk >> 32);
     pend_tg = (uint32_t)pk;
@@ -325,10 +330,11 @@ __global__ void __launch_bounds__(kMaxCostThreads)
       else if (improve)
         P.found_better[c] = 1;
     }
+    if (blockIdx.x == 0 && P.usum_reset && threadIdx.x < 8) P.usum_reset[(size_t)c * 8 + threadIdx.x] = 0;
   }
   if (blockIdx.x == 0 && P.keys_reset && threadIdx.x == 0) P.keys_reset[c] = kKeyNone;
   const float *pnz = nullptr; // the winner's noise row in the previous launch's external buffer
-  if (improve && P.pend_noise_mode == NOISE_EXTERNAL)
+  if (improve && !weighted && P.pend_noise_mode == NOISE_EXTERNAL)
     pnz = P.pend_noise + ((size_t)c * P.noise_m + (size_t)(pend_tg - P.noise_t0)) * P.n_noise * D;
 
   const float *nz = nullptr;
@@ -356,7 +362,16 @@ __global__ void __launch_bounds__(kMaxCostThreads)
     }
     // the pending winner's noise vector (one d-vector per sample, D16): three lanes of the
     // CTA's last warp redraw its Box-Muller pairs
-    if (improve && P.n_noise == 1 && warp == (blockDim.x >> 5) - 1 && lane < 3) {
+    if (weighted) {
+      // trajectory[w][j] -= gain * u[j] (generate_trajectories.cu:139-140): swin[j] = -(gain*u[j])
+      if (warp == (blockDim.x >> 5) - 1 && lane < D) {
+        const long long sum = P.pend_usum[(size_t)c * 8 + lane];
+        const long long poisoned = P.pend_usum[(size_t)c * 8 + 7];
+        const float u = poisoned ? __int_as_float(0x7fc00000)
+                                 : __double2float_rn(__dmul_rn(__ll2double_rn(sum), 0x1p-28));
+        swin[lane] = -dm::mul_(P.update_gain, u);
+      }
+    } else if (improve && P.n_noise == 1 && warp == (blockDim.x >> 5) - 1 && lane < 3) {
       float a = 0.0f, b = 0.0f;
       if (P.pend_noise_mode == NOISE_PHILOX) {
         dm::noise_pair(P.seed_lo, P.seed_hi, P.sigma, P.pend_iteration, c, pend_tg, 0, lane, &a, &b);
@@ -511,6 +526,65 @@ __global__ void __launch_bounds__(kMaxCostThreads)
         active ? ((unsigned long long)key_hi(P.select_mode, score) << 32) | tg : kKeyNone;
     key = warp_min_u64(key);
     if (lane == 0) atomicMin(P.keys + c, key);
+  }
+}
+
+// ------------------------------------------------------- update-vector kernel
+// compute_update_vector (generate_trajectories.cu:117-133): u[j] = sum over the climber's
+// samples of (best_score / ceilf(score_t)) * noise[t][j].  The reference sums with unordered
+// float atomicAdd; here every term is rounded to a multiple of 2^-28 and summed with 64-bit
+// integer atomics, so the result is independent of the order, the launch geometry and the
+// number of GPUs (oracle: orc_update_sums).  One thread per sample, grid-stride.
+template <int D>
+__global__ void __launch_bounds__(256) update_vector_kernel(const __grid_constant__ UpdateParams P) {
+  __shared__ long long s_part[8][8];
+  const uint32_t c = blockIdx.y;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  // the block's best_score: int(ceilf(.)) minimum over ALL ranks' samples (generate_trajectories.cu:109-111)
+  const float best = (float)(int)(uint32_t)(__ldg(P.keys + c) >> 32);
+  long long acc[D], poisoned = 0;
+#pragma unroll
+  for (int j = 0; j < D; ++j) acc[j] = 0;
+  for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < P.m; t += gridDim.x * blockDim.x) {
+    const float score = __ldg(P.scores + (size_t)c * P.m + t);
+    const float wgt = dm::div_(best, ceilf(score)); // :128-129
+    const uint32_t tg = (uint32_t)(P.sample_offset + t);
+    float eps[D];
+    if (P.noise_mode == NOISE_EXTERNAL) {
+      const float *nz = P.noise + ((size_t)c * P.noise_m + (size_t)(tg - P.noise_t0)) * D;
+#pragma unroll
+      for (int j = 0; j < D; ++j) eps[j] = __ldg(nz + j);
+    } else {
+      dm::noise_vec<D>(P.seed_lo, P.seed_hi, P.sigma, P.iteration, c, tg, 0, eps);
+    }
+#pragma unroll
+    for (int j = 0; j < D; ++j) {
+      const float term = dm::mul_(wgt, eps[j]); // :130-131
+      if (fabsf(term) < kUpdateTermMax)
+        acc[j] += __float2ll_rn(dm::mul_(term, kUpdateScale));
+      else
+        poisoned += 1; // non-finite or huge: the update vector becomes NaN
+    }
+  }
+  auto wsum = [&](long long v) {
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) v += __shfl_xor_sync(kFull, v, off);
+    return v;
+  };
+#pragma unroll
+  for (int j = 0; j < D; ++j) {
+    const long long v = wsum(acc[j]);
+    if (lane == 0) s_part[warp][j] = v;
+  }
+  {
+    const long long v = wsum(poisoned);
+    if (lane == 0) s_part[warp][7] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < 8 && (threadIdx.x < D || threadIdx.x == 7)) {
+    long long v = 0;
+    for (uint32_t q = 0; q < (blockDim.x >> 5); ++q) v += s_part[q][threadIdx.x];
+    if (v) atomicAdd((unsigned long long *)(P.usum + (size_t)c * 8 + threadIdx.x), (unsigned long long)v);
   }
 }
 
@@ -747,6 +821,19 @@ cudaError_t launch_cost(const CostParams &p_in, int d, int sm_count, cudaStream_
 cudaError_t launch_verify_div(dm::FastDiv d, uint32_t lo_bits, uint32_t hi_bits, int mode,
                               unsigned long long *bad, int sm_count, cudaStream_t st) {
   verify_div_kernel<<<sm_count * 8, 256, 0, st>>>(d, lo_bits, hi_bits, mode, bad);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_update_vector(const UpdateParams &p, int sm_count, cudaStream_t st) {
+  if (p.k == 0 || p.m == 0) return cudaSuccess;
+  unsigned bx = blocks_for(p.m, 256);
+  const unsigned cap = (unsigned)((sm_count * 8 + p.k - 1) / p.k);
+  if (bx > cap) bx = cap > 0 ? cap : 1;
+  const dim3 grid(bx, p.k);
+  if (p.d == 5)
+    update_vector_kernel<5><<<grid, 256, 0, st>>>(p);
+  else
+    update_vector_kernel<4><<<grid, 256, 0, st>>>(p);
   return cudaGetLastError();
 }
 

@@ -15,7 +15,12 @@ constexpr uint64_t kKeyNone = 0xFFFFFFFFFFFFFFFFull;
 enum NoiseMode : int { NOISE_ZERO = 0, NOISE_EXTERNAL = 1, NOISE_PHILOX = 2 };
 // PEND_SEED: the previous launch scored the unperturbed trajectories, its key seeds cur_hi
 // (generate_trajectories.cu:180-191); PEND_KEEP_BEST: the winner replaces the trajectory if better
-enum PendMode : int { PEND_NONE = 0, PEND_KEEP_BEST = 1, PEND_SEED = 2 };
+// PEND_WEIGHTED: the weighted update vector of the previous iteration (update_vector_kernel) is
+// subtracted from the trajectory (generate_trajectories.cu:117-142,242-251)
+enum PendMode : int { PEND_NONE = 0, PEND_KEEP_BEST = 1, PEND_SEED = 2, PEND_WEIGHTED = 3 };
+// fixed-point scale of the order-independent update-vector sums (2^28) and the largest term
+constexpr float kUpdateScale = 268435456.0f;
+constexpr float kUpdateTermMax = 4096.0f;
 
 // Device view of the voxel grid (dense, index ix + nx*iy + nx*ny*iz).
 struct GridDev {
@@ -69,6 +74,11 @@ struct CostParams {
   uint8_t *found_better;                // [k]
   float *traj_next;                     // [k][d][npad] or nullptr
   unsigned long long *keys_reset;       // [k] key buffer to re-arm for a later launch, or nullptr
+  // PEND_WEIGHTED: integer sums [k][8] left by update_vector_kernel (slot 7 = poisoned terms),
+  // the gain of generate_trajectories.cu:140, and the sum buffer to zero for the next one
+  const long long *pend_usum;
+  long long *usum_reset;
+  float update_gain;
   // launch geometry (filled by launch_cost): 2^parts_log2 threads per sample, each owning
   // wpp consecutive waypoints; 2^pw_log2 of them per CTA, the rest across a cluster
   uint32_t parts_log2, pw_log2, wpp;
@@ -85,6 +95,19 @@ struct FinalParams {
   float *out;
 };
 
+// compute_update_vector (generate_trajectories.cu:117-133) for every climber of this shard
+struct UpdateParams {
+  const float *scores;           // [k][m] of the cost launch just run
+  const unsigned long long *keys; // [k] CEIL_INT keys of that launch (hi = the block's best_score)
+  const float *noise;            // external [k][noise_m][1][d] or nullptr (Philox)
+  uint64_t noise_m, noise_t0;
+  int noise_mode;
+  uint32_t k, m, d, iteration, seed_lo, seed_hi;
+  float sigma;
+  uint64_t sample_offset;
+  long long *usum; // [k][8] accumulated with integer atomics
+};
+
 struct ScatterParams {
   const float *xyz;
   uint64_t num_points;
@@ -96,6 +119,7 @@ struct ScatterParams {
 cudaError_t launch_cost(const CostParams &p, int d, int sm_count, cudaStream_t st);
 cudaError_t launch_verify_div(dm::FastDiv d, uint32_t lo_bits, uint32_t hi_bits, int mode,
                               unsigned long long *bad, int sm_count, cudaStream_t st);
+cudaError_t launch_update_vector(const UpdateParams &p, int sm_count, cudaStream_t st);
 cudaError_t launch_final(const FinalParams &p, cudaStream_t st);
 cudaError_t launch_scatter(const ScatterParams &p, int sm_count, cudaStream_t st);
 cudaError_t launch_lookup(const GridDev &g, const float *xyz, uint64_t count, float coll_dist,

@@ -32,7 +32,8 @@ class Params(C.Structure):
                 ("collision_distance", C.c_float), ("collision_mode", C.c_int32),
                 ("select_mode", C.c_int32), ("sum_order", C.c_int32), ("limit_weight", C.c_float),
                 ("limit_min", C.c_void_p), ("limit_max", C.c_void_p), ("sigma", C.c_float),
-                ("seed", C.c_uint64), ("sample_offset", C.c_uint64), ("m_global", C.c_uint64)]
+                ("seed", C.c_uint64), ("sample_offset", C.c_uint64), ("m_global", C.c_uint64),
+                ("update_mode", C.c_int32), ("update_gain", C.c_float)]
 
 
 def _digest() -> str:
@@ -90,6 +91,10 @@ def lib() -> C.CDLL:
         L.orc_plan.argtypes = [C.POINTER(Params), C.POINTER(Grid), C.c_void_p, C.c_void_p,
                                C.c_uint32] + [C.c_void_p] * 9 + [C.c_int]
         L.orc_update_vector.argtypes = [C.POINTER(Params)] + [C.c_void_p] * 3
+        L.orc_update_sums.argtypes = [C.POINTER(Params), C.c_int32, C.c_void_p, C.c_void_p,
+                                      C.c_uint32, C.c_void_p]
+        L.orc_update_from_sum.argtypes = [C.c_int64, C.c_int64]
+        L.orc_update_from_sum.restype = C.c_float
         L.orc_build_message.argtypes = [C.c_void_p] * 4 + [C.c_uint32, C.c_uint32, C.c_float] + \
             [C.c_void_p] * 3
         _lib = L
@@ -214,6 +219,15 @@ class Oracle:
         out = np.empty((self.p.k, self.p.d), np.float32)
         lib().orc_update_vector(C.byref(self.p), _p(scores), _p(noise), _p(out))
         return out
+
+
+def update_sums(p_obj, best_rounded, scores, noise):
+    """Order-independent integer sums of gt.cu:117-133 for one climber (sums[7] = poisoned)."""
+    scores, noise = _f32(scores), _f32(noise)
+    sums = np.zeros(8, np.int64)
+    lib().orc_update_sums(C.byref(p_obj.p), int(best_rounded), _p(scores), _p(noise),
+                          scores.shape[0], _p(sums))
+    return sums
 
 
 def sincos(x):

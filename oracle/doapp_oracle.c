@@ -27,6 +27,8 @@ void orc_params_init(orc_params *p) {
   p->sum_order = ORC_SUM_WAYPOINT;
   p->sigma = 1.0f;
   p->seed = 1234; /* gt.cu:23 */
+  p->update_mode = ORC_UPDATE_KEEP_BEST;
+  p->update_gain = 10000.0f; /* gt.cu:140 */
 }
 
 /* ------------------------------------------------------------------------
@@ -598,6 +600,33 @@ void orc_plan(const orc_params *p, const orc_grid *g, const float *start, const 
   for (uint32_t it = 0; it < iters; ++it) {
     const float *nz_it = noise ? noise + (size_t)it * k * mg * nnd : NULL;
     orc_eval_all(p, g, traj, start, nz_it, (size_t)mg, 0, it, scores, NULL, num_threads);
+    if (p->update_mode == ORC_UPDATE_WEIGHTED) {
+      /* gt.cu:242-251 (commented out in the reference): u = sum_t (best/ceil(score_t)) noise_t,
+       * traj[w][j] -= gain * u[j]; n_noise == 1 */
+      float *nzc = nz_it ? NULL : (float *)malloc(sizeof(float) * (size_t)m * d);
+      for (uint32_t c = 0; c < k; ++c) {
+        int32_t best = INT_MAX;
+        for (uint32_t t = 0; t < m; ++t) {
+          int32_t r = orc_round_score(scores[(size_t)c * m + t]);
+          if (r < best) best = r;
+        }
+        const float *nz = nz_it ? nz_it + ((size_t)c * mg + p->sample_offset) * d : nzc;
+        if (!nz_it)
+          for (uint32_t t = 0; t < m; ++t)
+            for (uint32_t j = 0; j < d; ++j)
+              nzc[(size_t)t * d + j] = orc_noise_at(p, it, c, p->sample_offset + t, 0, j);
+        int64_t sums[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        orc_update_sums(p, best, scores + (size_t)c * m, nz, m, sums);
+        for (uint32_t j = 0; j < d; ++j) {
+          float delta = p->update_gain * orc_update_from_sum(sums[j], sums[7]);
+          for (uint32_t w = 0; w < n; ++w)
+            traj[c * nd + (size_t)w * d + j] = traj[c * nd + (size_t)w * d + j] - delta;
+        }
+        fb[c] = 1;
+      }
+      free(nzc);
+      continue;
+    }
     for (uint32_t c = 0; c < k; ++c) {
       /* gt.cu:109-111 atomicMin over the block, then :225-241 keep-best with
        * the lowest sample index winning ties */
@@ -674,6 +703,28 @@ void orc_update_vector(const orc_params *p, const float *scores, const float *no
         float term = wgt * noise[((size_t)c * p->m + t) * p->d + j];
         update[(size_t)c * p->d + j] = update[(size_t)c * p->d + j] + term;
       }
+}
+
+void orc_update_sums(const orc_params *p, int32_t best_rounded, const float *scores,
+                     const float *noise, uint32_t count, int64_t sums[8]) {
+  /* gt.cu:128-132: weight = best_score / ceilf(our_score); term = weight * noise */
+  const float best = (float)best_rounded;
+  for (uint32_t t = 0; t < count; ++t) {
+    float wgt = best / ceilf(scores[t]);
+    for (uint32_t j = 0; j < p->d; ++j) {
+      float term = wgt * noise[(size_t)t * p->d + j];
+      if (!(fabsf(term) < 4096.0f)) {
+        sums[7] += 1;
+        continue;
+      }
+      sums[j] += (int64_t)llrintf(term * 268435456.0f); /* exact scaling by 2^28, RN-even */
+    }
+  }
+}
+
+float orc_update_from_sum(int64_t sum, int64_t poisoned) {
+  if (poisoned) return NAN;
+  return (float)((double)sum * 0x1p-28);
 }
 
 void orc_build_message(const float *cur, const float *goal, const float *traj, const float *vel,

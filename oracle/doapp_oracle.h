@@ -33,6 +33,8 @@ extern "C" {
 
 enum { ORC_COLLISION_AS_SHIPPED = 0, ORC_COLLISION_INTENDED = 1 };
 enum { ORC_SELECT_CEIL_INT = 0, ORC_SELECT_FLOAT = 1 };
+/* KEEP_BEST = the live path gt.cu:225-241; WEIGHTED = the commented-out update gt.cu:117-142,242-251 */
+enum { ORC_UPDATE_KEEP_BEST = 0, ORC_UPDATE_WEIGHTED = 1 };
 enum { ORC_GRID_NONE = 0, ORC_GRID_U8 = 1, ORC_GRID_F32 = 2 };
 enum { ORC_FRAME_CDG = 0, ORC_FRAME_OG = 1 };
 /* order of the sum over waypoints of the per-waypoint sum of acc^2:
@@ -63,6 +65,8 @@ typedef struct orc_params {
   float sigma;
   uint64_t seed;
   uint64_t sample_offset, m_global;
+  int32_t update_mode; /* ORC_UPDATE_* */
+  float update_gain;   /* 10000.0f, gt.cu:140 */
 } orc_params;
 
 void orc_params_init(orc_params *p);
@@ -121,6 +125,19 @@ void orc_plan(const orc_params *p, const orc_grid *g, const float *start, const 
 /* gt.cu:117-142 / gt.test.cu:200-208: u[c][j] = sum_t (best/ceil(score_t)) * noise[t][j] */
 void orc_update_vector(const orc_params *p, const float *scores, const float *noise,
                        float *update /*[k][d]*/);
+
+/* gt.cu:117-133 for ONE climber with an order-independent sum (the reference's float
+ * atomicAdd order is arbitrary): every term weight*noise is rounded to a
+ * multiple of 2^-28 and the terms are summed as 64-bit integers, so the result does not
+ * depend on the order, the launch geometry or the number of GPUs.
+ *   best_rounded  the block's atomicMin of int(ceilf(score))          (gt.cu:109-111)
+ *   scores [m], noise [m][d] (n_noise == 1)
+ *   sums[j] += round_to_even(term * 2^28);  sums[7] counts terms that are not finite or
+ *   >= 4096 in magnitude ("poisoned": the update vector becomes NaN). */
+void orc_update_sums(const orc_params *p, int32_t best_rounded, const float *scores,
+                     const float *noise, uint32_t count, int64_t sums[8]);
+/* u[j] from the integer sums; NaN if poisoned */
+float orc_update_from_sum(int64_t sum, int64_t poisoned);
 
 /* ps.cu:179-209 (D11 fixed): (n+2) points of positions/velocities [n+2][d], times [n+2] */
 void orc_build_message(const float *cur, const float *goal, const float *traj, const float *vel,
