@@ -75,7 +75,19 @@ struct FastDiv {
   float b, r;
   float lo, hi; // |a| in [lo, hi) (or a == 0) takes the fast path; lo = +inf disables it
 };
-constexpr float kFastDivLo = 0x1p-60f, kFastDivHi = 0x1p+60f;
+constexpr float kFastDivLo = 0x1p-98f, kFastDivHi = 0x1p+60f;
+// The kernels do not test the 10 dividends of a waypoint but its 5 joint angles: if every
+// angle x of three consecutive waypoints is 0 or kFineLo <= |x| < kFineHi, and the divisor dt
+// lies in [kFastDtLo, kFastDtHi], then x - xprev is 0 or a multiple of 2^-59 below 2^18, the
+// velocity v is 0 or >= 2^-59/dt, and v - vprev is 0 or a multiple of ulp(2^-59/dt) >=
+// 2^-84/dt >= 2^-94: all inside [kFastDivLo, kFastDivHi).  kFineHi is also the range of
+// sincos_small.
+constexpr float kFineLo = 0x1p-36f, kFineHi = 0x1p+17f;
+constexpr float kFastDtLo = 0x1p-20f, kFastDtHi = 0x1p+10f;
+DM_HD bool fine_angle(float x) {
+  const float a = fabsf(x);
+  return (a == 0.0f) | ((a >= kFineLo) & (a < kFineHi));
+}
 
 DM_HD float div_fast_unguarded(float a, FastDiv d) {
   float q0 = mul_(a, d.r);

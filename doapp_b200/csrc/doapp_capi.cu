@@ -105,6 +105,7 @@ struct doapp_ctx {
   int use_limits = 0;
   float rpy_s = 0.0f, rpy_c = 0.0f;
   dm::FastDiv dt_div{};            // verified at create (verify_fast_div)
+  bool dt_fast_ok = false;         // ... and delta_t inside [kFastDtLo, kFastDtHi]
   DevBuf<unsigned long long> vbad; // mismatch counter of the verification kernels
   bool fast_math_ok = true;        // DOAPP_EXACT_DIV=1 forces the IEEE divides
 
@@ -244,6 +245,7 @@ CostParams base_cost_params(doapp_ctx *ctx) {
   p.rpy_c = ctx->rpy_c;
   p.grid = ctx->grid;
   p.dt_div = ctx->dt_div;
+  p.fast_ok = ctx->dt_fast_ok ? 1 : 0;
   return p;
 }
 
@@ -621,7 +623,9 @@ doapp_status doapp_create(const doapp_config *cfg, doapp_ctx **out) {
     // velocity / acceleration divides: reciprocal-multiply path, proven against the IEEE
     // divide for EVERY dividend in [2^-60, 2^60) for this delta_t, else disabled
     bool ok = false;
-    ST(verify_fast_div(ctx, cfg->delta_t, f2u(dm::kFastDivLo), f2u(dm::kFastDivHi) - 1, 0, &ok));
+    if (cfg->delta_t >= dm::kFastDtLo && cfg->delta_t <= dm::kFastDtHi)
+      ST(verify_fast_div(ctx, cfg->delta_t, f2u(dm::kFastDivLo), f2u(dm::kFastDivHi) - 1, 0, &ok));
+    ctx->dt_fast_ok = ok;
     volatile float rcp = 1.0f / cfg->delta_t;
     ctx->dt_div = dm::FastDiv{cfg->delta_t, rcp, ok ? dm::kFastDivLo : INFINITY,
                               ok ? dm::kFastDivHi : INFINITY};
@@ -709,6 +713,31 @@ doapp_status doapp_grid_alloc(doapp_ctx *ctx, int32_t kind, int32_t frame, uint3
     bool ok = false;
     if (frame == DOAPP_FRAME_CDG && top < dm::kFastDivHi)
       ST(verify_fast_div(ctx, g.res, 0u, f2u(top), 1, &ok));
+    // One unsigned compare per axis replaces (lo <= c) & (c < hi) & (index < n): the threshold
+    // is the smallest dividend a >= 0 with trunc(a / res) >= n (the index is monotone in a).  It
+    // is equivalent to the float bounds + index test of cpu_distance_grid.cu:115-122 provided the
+    // upper float bound is implied by the index test, i.e. the dividend of c == hi already
+    // reaches n; otherwise the grid runs the generic kernel.
+    auto threshold = [&](uint32_t n, float top_dividend, uint32_t *bits) -> bool {
+      auto idx = [&](uint32_t b) -> double {
+        float a;
+        memcpy(&a, &b, 4);
+        volatile float q = a / g.res; // IEEE RN, as __fdiv_rn
+        return std::trunc((double)q);
+      };
+      if (!(idx(f2u(top_dividend)) >= (double)n)) return false;
+      uint32_t lo = 0, hi = f2u(top_dividend); // idx(lo) < n <= idx(hi)
+      if (idx(0) >= (double)n) return false;
+      while (hi - lo > 1) {
+        uint32_t mid = lo + (hi - lo) / 2;
+        if (idx(mid) >= (double)n) hi = mid; else lo = mid;
+      }
+      *bits = hi;
+      return true;
+    };
+    if (ok)
+      ok = threshold(nx, 2.0f * g.x_off, &g.tx_bits) && threshold(ny, 2.0f * g.y_off, &g.ty_bits) &&
+           threshold(nz, g.z_max, &g.tz_bits) && g.res <= 1.0f;
     g.fast_idx = ok ? 1 : 0;
   }
   ctx->grid = g;

@@ -91,16 +91,16 @@ __device__ __forceinline__ P3 rot_z(float s, float c, P3 q) {
   return u;
 }
 
-// FAST: straight-line small-argument sin/cos (dm::sincos_small); *ok is cleared when an angle
-// is outside its range and the caller must redo the waypoint through the general path.
+// FAST: straight-line small-argument sin/cos (dm::sincos_small), valid for |angle| < 2^17:
+// the caller has checked the angles (dm::fine_angle) or redoes the waypoint through the
+// general path.
 template <int D, bool FAST>
 __device__ __forceinline__ void fk_points(const float (&th)[D], float rpy_s, float rpy_c,
-                                          P3 (&out)[5], bool *ok) {
+                                          P3 (&out)[5]) {
   float s, c;
   P3 p, q;
   auto sc = [&](float a) {
     if (FAST) {
-      *ok = *ok & (fabsf(a) < 131072.0f);
       dm::sincos_small(a, &s, &c);
     } else {
       dm::sincos(a, &s, &c);
@@ -174,50 +174,59 @@ __device__ __forceinline__ int collides(const CostParams &P, P3 p) {
   if (GM == GM_NONE) return 0;
   if (GM == GM_GENERIC) return grid_collides(P.grid, p.x, p.y, p.z, P.coll_dist);
   const GridDev &g = P.grid;
-  // cpu_distance_grid.cu:115-117 (half-open), branch-free
+  const float ax = dm::add_(p.x, g.x_off), ay = dm::add_(p.y, g.y_off);
+  if (FIDX) {
+    // cpu_distance_grid.cu:115-122 with half-open bounds.  Inside iff the bit
+    // patterns of x + x_off, y + y_off, z + 0 are below the per-axis thresholds as unsigned
+    // integers (GridDev::tx_bits): a negative sum or NaN has the top bits set, +0 absorbs
+    // z == -0, and the threshold is the smallest dividend whose voxel index reaches n.
+    const float az = dm::add_(p.z, 0.0f);
+    const bool in = (__float_as_uint(ax) < g.tx_bits) & (__float_as_uint(ay) < g.ty_bits) &
+                    (__float_as_uint(az) < g.tz_bits);
+    // :120-122, IEEE quotients through the verified reciprocal path
+    const uint32_t ix = __float2uint_rz(dm::div_fast_unguarded(ax, P.res_div));
+    const uint32_t iy = __float2uint_rz(dm::div_fast_unguarded(ay, P.res_div));
+    const uint32_t iz = __float2uint_rz(dm::div_fast_unguarded(az, P.res_div));
+    const uint32_t lin = (iz * g.ny + iy) * g.nx + ix; // < 2^32 cells (grid_alloc)
+    int hit = 0;
+    if (GM == GM_U8_CDG) {
+      if (in) hit = __ldg((const uint8_t *)g.cells + lin) != 0;
+    } else {
+      if (in) hit = __ldg((const float *)g.cells + lin) <= P.coll_dist; // generate_trajectories.cu:412
+    }
+    return hit;
+  }
   bool in = (p.x >= -g.x_off) & (p.x < g.x_off) & (p.y >= -g.y_off) & (p.y < g.y_off) &
             (p.z >= 0.0f) & (p.z < g.z_max);
-  const float ax = dm::add_(p.x, g.x_off), ay = dm::add_(p.y, g.y_off);
-  float fx, fy, fz; // :120-122, IEEE quotients (verified-exact fast path when FIDX)
-  if (FIDX) {
-    fx = dm::div_fast_unguarded(ax, P.res_div);
-    fy = dm::div_fast_unguarded(ay, P.res_div);
-    fz = dm::div_fast_unguarded(p.z, P.res_div);
-  } else {
-    fx = dm::div_(ax, g.res);
-    fy = dm::div_(ay, g.res);
-    fz = dm::div_(p.z, g.res);
-  }
+  const float fx = dm::div_(ax, g.res), fy = dm::div_(ay, g.res), fz = dm::div_(p.z, g.res);
   const uint32_t ix = __float2uint_rz(fx), iy = __float2uint_rz(fy), iz = __float2uint_rz(fz);
   in = in & (ix < g.nx) & (iy < g.ny) & (iz < g.nz);
-  const uint32_t lin = in ? (iz * g.ny + iy) * g.nx + ix : 0u; // < 2^32 cells (grid_alloc)
+  const uint32_t lin = in ? (iz * g.ny + iy) * g.nx + ix : 0u;
   if (GM == GM_U8_CDG) return in & (__ldg((const uint8_t *)g.cells + lin) != 0);
-  return in & (__ldg((const float *)g.cells + lin) <= P.coll_dist); // generate_trajectories.cu:412
+  return in & (__ldg((const float *)g.cells + lin) <= P.coll_dist);
 }
 
 // One waypoint of one sample: derivatives, smoothness / limit terms and the collision count
 // (generate_trajectories.cu:86-103,276-291,391-466).  FAST = straight-line code: reciprocal
-// divides and small-argument sin/cos computed unconditionally, one flag says whether every
-// operand was inside the verified ranges; the caller redoes the waypoint with FAST = false
-// (IEEE divides, full-range sin/cos) in the rare case it was not.  Both produce the same bits
+// divides and small-argument sin/cos computed unconditionally.  The return value says whether
+// the waypoint's joint angles are "fine" (dm::fine_angle): the FAST results are valid when
+// this and the two previous waypoints are (device_math.cuh), otherwise the caller redoes the
+// waypoint with FAST = false (IEEE divides, full-range sin/cos).  Both produce the same bits
 // wherever FAST is valid.  vnew = this waypoint's velocities (the caller commits them).
 template <int D, int GM, bool FIDX, bool LIM, bool FAST>
 __device__ __forceinline__ bool waypoint_cost(const CostParams &P, const float (&x)[D],
                                               const float (&xprev)[D], const float (&vprev)[D],
                                               float (&vnew)[D], float *a2_out, float *l2_out,
                                               int *coll_out) {
-  bool ok = true;
+  bool fine = true;
   float a2 = 0.0f, l2 = 0.0f;
   auto dv = [&](float a) -> float {
-    if (FAST) {
-      const float aa = fabsf(a);
-      ok = ok & ((aa == 0.0f) | ((aa >= P.dt_div.lo) & (aa < P.dt_div.hi)));
-      return dm::div_fast_unguarded(a, P.dt_div);
-    }
+    if (FAST) return dm::div_fast_unguarded(a, P.dt_div);
     return dm::div_(a, P.dt_div.b);
   };
 #pragma unroll
   for (int j = 0; j < D; ++j) {
+    if (FAST) fine = fine & dm::fine_angle(x[j]);
     const float v = dv(dm::sub_(x[j], xprev[j])); // :288
     const float a = dv(dm::sub_(v, vprev[j]));
     a2 = dm::add_(a2, dm::mul_(a, a)); // :76
@@ -231,14 +240,14 @@ __device__ __forceinline__ bool waypoint_cost(const CostParams &P, const float (
   int cnt = 0;
   if (GM != GM_NONE) {
     P3 pts[5];
-    fk_points<D, FAST>(x, P.rpy_s, P.rpy_c, pts, &ok);
+    fk_points<D, FAST>(x, P.rpy_s, P.rpy_c, pts);
 #pragma unroll
-    for (int l = 0; l < 5; ++l) cnt += collides<GM, FIDX>(P, pts[l]);
+    for (int l = 0; l < 5; ++l) cnt += collides<GM, FIDX && FAST>(P, pts[l]);
   }
   *a2_out = a2;
   *l2_out = l2;
   *coll_out = cnt;
-  return ok;
+  return fine;
 }
 
 // by-value interface of the out-of-line general path: keeps the hot loop's arrays in registers
@@ -430,11 +439,17 @@ __global__ void __launch_bounds__(kMaxCostThreads)
   w_end = w_end < P.n ? w_end : P.n;
 
   // priors of the first owned waypoint: the initial waypoint for BOTH derivative
-  // passes at w = 0 (generate_trajectories.cu:285), else recomputed
+  // passes at w = 0 (generate_trajectories.cu:285), else recomputed.
+  // fine1 / fine2: were the angles of the previous two waypoints "fine" (dm::fine_angle)?
+  // The straight-line results of a waypoint are used only if it and both predecessors are.
   float xprev[D], vprev[D];
+  bool fine1 = P.fast_ok != 0, fine2 = fine1;
   if (w == 0) {
 #pragma unroll
-    for (int j = 0; j < D; ++j) xprev[j] = vprev[j] = start[j];
+    for (int j = 0; j < D; ++j) {
+      xprev[j] = vprev[j] = start[j];
+      fine1 = fine1 & dm::fine_angle(start[j]);
+    }
   } else if (w < P.n) {
 #pragma unroll
     for (int j = 0; j < D; ++j) {
@@ -442,6 +457,8 @@ __global__ void __launch_bounds__(kMaxCostThreads)
       const float x2 = w >= 2 ? noisy(w - 2, j) : start[j];
       xprev[j] = x1;
       vprev[j] = dm::div_fast(dm::sub_(x1, x2), P.dt_div);
+      fine1 = fine1 & dm::fine_angle(x1);
+      fine2 = fine2 & dm::fine_angle(x2);
     }
   }
 
@@ -464,8 +481,12 @@ __global__ void __launch_bounds__(kMaxCostThreads)
     for (int j = 0; j < D; ++j) x[j] = noisy(w, j);
     float a2, l2;
     int cw;
-    if (!waypoint_cost<D, GM, FIDX, LIM, true>(P, x, xprev, vprev, vnew, &a2, &l2, &cw)) {
-      WpIn<D> in; // rare: an operand outside the verified ranges -> IEEE divides, full sin/cos
+    const bool fine0 = waypoint_cost<D, GM, FIDX, LIM, true>(P, x, xprev, vprev, vnew, &a2, &l2, &cw);
+    const bool fast_valid = fine0 & fine1 & fine2;
+    fine2 = fine1;
+    fine1 = fine0 & (P.fast_ok != 0);
+    if (!fast_valid) {
+      WpIn<D> in; // rare: an angle outside the verified ranges -> IEEE divides, full sin/cos
 #pragma unroll
       for (int j = 0; j < D; ++j) {
         in.x[j] = x[j];
@@ -690,8 +711,7 @@ __global__ void debug_fk_kernel(const float *wp, uint64_t count, float rpy_s, fl
 #pragma unroll
   for (int j = 0; j < D; ++j) th[j] = wp[i * D + j];
   P3 pts[5];
-  bool ok = true;
-  fk_points<D, false>(th, rpy_s, rpy_c, pts, &ok);
+  fk_points<D, false>(th, rpy_s, rpy_c, pts);
   for (int l = 0; l < 5; ++l) {
     out[(i * 5 + l) * 3 + 0] = pts[l].x;
     out[(i * 5 + l) * 3 + 1] = pts[l].y;

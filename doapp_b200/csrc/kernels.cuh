@@ -36,6 +36,12 @@ struct GridDev {
   // every dividend this frame can produce (doapp_capi.cu: verify_fast_index)
   int fast_idx;
   float res_rcp;
+  // fast_idx only: a point is inside iff, per axis, the BIT PATTERN of x + x_off (y + y_off,
+  // z + 0) is below these thresholds as an unsigned integer: negative sums and NaN have the
+  // top bits set, and the threshold is the smallest dividend whose voxel index reaches n, so
+  // one compare replaces the two float bounds tests and the index test (doapp_grid_alloc
+  // establishes and checks the equivalence)
+  uint32_t tx_bits, ty_bits, tz_bits;
 };
 
 struct CostParams {
@@ -61,6 +67,7 @@ struct CostParams {
   unsigned long long *keys;      // [k] packed argmin keys for the update rule, or nullptr
   unsigned long long *keys_float; // [k] packed (float bits, t) keys for the host-style argmin
   dm::FastDiv dt_div, res_div; // divisor + RN(1/divisor)
+  int fast_ok; // 1: the reciprocal dt divide was verified and dt is in [kFastDtLo, kFastDtHi]
   // pending keep-best of the previous launch, applied by this one while it stages the
   // trajectory (see cost_kernel): winner key per climber, the noise that launch drew, the
   // climber's current rounded score in / out, and the other trajectory buffer to write
