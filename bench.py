@@ -37,6 +37,9 @@ WORKLOADS = {
                grid_n=128, res=0.01, n=64, m=1024, iters=100, sigma=0.05, fill=0.0),
     "c4": dict(desc="C4: 128 waypoints x 131072 samples/GPU, 128^3 u8 grid, 4 iterations per step",
                grid_n=128, res=0.01, n=128, m=131072, iters=4, sigma=0.05, fill=0.0),
+    "c4m": dict(desc="C4 (whole 1M-sample config on each GPU): 128 waypoints x 1048576 samples/GPU, "
+                     "128^3 u8 grid, 2 iterations per step",
+                grid_n=128, res=0.01, n=128, m=1048576, iters=2, sigma=0.05, fill=0.0),
     "c5": dict(desc="C5: 512^3 u8 grid (128 MiB, L2-spill), 128 waypoints x 16384 samples/GPU, "
                     "4 iterations per step",
                grid_n=512, res=0.0025, n=128, m=16384, iters=4, sigma=0.5, fill=0.05),

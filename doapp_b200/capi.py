@@ -64,7 +64,7 @@ def load_library(path: str | None = None) -> C.CDLL:
     global _lib
     if _lib is not None and path is None:
         return _lib
-    p = path or LIB_PATH
+    p = path or os.environ.get("DOAPP_LIB") or LIB_PATH  # DOAPP_LIB: tuning builds only
     if not os.path.exists(p):
         raise FileNotFoundError(
             f"{p} not found: build it with `python -m doapp_b200.build` (no CPU fallback exists)")

@@ -195,6 +195,104 @@ DM_HD void sincos(float x, float *s, float *c) {
   }
 }
 
+#if defined(__CUDACC__)
+// ---------------------------------------------------------------------------
+// Packed fp32x2 arithmetic (sm_100a FFMA2 / FADD2 / FMUL2): one issue slot carries the same
+// operation for two samples.  Every operation is an IEEE round-to-nearest fma per half, so
+// the results equal the scalar helpers above bit for bit.  add / mul are written as
+// fma(a, 1, b) / fma(a, b, -0) (exact identities, ptxas emits FADD2 / FMUL2).
+//
+// HAZARD: ptxas contracts a packed multiply followed by a packed add of its result into one
+// FFMA2 even under --fmad=false (observed with CUDA 12.9).  Wherever the specification
+// rounds the product before the addition (acc*acc summed, t = x*(2/pi) then t + magic), the
+// product must therefore be formed with the scalar __fmul_rn per half (f2_mul_rounded), never
+// with f2_mul.
+struct f2 {
+  unsigned long long v;
+};
+__device__ __forceinline__ f2 f2_pack(float lo, float hi) {
+  f2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r.v) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void f2_unpack(f2 a, float *lo, float *hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(*lo), "=f"(*hi) : "l"(a.v));
+}
+__device__ __forceinline__ float f2_lo(f2 a) {
+  float lo, hi;
+  f2_unpack(a, &lo, &hi);
+  return lo;
+}
+__device__ __forceinline__ float f2_hi(f2 a) {
+  float lo, hi;
+  f2_unpack(a, &lo, &hi);
+  return hi;
+}
+__device__ __forceinline__ f2 f2_splat(float c) { return f2_pack(c, c); }
+__device__ __forceinline__ f2 f2_fma(f2 a, f2 b, f2 c) {
+  f2 r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r.v) : "l"(a.v), "l"(b.v), "l"(c.v));
+  return r;
+}
+__device__ __forceinline__ f2 f2_neg(f2 a) { // folds into an operand modifier
+  float lo, hi;
+  f2_unpack(a, &lo, &hi);
+  return f2_pack(-lo, -hi);
+}
+__device__ __forceinline__ f2 f2_add(f2 a, f2 b) { return f2_fma(a, f2_splat(1.0f), b); }
+__device__ __forceinline__ f2 f2_sub(f2 a, f2 b) { return f2_fma(b, f2_splat(-1.0f), a); }
+// product consumed as an fma operand or converted, never by an add/sub (see HAZARD)
+__device__ __forceinline__ f2 f2_mul(f2 a, f2 b) { return f2_fma(a, b, f2_splat(-0.0f)); }
+// product that the specification rounds before adding it to something
+__device__ __forceinline__ f2 f2_mul_rounded(f2 a, f2 b) {
+  float al, ah, bl, bh;
+  f2_unpack(a, &al, &ah);
+  f2_unpack(b, &bl, &bh);
+  return f2_pack(__fmul_rn(al, bl), __fmul_rn(ah, bh));
+}
+__device__ __forceinline__ f2 f2_div_fast_unguarded(f2 a, FastDiv d) {
+  const f2 r = f2_splat(d.r);
+  f2 q0 = f2_mul(a, r);
+  f2 e = f2_fma(f2_splat(-d.b), q0, a);
+  return f2_fma(e, r, q0);
+}
+// sincos_small on two angles; quadrant fix-up per half as in sincos_core
+__device__ __forceinline__ void f2_sincos_small(f2 x, f2 *s, f2 *c) {
+  const float kMagic = 12582912.0f;
+  f2 t = f2_mul_rounded(x, f2_splat(kTwoOverPi));
+  f2 tm = f2_add(t, f2_splat(kMagic));
+  f2 kf = f2_add(tm, f2_splat(-kMagic));
+  f2 r = f2_fma(kf, f2_splat(-kP1), x); // fma(-kf, P, x) == fma(kf, -P, x)
+  r = f2_fma(kf, f2_splat(-kP2), r);
+  r = f2_fma(kf, f2_splat(-kP3), r);
+  f2 z = f2_mul(r, r);
+  f2 ps = f2_fma(f2_splat(kS3), z, f2_splat(kS2));
+  ps = f2_fma(ps, z, f2_splat(kS1));
+  ps = f2_mul(ps, z);
+  f2 sin_r = f2_fma(ps, r, r);
+  f2 pc = f2_fma(f2_splat(kC3), z, f2_splat(kC2));
+  pc = f2_fma(pc, z, f2_splat(kC1));
+  pc = f2_fma(pc, z, f2_splat(-0.5f));
+  f2 cos_r = f2_fma(pc, z, f2_splat(1.0f));
+  float sl, sh, cl, ch, tl, th;
+  f2_unpack(sin_r, &sl, &sh);
+  f2_unpack(cos_r, &cl, &ch);
+  f2_unpack(tm, &tl, &th);
+  auto fix = [](float sin_v, float cos_v, uint32_t q, float *so, float *co) {
+    const bool swap = (q & 1u) != 0;
+    const float sa = swap ? cos_v : sin_v, ca = swap ? sin_v : cos_v;
+    const uint32_t qs = q << 30;
+    *so = __uint_as_float(__float_as_uint(sa) ^ (qs & 0x80000000u));
+    *co = __uint_as_float(__float_as_uint(ca) ^ ((qs + 0x40000000u) & 0x80000000u));
+  };
+  float s0, s1, c0, c1;
+  fix(sl, cl, __float_as_uint(tl) & 3u, &s0, &c0);
+  fix(sh, ch, __float_as_uint(th) & 3u, &s1, &c1);
+  *s = f2_pack(s0, s1);
+  *c = f2_pack(c0, c1);
+}
+#endif // __CUDACC__
+
 // natural log on (0, 1]
 DM_HD float log_(float x) {
 #if defined(__CUDA_ARCH__)

@@ -105,6 +105,7 @@ struct doapp_ctx {
   int use_limits = 0;
   float rpy_s = 0.0f, rpy_c = 0.0f;
   dm::FastDiv dt_div{};            // verified at create (verify_fast_div)
+  int pk_mode = -1;                // DOAPP_PK=0/1 forces the scalar / packed cost kernel
   bool dt_fast_ok = false;         // ... and delta_t inside [kFastDtLo, kFastDtHi]
   DevBuf<unsigned long long> vbad; // mismatch counter of the verification kernels
   bool fast_math_ok = true;        // DOAPP_EXACT_DIV=1 forces the IEEE divides
@@ -246,6 +247,7 @@ CostParams base_cost_params(doapp_ctx *ctx) {
   p.grid = ctx->grid;
   p.dt_div = ctx->dt_div;
   p.fast_ok = ctx->dt_fast_ok ? 1 : 0;
+  p.pk_mode = ctx->pk_mode;
   return p;
 }
 
@@ -591,6 +593,8 @@ doapp_status doapp_create(const doapp_config *cfg, doapp_ctx **out) {
   ctx->S = (uint64_t)cfg->num_climbers * cfg->samples_per_climber;
   const char *ng = getenv("DOAPP_NO_GRAPH");
   ctx->use_graph = !(ng && ng[0] == '1');
+  const char *pkv = getenv("DOAPP_PK");
+  ctx->pk_mode = (pkv && (pkv[0] == '0' || pkv[0] == '1')) ? pkv[0] - '0' : -1;
   const char *xd = getenv("DOAPP_EXACT_DIV");
   ctx->fast_math_ok = !(xd && xd[0] == '1');
   host_sincos(-1.5707963267948966f, &ctx->rpy_s, &ctx->rpy_c);

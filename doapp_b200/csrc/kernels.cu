@@ -275,6 +275,105 @@ __device__ __forceinline__ unsigned long long warp_min_u64(unsigned long long v)
   return v;
 }
 
+// ---- pending update of the PREVIOUS launch, applied while the trajectory is staged -------
+// Keep-best (generate_trajectories.cu:225-241, D5/D6 fixed): the previous cost launch left the
+// climber's winning key; instead of a separate update kernel every CTA adds the winner's noise
+// while it stages the trajectory, and the climber's first CTA also writes the updated state for
+// the launch after this one.  Weighted (:117-142): the update vector is subtracted instead.
+struct Pending {
+  bool improve;  // block-uniform: the staged trajectory gets swin[] / the winner's noise added
+  bool weighted;
+  uint32_t tg;      // winner's global sample index
+  const float *pnz; // winner's noise row in the previous launch's external buffer
+};
+
+template <int D>
+__device__ __forceinline__ Pending pending_decide(const CostParams &P, uint32_t c, float *swin) {
+  Pending pd{false, P.pend_mode == PEND_WEIGHTED, 0u, nullptr};
+  const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (pd.weighted) {
+    pd.improve = true;
+    if (blockIdx.x == 0 && threadIdx.x == 0) P.found_better[c] = 1;
+  } else if (P.pend_mode != PEND_NONE) {
+    const unsigned long long pk = __ldg(P.pend_keys + c);
+    const uint32_t hi = (uint32_t)(pk >> 32);
+    pd.tg = (uint32_t)pk;
+    uint32_t cur_new = hi;
+    if (P.pend_mode == PEND_KEEP_BEST) {
+      const uint32_t cur = __ldg(P.cur_hi_in + c);
+      pd.improve = hi < cur;
+      cur_new = pd.improve ? hi : cur;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+      P.cur_hi_out[c] = cur_new;
+      if (P.pend_mode == PEND_SEED)
+        P.found_better[c] = 0;
+      else if (pd.improve)
+        P.found_better[c] = 1;
+    }
+  }
+  if (blockIdx.x == 0 && P.usum_reset && threadIdx.x < 8) P.usum_reset[(size_t)c * 8 + threadIdx.x] = 0;
+  if (blockIdx.x == 0 && P.keys_reset && threadIdx.x == 0) P.keys_reset[c] = kKeyNone;
+  if (pd.improve && !pd.weighted && P.pend_noise_mode == NOISE_EXTERNAL)
+    pd.pnz = P.pend_noise + ((size_t)c * P.noise_m + (size_t)(pd.tg - P.noise_t0)) * P.n_noise * D;
+  if (pd.weighted) {
+    // trajectory[w][j] -= gain * u[j] (generate_trajectories.cu:139-140): swin[j] = -(gain*u[j])
+    if (warp == (blockDim.x >> 5) - 1 && lane < D) {
+      const long long sum = P.pend_usum[(size_t)c * 8 + lane];
+      const long long poisoned = P.pend_usum[(size_t)c * 8 + 7];
+      const float u = poisoned ? __int_as_float(0x7fc00000)
+                               : __double2float_rn(__dmul_rn(__ll2double_rn(sum), 0x1p-28));
+      swin[lane] = -dm::mul_(P.update_gain, u);
+    }
+  } else if (pd.improve && P.n_noise == 1 && warp == (blockDim.x >> 5) - 1 && lane < 3) {
+    // the winner's noise vector (one d-vector per sample, D16): three lanes of the CTA's last
+    // warp redraw its Box-Muller pairs
+    float a = 0.0f, b = 0.0f;
+    if (P.pend_noise_mode == NOISE_PHILOX) {
+      dm::noise_pair(P.seed_lo, P.seed_hi, P.sigma, P.pend_iteration, c, pd.tg, 0, lane, &a, &b);
+    } else if (P.pend_noise_mode == NOISE_EXTERNAL) {
+      a = 2 * lane < D ? __ldg(pd.pnz + 2 * lane) : 0.0f;
+      b = 2 * lane + 1 < D ? __ldg(pd.pnz + 2 * lane + 1) : 0.0f;
+    }
+    if (2 * lane < D) swin[2 * lane] = a;
+    if (2 * lane + 1 < D) swin[2 * lane + 1] = b;
+  }
+  return pd;
+}
+
+// Stage the climber's trajectory (with the pending update applied): SoA [j][npad] in global ->
+// AoS [w][DP] in shared; SOA stores [j][npad + 2] instead (waypoint n duplicates n - 1), so
+// that one 64-bit shared load yields the packed (w, w + 1) operand of the packed kernel.
+template <int D, int DP, bool SOA>
+__device__ __forceinline__ void stage_trajectory(const CostParams &P, uint32_t c, const Pending &pd,
+                                                 const float *swin, float *sbase) {
+  if (pd.improve) __syncthreads(); // block-uniform; swin is complete
+  const float *traj = P.traj + (size_t)c * D * P.npad;
+  float *tnext = (blockIdx.x == 0 && P.traj_next) ? P.traj_next + (size_t)c * D * P.npad : nullptr;
+  for (uint32_t i = threadIdx.x; i < P.n * D; i += blockDim.x) {
+    const uint32_t j = i / P.n, w = i - j * P.n;
+    float b = __ldg(traj + (size_t)j * P.npad + w);
+    if (pd.improve) {
+      float e;
+      if (P.n_noise == 1)
+        e = swin[j];
+      else if (P.pend_noise_mode == NOISE_EXTERNAL)
+        e = __ldg(pd.pnz + (size_t)w * D + j);
+      else
+        e = dm::noise_at(P.seed_lo, P.seed_hi, P.sigma, P.pend_iteration, c, pd.tg, w, j);
+      b = dm::add_(b, e);
+    }
+    if (SOA) {
+      sbase[j * (P.npad + 2) + w] = b;
+      if (w == P.n - 1) sbase[j * (P.npad + 2) + w + 1] = b;
+    } else {
+      sbase[w * DP + j] = b;
+    }
+    if (tnext) tnext[(size_t)j * P.npad + w] = b;
+  }
+  __syncthreads();
+}
+
 template <int D, int GM, bool NPW, bool FIDX, bool LIM>
 __global__ void __launch_bounds__(kMaxCostThreads)
     cost_kernel(const __grid_constant__ CostParams P) {
@@ -311,40 +410,7 @@ __global__ void __launch_bounds__(kMaxCostThreads)
 #pragma unroll
   for (int j = 0; j < D; ++j) start[j] = __ldg(P.start + j);
 
-  // ---- pending keep-best of the PREVIOUS launch (generate_trajectories.cu:225-241, D5/D6
-  // fixed).  The previous cost launch left the climber's winning key; instead of a separate
-  // update kernel every CTA applies the winner's noise while it stages the trajectory, and
-  // the climber's first CTA also writes the updated state for the launch after this one.
-  uint32_t pend_tg = 0;
-  bool improve = false; // block-uniform: the staged trajectory gets swin[] / the winner's noise added
-  const bool weighted = P.pend_mode == PEND_WEIGHTED;
-  if (weighted) {
-    improve = true;
-    if (blockIdx.x == 0 && threadIdx.x == 0) P.found_better[c] = 1;
-    if (blockIdx.x == 0 && P.usum_reset && threadIdx.x < 8) P.usum_reset[(size_t)c * 8 + threadIdx.x] = 0;
-  } else if (P.pend_mode != PEND_NONE) {
-    const unsigned long long pk = __ldg(P.pend_keys + c);
-    const uint32_t hi = (uint32_t)(pk >> 32);
-    pend_tg = (uint32_t)pk;
-    uint32_t cur_new = hi;
-    if (P.pend_mode == PEND_KEEP_BEST) {
-      const uint32_t cur = __ldg(P.cur_hi_in + c);
-      improve = hi < cur;
-      cur_new = improve ? hi : cur;
-    }
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
-      P.cur_hi_out[c] = cur_new;
-      if (P.pend_mode == PEND_SEED)
-        P.found_better[c] = 0;
-      else if (improve)
-        P.found_better[c] = 1;
-    }
-    if (blockIdx.x == 0 && P.usum_reset && threadIdx.x < 8) P.usum_reset[(size_t)c * 8 + threadIdx.x] = 0;
-  }
-  if (blockIdx.x == 0 && P.keys_reset && threadIdx.x == 0) P.keys_reset[c] = kKeyNone;
-  const float *pnz = nullptr; // the winner's noise row in the previous launch's external buffer
-  if (improve && !weighted && P.pend_noise_mode == NOISE_EXTERNAL)
-    pnz = P.pend_noise + ((size_t)c * P.noise_m + (size_t)(pend_tg - P.noise_t0)) * P.n_noise * D;
+  const Pending pd = pending_decide<D>(P, c, swin);
 
   const float *nz = nullptr;
   if (P.noise_mode == NOISE_EXTERNAL)
@@ -369,54 +435,8 @@ __global__ void __launch_bounds__(kMaxCostThreads)
         if (2 * warp + 1 < D && warp < 2) seps[(2 * warp + 1) * 32 + lane] = b;
       }
     }
-    // the pending winner's noise vector (one d-vector per sample, D16): three lanes of the
-    // CTA's last warp redraw its Box-Muller pairs
-    if (weighted) {
-      // trajectory[w][j] -= gain * u[j] (generate_trajectories.cu:139-140): swin[j] = -(gain*u[j])
-      if (warp == (blockDim.x >> 5) - 1 && lane < D) {
-        const long long sum = P.pend_usum[(size_t)c * 8 + lane];
-        const long long poisoned = P.pend_usum[(size_t)c * 8 + 7];
-        const float u = poisoned ? __int_as_float(0x7fc00000)
-                                 : __double2float_rn(__dmul_rn(__ll2double_rn(sum), 0x1p-28));
-        swin[lane] = -dm::mul_(P.update_gain, u);
-      }
-    } else if (improve && P.n_noise == 1 && warp == (blockDim.x >> 5) - 1 && lane < 3) {
-      float a = 0.0f, b = 0.0f;
-      if (P.pend_noise_mode == NOISE_PHILOX) {
-        dm::noise_pair(P.seed_lo, P.seed_hi, P.sigma, P.pend_iteration, c, pend_tg, 0, lane, &a, &b);
-      } else if (P.pend_noise_mode == NOISE_EXTERNAL) {
-        a = 2 * lane < D ? __ldg(pnz + 2 * lane) : 0.0f;
-        b = 2 * lane + 1 < D ? __ldg(pnz + 2 * lane + 1) : 0.0f;
-      }
-      if (2 * lane < D) swin[2 * lane] = a;
-      if (2 * lane + 1 < D) swin[2 * lane + 1] = b;
-    }
   }
-  if (improve) __syncthreads(); // block-uniform
-
-  // stage the climber's trajectory (with the pending update applied): SoA [j][npad] in
-  // global -> AoS [w][DP] in shared
-  {
-    const float *traj = P.traj + (size_t)c * D * P.npad;
-    float *tnext = (blockIdx.x == 0 && P.traj_next) ? P.traj_next + (size_t)c * D * P.npad : nullptr;
-    for (uint32_t i = threadIdx.x; i < P.n * D; i += blockDim.x) {
-      const uint32_t j = i / P.n, w = i - j * P.n;
-      float b = __ldg(traj + (size_t)j * P.npad + w);
-      if (improve) {
-        float e;
-        if (P.n_noise == 1)
-          e = swin[j];
-        else if (P.pend_noise_mode == NOISE_EXTERNAL)
-          e = __ldg(pnz + (size_t)w * D + j);
-        else
-          e = dm::noise_at(P.seed_lo, P.seed_hi, P.sigma, P.pend_iteration, c, pend_tg, w, j);
-        b = dm::add_(b, e);
-      }
-      sbase[w * DP + j] = b;
-      if (tnext) tnext[(size_t)j * P.npad + w] = b;
-    }
-  }
-  __syncthreads();
+  stage_trajectory<D, DP, false>(P, c, pd, swin, sbase);
   if (share_noise) {
 #pragma unroll
     for (int j = 0; j < D; ++j) eps[j] = seps[j * 32 + lane];
@@ -535,6 +555,261 @@ __global__ void __launch_bounds__(kMaxCostThreads)
     const size_t s = (size_t)c * P.m + t;
     if (P.scores) P.scores[s] = score;
     if (P.collisions) P.collisions[s] = coll;
+  }
+  if (P.keys_float) {
+    unsigned long long key =
+        active ? ((unsigned long long)key_hi_float(score) << 32) | tg : kKeyNone;
+    key = warp_min_u64(key);
+    if (lane == 0) atomicMin(P.keys_float + c, key);
+  }
+  if (P.keys) {
+    unsigned long long key =
+        active ? ((unsigned long long)key_hi(P.select_mode, score) << 32) | tg : kKeyNone;
+    key = warp_min_u64(key);
+    if (lane == 0) atomicMin(P.keys + c, key);
+  }
+}
+
+// ===================================================== packed (two samples per thread) path
+// For launches with one thread per sample, the thread walks its waypoints two at a time and
+// all fp32 arithmetic is issued as packed fma.rn.f32x2 (FFMA2 / FADD2 / FMUL2), waypoint w in
+// the low half and w + 1 in the high half:
+// the FMA pipe does the same work in half the issue slots, which is what bounds this kernel
+// (profiles/r01).  Per-half work is only what has no packed form: compares, float->int,
+// index arithmetic, the gathers.  Results equal the scalar kernel bit for bit.
+struct P3v {
+  dm::f2 x, y, z;
+};
+__device__ __forceinline__ P3v rot_y2(dm::f2 s, dm::f2 c, P3v q) {
+  P3v u;
+  u.x = dm::f2_fma(s, q.z, dm::f2_mul(c, q.x));
+  u.y = q.y;
+  u.z = dm::f2_fma(c, q.z, dm::f2_mul(dm::f2_neg(s), q.x));
+  return u;
+}
+__device__ __forceinline__ P3v rot_z2(dm::f2 s, dm::f2 c, P3v q) {
+  P3v u;
+  u.x = dm::f2_fma(dm::f2_neg(s), q.y, dm::f2_mul(c, q.x));
+  u.y = dm::f2_fma(c, q.y, dm::f2_mul(s, q.x));
+  u.z = q.z;
+  return u;
+}
+
+// fk_points<D, true> on two waypoints (generate_trajectories.cu:397-463)
+template <int D>
+__device__ __forceinline__ void fk_points2(const dm::f2 (&th)[D], float rpy_s, float rpy_c,
+                                           P3v (&out)[5]) {
+  using namespace dm;
+  f2 s, c;
+  P3v p, q;
+  f2_sincos_small(th[0], &s, &c); // base, gt.cu:405-410
+  q = P3v{f2_splat(0.0f), f2_splat(-0.0015f), f2_splat(0.0715f)};
+  p = rot_y2(s, c, q);
+  out[0] = p;
+  f2_sincos_small(th[1], &s, &c); // shoulder, :416-421
+  q = P3v{p.x, p.y, f2_add(p.z, f2_splat(0.045f))};
+  p = rot_z2(s, c, q);
+  out[1] = p;
+  f2_sincos_small(th[2], &s, &c); // elbow, :427-432
+  q = P3v{p.x, p.y, f2_add(p.z, f2_splat(0.1f))};
+  p = rot_y2(s, c, q);
+  out[2] = p;
+  f2_sincos_small(th[3], &s, &c); // wrist, :438-443
+  q = P3v{p.x, p.y, f2_add(p.z, f2_splat(0.1f))};
+  p = rot_y2(s, c, q);
+  out[3] = p;
+  q = P3v{p.x, f2_add(p.y, f2_splat(-0.0125f)), f2_add(p.z, f2_splat(0.08f))}; // :449-454
+  if (D >= 5) {
+    f2_sincos_small(th[D >= 5 ? 4 : 0], &s, &c);
+    p = rot_y2(s, c, q);
+  } else {
+    p = q;
+  }
+  p = rot_y2(f2_splat(rpy_s), f2_splat(rpy_c), p); // :456-459
+  p = P3v{p.x, f2_add(p.y, f2_splat(-0.005f)), f2_add(p.z, f2_splat(0.07f))};
+  out[4] = p;
+}
+
+// collides<GM, true> on two points (threshold form, see GridDev::tx_bits)
+template <int GM>
+__device__ __forceinline__ void collides2(const CostParams &P, P3v p, int *hit_lo, int *hit_hi) {
+  using namespace dm;
+  const GridDev &g = P.grid;
+  const f2 ax = f2_add(p.x, f2_splat(g.x_off)), ay = f2_add(p.y, f2_splat(g.y_off));
+  const f2 az = f2_add(p.z, f2_splat(0.0f));
+  const f2 fx = f2_div_fast_unguarded(ax, P.res_div), fy = f2_div_fast_unguarded(ay, P.res_div),
+           fz = f2_div_fast_unguarded(az, P.res_div);
+  auto half = [&](float axh, float ayh, float azh, float fxh, float fyh, float fzh) -> int {
+    const bool in = (__float_as_uint(axh) < g.tx_bits) & (__float_as_uint(ayh) < g.ty_bits) &
+                    (__float_as_uint(azh) < g.tz_bits);
+    const uint32_t ix = __float2uint_rz(fxh), iy = __float2uint_rz(fyh), iz = __float2uint_rz(fzh);
+    const uint32_t lin = (iz * g.ny + iy) * g.nx + ix;
+    int hit = 0;
+    if (GM == GM_U8_CDG) {
+      if (in) hit = __ldg((const uint8_t *)g.cells + lin) != 0;
+    } else {
+      if (in) hit = __ldg((const float *)g.cells + lin) <= P.coll_dist;
+    }
+    return hit;
+  };
+  *hit_lo = half(f2_lo(ax), f2_lo(ay), f2_lo(az), f2_lo(fx), f2_lo(fy), f2_lo(fz));
+  *hit_hi = half(f2_hi(ax), f2_hi(ay), f2_hi(az), f2_hi(fx), f2_hi(fy), f2_hi(fz));
+}
+
+// waypoint_cost<..., FAST = true> on two CONSECUTIVE WAYPOINTS (lo = w, hi = w + 1) of one
+// sample.  xprev / vprev are waypoint w - 1's angles and velocities; the hi half's priors are
+// the lo half's own results.  fine_lo / fine_hi as waypoint_cost's return value.
+template <int D, int GM, bool LIM>
+__device__ __forceinline__ void waypoint_cost2(const CostParams &P, const dm::f2 (&x)[D],
+                                               const float (&xprev)[D], const float (&vprev)[D],
+                                               dm::f2 (&vnew)[D], dm::f2 *a2_out, dm::f2 *l2_out,
+                                               int *coll_lo, int *coll_hi, bool *fine_lo,
+                                               bool *fine_hi) {
+  using namespace dm;
+  bool f_lo = true, f_hi = true;
+  f2 a2 = f2_splat(0.0f), l2 = f2_splat(0.0f);
+#pragma unroll
+  for (int j = 0; j < D; ++j) {
+    f_lo = f_lo & fine_angle(f2_lo(x[j]));
+    f_hi = f_hi & fine_angle(f2_hi(x[j]));
+    const f2 xp = f2_pack(xprev[j], f2_lo(x[j]));
+    const f2 v = f2_div_fast_unguarded(f2_sub(x[j], xp), P.dt_div); // :288
+    const f2 vp = f2_pack(vprev[j], f2_lo(v));
+    const f2 a = f2_div_fast_unguarded(f2_sub(v, vp), P.dt_div);
+    a2 = f2_add(a2, f2_mul_rounded(a, a)); // :76 (product rounded, then added)
+    vnew[j] = v;
+    if (LIM) {
+      const f2 over = f2_sub(x[j], f2_splat(P.lim_max[j])), under = f2_sub(f2_splat(P.lim_min[j]), x[j]);
+      const float h0 = fmaxf(0.0f, fmaxf(f2_lo(over), f2_lo(under)));
+      const float h1 = fmaxf(0.0f, fmaxf(f2_hi(over), f2_hi(under)));
+      l2 = f2_add(l2, f2_pack(__fmul_rn(h0, h0), __fmul_rn(h1, h1)));
+    }
+  }
+  int c_lo = 0, c_hi = 0;
+  if (GM != GM_NONE) {
+    P3v pts[5];
+    fk_points2<D>(x, P.rpy_s, P.rpy_c, pts);
+#pragma unroll
+    for (int l = 0; l < 5; ++l) {
+      int h0, h1;
+      collides2<GM>(P, pts[l], &h0, &h1);
+      c_lo += h0;
+      c_hi += h1;
+    }
+  }
+  *a2_out = a2;
+  *l2_out = l2;
+  *coll_lo = c_lo;
+  *coll_hi = c_hi;
+  *fine_lo = f_lo;
+  *fine_hi = f_hi;
+}
+
+constexpr int kPkThreads = 128;
+#ifndef DOAPP_PK_MINBLOCKS
+#define DOAPP_PK_MINBLOCKS 4
+#endif
+
+// One thread = one sample, TWO consecutive waypoints per step in the two halves of packed
+// registers.  Same sample-to-lane mapping, noise, staging prologue and outputs as cost_kernel
+// with one thread per sample.
+template <int D, int GM, bool LIM>
+__global__ void __launch_bounds__(kPkThreads, DOAPP_PK_MINBLOCKS)
+    cost_kernel_pk(const __grid_constant__ CostParams P) {
+  using namespace dm;
+  extern __shared__ __align__(16) float smem[];
+  const uint32_t NP = P.npad + 2;
+  float *sbase = smem;                     // [D][NP], waypoint n duplicates n - 1
+  float *swin = sbase + (size_t)D * NP;    // [8] pending winner's noise / update vector
+  const uint32_t c = blockIdx.y;
+  const int lane = threadIdx.x & 31;
+  uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  const bool active = t < P.m;
+  t = active ? t : P.m - 1; // idle lanes shadow the last sample (no divergence, no stores)
+  const uint32_t tg = (uint32_t)(P.sample_offset + t);
+
+  const Pending pd = pending_decide<D>(P, c, swin);
+
+  // stage 1: one d-vector of noise per sample (generate_trajectories.cu:37-59)
+  float eps[D];
+#pragma unroll
+  for (int j = 0; j < D; ++j) eps[j] = 0.0f;
+  if (P.noise_mode == NOISE_EXTERNAL) {
+    const float *nz = P.noise + ((size_t)c * P.noise_m + (size_t)(tg - P.noise_t0)) * D;
+#pragma unroll
+    for (int j = 0; j < D; ++j) eps[j] = __ldg(nz + j);
+  } else if (P.noise_mode == NOISE_PHILOX) {
+    noise_vec<D>(P.seed_lo, P.seed_hi, P.sigma, P.iteration, c, tg, 0, eps);
+  }
+  stage_trajectory<D, 0, true>(P, c, pd, swin, sbase);
+
+  float xprev[D], vprev[D];
+  bool fine1 = P.fast_ok != 0, fine2 = fine1;
+#pragma unroll
+  for (int j = 0; j < D; ++j) { // generate_trajectories.cu:285, SURVEY D7
+    xprev[j] = vprev[j] = __ldg(P.start + j);
+    fine1 = fine1 & fine_angle(xprev[j]);
+  }
+
+  float total = 0.0f, ltotal = 0.0f;
+  int coll = 0;
+  for (uint32_t w = 0; w < P.n; w += 2) {
+    const bool has_hi = w + 1 < P.n;
+    f2 x[D], vnew[D];
+#pragma unroll
+    for (int j = 0; j < D; ++j) { // generate_trajectories.cu:53-57
+      const float2 b = *reinterpret_cast<const float2 *>(sbase + j * NP + w);
+      x[j] = f2_pack(add_(b.x, eps[j]), add_(b.y, eps[j]));
+    }
+    f2 a2, l2;
+    int cw0, cw1;
+    bool f0, f1;
+    waypoint_cost2<D, GM, LIM>(P, x, xprev, vprev, vnew, &a2, &l2, &cw0, &cw1, &f0, &f1);
+    const bool valid0 = f0 & fine1 & fine2, valid1 = f1 & f0 & fine1;
+    fine2 = f0 & (P.fast_ok != 0);
+    fine1 = f1 & (P.fast_ok != 0);
+    if (!(valid0 & valid1)) { // rare: redo the offending waypoint(s) with IEEE divides, full sin/cos
+#pragma unroll 1
+      for (int h = 0; h < 2; ++h) {
+        if (h == 0 ? valid0 : valid1) continue;
+        WpIn<D> in;
+#pragma unroll
+        for (int j = 0; j < D; ++j) { // the hi waypoint's priors are the (possibly redone) lo results
+          in.x[j] = h ? f2_hi(x[j]) : f2_lo(x[j]);
+          in.xprev[j] = h ? f2_lo(x[j]) : xprev[j];
+          in.vprev[j] = h ? f2_lo(vnew[j]) : vprev[j];
+        }
+        const WpOut<D> o = waypoint_cost_general<D, GM, true, LIM>(P, in);
+#pragma unroll
+        for (int j = 0; j < D; ++j)
+          vnew[j] = h ? f2_pack(f2_lo(vnew[j]), o.vnew[j]) : f2_pack(o.vnew[j], f2_hi(vnew[j]));
+        a2 = h ? f2_pack(f2_lo(a2), o.a2) : f2_pack(o.a2, f2_hi(a2));
+        l2 = h ? f2_pack(f2_lo(l2), o.l2) : f2_pack(o.l2, f2_hi(l2));
+        if (h) cw1 = o.coll; else cw0 = o.coll;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < D; ++j) {
+      xprev[j] = f2_hi(x[j]);
+      vprev[j] = f2_hi(vnew[j]);
+    }
+    // fixed order: left fold over the waypoints (oracle ORC_SUM_WAYPOINT)
+    coll += cw0;
+    total = add_(total, f2_lo(a2));
+    if (LIM) ltotal = add_(ltotal, f2_lo(l2));
+    if (has_hi) {
+      coll += cw1;
+      total = add_(total, f2_hi(a2));
+      if (LIM) ltotal = add_(ltotal, f2_hi(l2));
+    }
+  }
+
+  float score = add_((float)coll, mul_(P.smooth_scale, total)); // :81,100,107-108
+  if (LIM && P.limit_weight != 0.0f) score = add_(score, mul_(P.limit_weight, ltotal));
+  if (active) {
+    const size_t si = (size_t)c * P.m + t;
+    if (P.scores) P.scores[si] = score;
+    if (P.collisions) P.collisions[si] = coll;
   }
   if (P.keys_float) {
     unsigned long long key =
@@ -774,14 +1049,45 @@ static cudaError_t launch_cost_t(const CostParams &p, dim3 grid, unsigned thread
   return cudaLaunchKernelEx(&cfg, kern, p);
 }
 
+template <int D, int GM, bool LIM>
+static cudaError_t launch_cost_pk_t(const CostParams &p, cudaStream_t st) {
+  const size_t smem = ((size_t)D * (p.npad + 2) + 8) * sizeof(float);
+  auto kern = cost_kernel_pk<D, GM, LIM>;
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+  }
+  const dim3 grid((p.m + kPkThreads - 1) / kPkThreads, p.k);
+  kern<<<grid, kPkThreads, smem, st>>>(p);
+  return cudaGetLastError();
+}
+
 template <int D>
-static cudaError_t launch_cost_d(const CostParams &p, dim3 grid, unsigned threads, size_t smem,
-                                 unsigned cluster, cudaStream_t st) {
+static cudaError_t launch_cost_pk_d(const CostParams &p, int gm, cudaStream_t st) {
+  const bool lim = p.use_limits != 0;
+#define DOAPP_PK(GMV)                                                                 \
+  return lim ? launch_cost_pk_t<D, GMV, true>(p, st) : launch_cost_pk_t<D, GMV, false>(p, st)
+  switch (gm) {
+  case GM_U8_CDG: DOAPP_PK(GM_U8_CDG);
+  case GM_F32_CDG: DOAPP_PK(GM_F32_CDG);
+  default: DOAPP_PK(GM_NONE);
+  }
+#undef DOAPP_PK
+}
+
+static int grid_mode_of(const CostParams &p) {
   int gm = GM_NONE;
   if (p.collision_mode != 0 && p.grid.kind != 0 && p.grid.cells) {
     gm = GM_GENERIC;
     if (p.grid.frame == 0 && p.grid.fast_idx) gm = p.grid.kind == 1 ? GM_U8_CDG : GM_F32_CDG;
   }
+  return gm;
+}
+
+template <int D>
+static cudaError_t launch_cost_d(const CostParams &p, dim3 grid, unsigned threads, size_t smem,
+                                 unsigned cluster, cudaStream_t st) {
+  const int gm = grid_mode_of(p);
   const bool npw = p.n_noise != 1 && p.noise_mode != NOISE_ZERO;
   const bool lim = p.use_limits != 0;
 #define DOAPP_GO(GMV)                                                                       \
@@ -823,6 +1129,17 @@ cudaError_t launch_cost(const CostParams &p_in, int d, int sm_count, cudaStream_
     // tuning override: DOAPP_PARTS_LOG2 caps the threads per sample (profiling only)
     static const char *env = getenv("DOAPP_PARTS_LOG2");
     if (env && env[0] >= '0' && env[0] <= '5' && (uint32_t)(env[0] - '0') < lg) lg = env[0] - '0';
+  }
+  {
+    // One thread per sample with two waypoints per step in packed fp32x2 arithmetic whenever
+    // the samples alone fill the chip (DOAPP_PK=0/1 forces the choice where it is legal).
+    const bool npw = p.n_noise != 1 && p.noise_mode != NOISE_ZERO;
+    const int gm = grid_mode_of(p);
+    bool pk = lg == 0;
+    if (p.pk_mode == 1) pk = true;
+    if (p.pk_mode == 0) pk = false;
+    if (pk && !npw && gm != GM_GENERIC && p.fast_ok)
+      return d == 5 ? launch_cost_pk_d<5>(p, gm, st) : launch_cost_pk_d<4>(p, gm, st);
   }
   p.parts_log2 = lg;
   const uint32_t T = 1u << lg;

@@ -67,6 +67,7 @@ struct CostParams {
   unsigned long long *keys;      // [k] packed argmin keys for the update rule, or nullptr
   unsigned long long *keys_float; // [k] packed (float bits, t) keys for the host-style argmin
   dm::FastDiv dt_div, res_div; // divisor + RN(1/divisor)
+  int pk_mode; // packed two-samples-per-thread kernel: -1 auto, 0 never, 1 whenever legal (DOAPP_PK)
   int fast_ok; // 1: the reciprocal dt divide was verified and dt is in [kFastDtLo, kFastDtHi]
   // pending keep-best of the previous launch, applied by this one while it stages the
   // trajectory (see cost_kernel): winner key per climber, the noise that launch drew, the

@@ -160,3 +160,49 @@ def test_c1_golden_kat(capi):
     assert hashlib.sha256(r["collisions"].tobytes()).hexdigest() == kat["collisions_sha256"]
     assert hashlib.sha256(nz.tobytes()).hexdigest() == kat["noise_sha256"]
     assert r["argmin"] == kat["argmin"] and int(r["collisions"].sum()) == kat["collisions_total"]
+
+
+PK_CASES = [  # (k, m, n, d, grid, sigma, limits)
+    (1, 64, 32, 5, "u8", 0.1, False),
+    (2, 37, 50, 4, "u8", 0.3, False),     # ragged m, d = 4
+    (1, 1, 16, 5, "u8", 0.1, False),
+    (1, 5, 1, 5, "u8", 0.5, False),       # single waypoint: the high half is idle
+    (1, 1000, 64, 5, "f32", 0.5, False),
+    (3, 129, 33, 5, "u8", 0.3, True),      # odd n: the last step's high half is idle
+    (1, 256, 128, 5, "none", 0.2, False),
+]
+
+
+@pytest.mark.parametrize("k,m,n,d,grid,sigma,limits", PK_CASES)
+def test_packed_kernel_parity(capi, oracle_mod, monkeypatch, k, m, n, d, grid, sigma, limits):
+    """cost_kernel_pk (two waypoints per step in packed fma.rn.f32x2) against the oracle, forced on with
+    DOAPP_PK=1 at sizes the oracle finishes in seconds; includes angles that are exactly zero
+    (straight-line path valid) and denormal-small (must take the IEEE fallback per half)."""
+    monkeypatch.setenv("DOAPP_PK", "1")
+    kw = dict(sigma=sigma)
+    if limits:
+        kw["limit_weight"] = 2.0
+    ctx, orc = _mk(capi, oracle_mod, k, m, n, d, 1, **kw)
+    if limits:
+        lo, hi = -0.3 * np.ones(d, np.float32), 0.6 * np.ones(d, np.float32)
+        ctx.set_limits(lo, hi)
+        orc.set_limits(lo, hi)
+    if grid != "none":
+        g = synth.box_grid(64, 0.02) if grid == "u8" else synth.box_distance_grid(64, 0.02)
+        ctx.set_grid(g, 0.02)
+        orc.set_grid(g, 0.02)
+    start = synth.START[:d]
+    base = np.stack([capi.plan_lerp(start, synth.GOALS[c % 2][:d], n) for c in range(k)])
+    nz = synth.noise(k, m, 1, d, sigma)
+    if m >= 8:
+        nz[0, 1] = 0.0                      # x == base: zeros for the joints that do not move
+        nz[0, 2, 0, :] = 1e-41              # denormal angles: outside the verified ranges
+        nz[0, 5, 0, 1] = -base[0, 3, 1]     # one angle exactly 0 in the middle of a trajectory
+        nz[0, 6, 0, 0] = 3e5                # |angle| >= 2^17: full-range sin/cos
+    for noise in (nz, None):
+        a = ctx.cost_eval(base, start, noise, iteration=2)
+        b = orc.cost_eval(base, start, noise, iteration=2)
+        assert np.array_equal(a["collisions"], b["collisions"])
+        assert np.array_equal(a["scores"].view(np.uint32), b["scores"].view(np.uint32))
+        assert a["argmin"] == b["argmin"]
+    ctx.close()

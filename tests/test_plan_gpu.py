@@ -121,10 +121,10 @@ def test_replan_dynamic_matches_stepwise(capi, oracle_mod):
     ctx.close()
 
 
-@pytest.mark.parametrize("env", ["DOAPP_NO_GRAPH", "DOAPP_EXACT_DIV"])
+@pytest.mark.parametrize("env", ["DOAPP_NO_GRAPH", "DOAPP_EXACT_DIV", "DOAPP_PK"])
 def test_alternate_paths_bit_identical(capi, monkeypatch, env):
-    """The un-graphed launch path and the IEEE-divide kernels give the same bits as the default
-    graphed / verified-reciprocal path."""
+    """The un-graphed launch path, the IEEE-divide kernels and the packed two-waypoints-per-step
+    kernel (fma.rn.f32x2) give the same bits as the default path."""
     k, m, n, iters = 3, 200, 64, 6
     init = capi.plan_lerp(synth.START, synth.GOALS[1], n)
     g = synth.box_grid(64, 0.02)
