@@ -31,7 +31,7 @@ ABI_SYMBOLS = [
     "doapp_set_limits", "doapp_noise_generate", "doapp_cost_eval", "doapp_stage_inputs",
     "doapp_cost_eval_dev", "doapp_read_results", "doapp_plan_lerp", "doapp_plan",
     "doapp_plan_async", "doapp_plan_wait", "doapp_plan_state", "doapp_replan_dynamic",
-    "doapp_plan_bench", "doapp_plan_profile", "doapp_comm_unique_id", "doapp_comm_init", "doapp_grid_broadcast",
+    "doapp_plan_bench", "doapp_plan_profile", "doapp_probe_gather", "doapp_comm_unique_id", "doapp_comm_init", "doapp_grid_broadcast",
     "doapp_launch_count", "doapp_debug_sincos", "doapp_debug_fk",
 ]
 
@@ -103,6 +103,7 @@ def load_library(path: str | None = None) -> C.CDLL:
                                        vp, vp]
     L.doapp_plan_bench.argtypes = [vp, C.c_uint32, C.c_uint32, vp]
     L.doapp_plan_profile.argtypes = [vp, C.c_uint32, vp, vp, vp]
+    L.doapp_probe_gather.argtypes = [vp, C.c_size_t, C.c_uint32, vp]
     L.doapp_comm_unique_id.argtypes = [vp]
     L.doapp_comm_init.argtypes = [vp, vp, C.c_int32, C.c_int32]
     L.doapp_grid_broadcast.argtypes = [vp, C.c_int32]
@@ -312,6 +313,12 @@ class Context:
                                              _p(clouds), npts, _p(bt), C.addressof(bs),
                                              C.addressof(ms)))
         return dict(best_traj=bt, best_score=bs.value, elapsed_ms=ms.value)
+
+    def probe_gather(self, array_bytes: int, cell_bytes: int = 1) -> float:
+        """Random single-cell loads per second from a scratch array (roofline denominator)."""
+        out = C.c_double()
+        self._ck(self.L.doapp_probe_gather(self.h, array_bytes, cell_bytes, C.addressof(out)))
+        return out.value
 
     # -- multi-GPU ---------------------------------------------------------
     def comm_init(self, uid: bytes, rank: int, nranks: int):

@@ -1235,6 +1235,37 @@ doapp_status doapp_plan_profile(doapp_ctx *ctx, uint32_t iters, float *cost_ms_t
   return DOAPP_OK;
 }
 
+doapp_status doapp_probe_gather(doapp_ctx *ctx, size_t array_bytes, uint32_t cell_bytes,
+                                double *gathers_per_sec) {
+  if (!ctx) return DOAPP_INVALID_ARG;
+  if (!gathers_per_sec || array_bytes < 4096 || (cell_bytes != 1 && cell_bytes != 4))
+    return fail(ctx, DOAPP_INVALID_ARG, "doapp_probe_gather: bad argument");
+  CU(cudaSetDevice(ctx->cfg.device));
+  DevBuf<uint8_t> arr;
+  DevBuf<uint32_t> sink;
+  doapp_status st = [&]() -> doapp_status {
+    ST(ensure(ctx, arr, array_bytes));
+    ST(ensure(ctx, sink, 1));
+    CU(cudaMemsetAsync(arr.p, 1, array_bytes, ctx->stream));
+    const uint32_t blocks = (uint32_t)ctx->sm_count * 8, per_thread = 1024;
+    const uint64_t cells = array_bytes / cell_bytes;
+    for (int rep = 0; rep < 3; ++rep) { // the last repetition is the measurement
+      CU(cudaEventRecord(ctx->ev0, ctx->stream));
+      CU(launch_gather_probe(arr.p, cells, cell_bytes, blocks, per_thread, sink.p, ctx->stream));
+      CU(cudaEventRecord(ctx->ev1, ctx->stream));
+      ctx->launches += 1;
+    }
+    CU(cudaStreamSynchronize(ctx->stream));
+    float ms = 0.0f;
+    CU(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+    *gathers_per_sec = (double)blocks * 256.0 * per_thread / (ms * 1e-3);
+    return DOAPP_OK;
+  }();
+  release(arr);
+  release(sink);
+  return st;
+}
+
 // ------------------------------------------------------------------- multi-GPU
 
 doapp_status doapp_comm_unique_id(uint8_t id[DOAPP_COMM_ID_BYTES]) {

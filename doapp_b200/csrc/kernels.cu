@@ -934,6 +934,28 @@ __global__ void scatter_kernel(const __grid_constant__ ScatterParams P) {
   }
 }
 
+// ------------------------------------------------------------ gather probe
+// Roofline denominator for the collision lookups: independent random loads of one
+// cell each (one 32-byte sector per load) from an array of a chosen size, 8 in flight per
+// thread.  An 8 MiB array measures the L2 gather rate, one larger than L2 the HBM rate.
+template <typename T>
+__global__ void __launch_bounds__(256) gather_probe_kernel(const T *cells, uint64_t num_cells,
+                                                           uint32_t per_thread, uint32_t *sink) {
+  uint32_t h = (blockIdx.x * blockDim.x + threadIdx.x) * 0x9E3779B9u + 0x7F4A7C15u;
+  uint32_t acc = 0;
+  for (uint32_t i = 0; i < per_thread; i += 8) {
+    uint64_t idx[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      h ^= h << 13; h ^= h >> 17; h ^= h << 5; // xorshift32
+      idx[u] = ((uint64_t)h * num_cells) >> 32;
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) acc += (uint32_t)__ldg(cells + idx[u]);
+  }
+  if (acc == 0xFFFFFFFFu) *sink = acc; // keeps the loads alive
+}
+
 __global__ void lookup_kernel(GridDev g, const float *xyz, uint64_t count, float coll_dist,
                               long long *cell_index, uint8_t *collides) {
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -1185,6 +1207,16 @@ cudaError_t launch_scatter(const ScatterParams &p, int sm_count, cudaStream_t st
   unsigned cap = (unsigned)sm_count * 8;
   if (blocks > cap) blocks = cap;
   scatter_kernel<<<blocks, 256, 0, st>>>(p);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_gather_probe(const void *cells, uint64_t num_cells, uint32_t cell_bytes,
+                                uint32_t blocks, uint32_t per_thread, uint32_t *sink,
+                                cudaStream_t st) {
+  if (cell_bytes == 4)
+    gather_probe_kernel<float><<<blocks, 256, 0, st>>>((const float *)cells, num_cells, per_thread, sink);
+  else
+    gather_probe_kernel<uint8_t><<<blocks, 256, 0, st>>>((const uint8_t *)cells, num_cells, per_thread, sink);
   return cudaGetLastError();
 }
 

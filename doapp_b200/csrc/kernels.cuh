@@ -130,6 +130,9 @@ cudaError_t launch_verify_div(dm::FastDiv d, uint32_t lo_bits, uint32_t hi_bits,
 cudaError_t launch_update_vector(const UpdateParams &p, int sm_count, cudaStream_t st);
 cudaError_t launch_final(const FinalParams &p, cudaStream_t st);
 cudaError_t launch_scatter(const ScatterParams &p, int sm_count, cudaStream_t st);
+cudaError_t launch_gather_probe(const void *cells, uint64_t num_cells, uint32_t cell_bytes,
+                                uint32_t blocks, uint32_t per_thread, uint32_t *sink,
+                                cudaStream_t st);
 cudaError_t launch_lookup(const GridDev &g, const float *xyz, uint64_t count, float coll_dist,
                           long long *cell_index, uint8_t *collides, cudaStream_t st);
 cudaError_t launch_noise_fill(const CostParams &p, int d, float *out, cudaStream_t st);

@@ -261,6 +261,13 @@ DOAPP_API doapp_status doapp_plan_bench(doapp_ctx *ctx, uint32_t iters, uint32_t
 DOAPP_API doapp_status doapp_plan_profile(doapp_ctx *ctx, uint32_t iters, float *cost_ms_total,
                                           uint32_t *cost_launches, float *loop_ms);
 
+/* Roofline probe: rate of independent random single-cell loads (one 32-byte
+ * sector each) from a scratch array of `array_bytes`, the memory-side ceiling of the
+ * collision lookups of generate_trajectories.cu:412 / cpu_distance_grid.cu:113-126.  An array
+ * well inside L2 gives the L2 gather rate, one larger than L2 the HBM rate. */
+DOAPP_API doapp_status doapp_probe_gather(doapp_ctx *ctx, size_t array_bytes, uint32_t cell_bytes,
+                                          double *gathers_per_sec);
+
 /* ---- multi-GPU ------------------------------------------- */
 
 #define DOAPP_COMM_ID_BYTES 128
