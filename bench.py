@@ -316,7 +316,10 @@ def run_ours(args, w, rank, world, local_rank):
         peaks = json.load(open(pk))
     hbm = float(peaks.get("hbm_gbs", 6650.0))
     per_launch_s = cost_ms * 1e-3 / max(1, cost_launches)
-    alg = alg_bytes_per_wps(n) * m * n
+    # one launch per iteration, or ONE persistent launch running all the iterations
+    units_per_launch = m * n * iters / max(1, cost_launches)
+    alg = alg_bytes_per_wps(n) * units_per_launch
+    kernel_name = "plan_persistent_kernel" if cost_launches == 1 and iters > 1 else "cost_kernel"
     achieved = alg / per_launch_s / 1e9
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
@@ -332,17 +335,18 @@ def run_ours(args, w, rank, world, local_rank):
                 "h2d_bytes_per_step": int(h_start.nbytes + h_init.nbytes),
                 "d2h_bytes_per_step": int(2 * h_init.nbytes + 16)},
         "gpu_launches": int(launches),
-        "roofline": {"bound": "hbm", "kernel": "cost_kernel", "achieved": achieved, "peak": hbm,
+        "roofline": {"bound": "hbm", "kernel": kernel_name, "achieved": achieved, "peak": hbm,
                      "unit": "GB/s", "frac": achieved / hbm,
-                     "traffic": NCU_TRAFFIC.get(args.workload),
+                     "traffic": (NCU_TRAFFIC.get(args.workload) if kernel_name == "cost_kernel"
+                                 else None),
                      "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",
                      "avg_launch_us": per_launch_s * 1e6, "launches_timed": cost_launches,
-                     "alg_bytes_per_launch": alg,
+                     "alg_bytes_per_launch": alg, "units_per_launch": units_per_launch,
                      "kernel_share_of_step": cost_ms / loop_ms if loop_ms else None},
         "clocks": clocks,
         "best_score": r["best_score"],
     }
-    gathers_per_s = LINKS * m * n / per_launch_s
+    gathers_per_s = LINKS * units_per_launch / per_launch_s
     line["gather_roofline"] = {
         "what": "north_star's L2/HBM gather roofline: collision lookups per second of the cost "
                 "kernel against the measured rate of independent random one-sector loads "

@@ -87,6 +87,9 @@ struct doapp_ctx {
   DevBuf<int32_t> coll, final_coll;
   DevBuf<unsigned long long> keys, keys_float;
   DevBuf<uint32_t> cur_hi;
+  DevBuf<unsigned long long> pkeys; // persistent planner: 3 x [k] rotating keys
+  DevBuf<unsigned int> pbar;        // ... and its grid barrier counter
+  int persist_mode = -1;            // DOAPP_PERSIST=0/1: never / whenever legal
   DevBuf<long long> usum; // weighted update: 2 x [k][8] integer sums (ping-pong)
   // Ping-pong state of the planner: traj holds two [k][d][npad] halves, cur_hi two [k]
   // halves, keys three [k] buffers (read / write / being re-armed).  Every launch that
@@ -131,6 +134,7 @@ struct doapp_ctx {
   // per-launch CUDA-event timing of the cost kernel (doapp_plan_profile)
   std::vector<cudaEvent_t> prof_events;
   bool profiling = false;
+  uint32_t prof_launches = 0; // cost launches the last profiled plan timed
 
   std::vector<float> h_out;
 };
@@ -329,6 +333,73 @@ doapp_status upload_start(doapp_ctx *ctx, const float *start) {
   return DOAPP_OK;
 }
 
+// The whole keep-best loop in one cooperative launch (plan_persistent_kernel) when the problem
+// fits one co-resident wave: single rank, keep-best rule, one noise vector per sample.
+doapp_status persistent_eligible(doapp_ctx *ctx, PersistParams *q, bool *ok) {
+  *ok = false;
+  const doapp_config &c = ctx->cfg;
+  if (ctx->persist_mode == 0 || ctx->comm || c.update_mode != DOAPP_UPDATE_KEEP_BEST ||
+      c.noise_waypoints != 1)
+    return DOAPP_OK;
+  CostParams p = base_cost_params(ctx);
+  CU(persistent_plan_config(p, c.waypoint_dim, ctx->sm_count, q, ok));
+  return DOAPP_OK;
+}
+
+doapp_status enqueue_plan_persistent(doapp_ctx *ctx, PersistParams q, uint32_t iters, int noise_mode,
+                                     uint64_t *kernels) {
+  const doapp_config &c = ctx->cfg;
+  const size_t k = c.num_climbers;
+  reset_plan_state(ctx);
+  CU(cudaMemsetAsync(ctx->keys.p, 0xFF, sizeof(unsigned long long) * 3 * k, ctx->stream));
+  // seed pass: score the k unperturbed trajectories (gt.cu:180-191); its keys seed cur_hi
+  ST(launch_pass(ctx, climber_cost_params(ctx), PEND_NONE, 0, NOISE_ZERO, nullptr, true));
+  ST(ensure(ctx, ctx->pkeys, 3 * k));
+  ST(ensure(ctx, ctx->pbar, 1));
+  CU(cudaMemsetAsync(ctx->pkeys.p, 0xFF, sizeof(unsigned long long) * 3 * k, ctx->stream));
+  CU(cudaMemsetAsync(ctx->pbar.p, 0, sizeof(unsigned int), ctx->stream));
+  CostParams &p = q.cost;
+  p.traj = traj_half_ptr(ctx, ctx->traj_s);
+  p.traj_next = traj_half_ptr(ctx, 1 - ctx->traj_s);
+  p.pend_keys = ctx->keys.p + (size_t)ctx->key_w * k;
+  p.cur_hi_out = ctx->cur_hi.p + (size_t)(1 - ctx->cur_s) * k;
+  p.found_better = ctx->found.p;
+  p.noise_mode = noise_mode;
+  p.noise_m = ctx->m_global;
+  p.noise_t0 = 0;
+  q.iters = iters;
+  q.keys3 = ctx->pkeys.p;
+  q.barrier = ctx->pbar.p;
+  q.noise_base = noise_mode == NOISE_EXTERNAL ? ctx->noise.p : nullptr;
+  q.noise_iter_stride = (uint64_t)c.num_climbers * ctx->m_global * c.waypoint_dim;
+  if (ctx->profiling) CU(cudaEventRecord(ctx->prof_events[0], ctx->stream));
+  CU(launch_persistent_plan(q, c.waypoint_dim, ctx->stream));
+  if (ctx->profiling) CU(cudaEventRecord(ctx->prof_events[1], ctx->stream));
+  ctx->prof_launches = 1;
+  ctx->traj_s ^= 1;
+  ctx->cur_s ^= 1;
+  {
+    CostParams f0 = climber_cost_params(ctx);
+    f0.scores = ctx->final_scores.p;
+    f0.collisions = ctx->final_coll.p;
+    ST(launch_pass(ctx, f0, PEND_NONE, 0, NOISE_ZERO, nullptr, false));
+    FinalParams f{};
+    f.traj = traj_half_ptr(ctx, ctx->traj_s);
+    f.start = ctx->start.p;
+    f.scores = ctx->final_scores.p;
+    f.found_better = ctx->found.p;
+    f.k = c.num_climbers;
+    f.n = c.num_waypoints;
+    f.npad = ctx->npad;
+    f.d = c.waypoint_dim;
+    f.dt = c.delta_t;
+    f.out = ctx->out.p;
+    CU(launch_final(f, ctx->stream));
+  }
+  if (kernels) *kernels = 4;
+  return DOAPP_OK;
+}
+
 // Enqueue the planner loop (no host synchronisation inside).  One launch per stage:
 //   seed pass   scores the k unperturbed trajectories                      (gt.cu:180-191)
 //   iteration i costs the samples; while staging it first applies the keep-best of
@@ -341,6 +412,13 @@ doapp_status enqueue_plan(doapp_ctx *ctx, uint32_t iters, int noise_mode, uint64
   const size_t k = c.num_climbers;
   uint64_t nk = 0;
   NcclApi *nccl = ctx->comm ? nccl_api(nullptr) : nullptr;
+  {
+    PersistParams q{};
+    bool persistent = false;
+    ST(persistent_eligible(ctx, &q, &persistent));
+    if (persistent) return enqueue_plan_persistent(ctx, q, iters, noise_mode, kernels);
+  }
+  ctx->prof_launches = iters;
   reset_plan_state(ctx);
   CU(cudaMemsetAsync(ctx->keys.p, 0xFF, sizeof(unsigned long long) * 3 * k, ctx->stream));
   ST(launch_pass(ctx, climber_cost_params(ctx), PEND_NONE, 0, NOISE_ZERO, nullptr, true));
@@ -452,7 +530,11 @@ doapp_status reset_climbers(doapp_ctx *ctx) {
 }
 
 doapp_status run_plan(doapp_ctx *ctx, uint32_t iters, int noise_mode) {
-  if (!ctx->use_graph || ctx->profiling) {
+  PersistParams pq{};
+  bool persistent = false;
+  ST(persistent_eligible(ctx, &pq, &persistent));
+  // the persistent path is four launches in all: nothing for a graph to amortise
+  if (!ctx->use_graph || ctx->profiling || persistent) {
     uint64_t nk = 0;
     ST(enqueue_plan(ctx, iters, noise_mode, &nk));
     ctx->launches += nk;
@@ -593,6 +675,8 @@ doapp_status doapp_create(const doapp_config *cfg, doapp_ctx **out) {
   ctx->S = (uint64_t)cfg->num_climbers * cfg->samples_per_climber;
   const char *ng = getenv("DOAPP_NO_GRAPH");
   ctx->use_graph = !(ng && ng[0] == '1');
+  const char *psv = getenv("DOAPP_PERSIST");
+  ctx->persist_mode = (psv && (psv[0] == '0' || psv[0] == '1')) ? psv[0] - '0' : -1;
   const char *pkv = getenv("DOAPP_PK");
   ctx->pk_mode = (pkv && (pkv[0] == '0' || pkv[0] == '1')) ? pkv[0] - '0' : -1;
   const char *xd = getenv("DOAPP_EXACT_DIV");
@@ -659,7 +743,7 @@ void doapp_destroy(doapp_ctx *ctx) {
   release(ctx->pts); release(ctx->coll); release(ctx->final_coll); release(ctx->keys);
   release(ctx->keys_float); release(ctx->cur_hi); release(ctx->found); release(ctx->grid_cells);
   release(ctx->lookup_coll); release(ctx->lookup_idx); release(ctx->dbg_a); release(ctx->dbg_b);
-  release(ctx->dbg_c); release(ctx->vbad); release(ctx->usum);
+  release(ctx->dbg_c); release(ctx->vbad); release(ctx->usum); release(ctx->pkeys); release(ctx->pbar);
   for (cudaEvent_t e : ctx->prof_events) cudaEventDestroy(e);
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->ev1) cudaEventDestroy(ctx->ev1);
@@ -1209,7 +1293,7 @@ doapp_status doapp_plan_profile(doapp_ctx *ctx, uint32_t iters, float *cost_ms_t
     return fail(ctx, DOAPP_INVALID_ARG, "doapp_plan_profile: staged noise covers %u iterations",
                 ctx->plan_iters);
   CU(cudaSetDevice(ctx->cfg.device));
-  while (ctx->prof_events.size() < 2 * (size_t)iters) {
+  while (ctx->prof_events.size() < 2 * (size_t)(iters ? iters : 1)) {
     cudaEvent_t e = nullptr;
     CU(cudaEventCreate(&e));
     ctx->prof_events.push_back(e);
@@ -1223,13 +1307,14 @@ doapp_status doapp_plan_profile(doapp_ctx *ctx, uint32_t iters, float *cost_ms_t
   CU(cudaEventRecord(ctx->ev1, ctx->stream));
   CU(cudaStreamSynchronize(ctx->stream));
   float total = 0.0f;
-  for (uint32_t it = 0; it < iters; ++it) {
+  const uint32_t timed = ctx->prof_launches; // iters launches, or 1 persistent launch
+  for (uint32_t it = 0; it < timed; ++it) {
     float ms = 0.0f;
     CU(cudaEventElapsedTime(&ms, ctx->prof_events[2 * it], ctx->prof_events[2 * it + 1]));
     total += ms;
   }
   if (cost_ms_total) *cost_ms_total = total;
-  if (cost_launches) *cost_launches = iters;
+  if (cost_launches) *cost_launches = timed;
   if (loop_ms) CU(cudaEventElapsedTime(loop_ms, ctx->ev0, ctx->ev1));
   ctx->plan_pending = true;
   return DOAPP_OK;

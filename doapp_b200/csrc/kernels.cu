@@ -570,6 +570,217 @@ __global__ void __launch_bounds__(kMaxCostThreads)
   }
 }
 
+// ================================================================ persistent planner kernel
+// Small problems (BASELINE config 2: 1024 samples x 64 waypoints) are latency-bound: a launch
+// per iteration costs more than the iteration's arithmetic.  Like the reference's
+// optimize_trajectories (generate_trajectories.cu:197-253: one launch, loop inside), this kernel
+// runs the whole keep-best loop in one cooperative launch: a CTA owns a few samples with
+// 2^t_log2 threads each (one or a few waypoints per thread), the trajectory stays in shared
+// memory across iterations, and one grid-wide barrier per iteration publishes the argmin key.
+// Arithmetic, noise, keys and tie-breaking are those of cost_kernel, so the result is
+// bit-identical to the launch-per-iteration path.
+__device__ __forceinline__ void grid_arrive(unsigned int *counter) {
+  __threadfence();
+  atomicAdd(counter, 1u);
+}
+__device__ __forceinline__ void grid_wait(const unsigned int *counter, unsigned int target) {
+  unsigned int v;
+  do {
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(counter) : "memory");
+  } while (v < target);
+}
+
+template <int D, int GM, bool LIM>
+__global__ void __launch_bounds__(256) plan_persistent_kernel(const __grid_constant__ PersistParams Q) {
+  const CostParams &P = Q.cost;
+  constexpr bool FIDX = GM == GM_U8_CDG || GM == GM_F32_CDG;
+  extern __shared__ __align__(16) float smem[];
+  const uint32_t T = 1u << Q.t_log2, SB = blockDim.x >> Q.t_log2;
+  const uint32_t WS = T * P.wpp; // waypoint slots per sample (>= n)
+  float *sbase = smem;                                   // [D][npad]  current trajectory
+  float *spart = sbase + (size_t)D * P.npad;             // [SB][WS]   per-waypoint sum of acc^2
+  float *slim = spart + (size_t)SB * WS;                 // [SB][WS]   (limits)
+  float *seps = slim + (LIM ? (size_t)SB * WS : 0);      // [SB][8]    this iteration's noise
+  float *swin = seps + (size_t)SB * 8;                   // [8]        winner's noise
+  int *scoll = (int *)(swin + 8);                        // [SB]
+  unsigned long long *skey = (unsigned long long *)(scoll + ((SB + 1) & ~1u)); // [1] CTA minimum
+
+  const uint32_t c = blockIdx.y, k = gridDim.y;
+  const uint32_t s = threadIdx.x >> Q.t_log2, r = threadIdx.x & (T - 1);
+  uint32_t t = blockIdx.x * SB + s;
+  const bool active = t < P.m;
+  t = active ? t : P.m - 1;
+  const uint32_t tg = (uint32_t)(P.sample_offset + t);
+  const unsigned int num_ctas = gridDim.x * gridDim.y;
+
+  float start[D];
+#pragma unroll
+  for (int j = 0; j < D; ++j) start[j] = __ldg(P.start + j);
+  for (uint32_t i = threadIdx.x; i < (uint32_t)D * P.npad; i += blockDim.x)
+    sbase[i] = __ldg(P.traj + (size_t)c * D * P.npad + i);
+  if (threadIdx.x < SB) scoll[threadIdx.x] = 0;
+  if (threadIdx.x == 0) *skey = kKeyNone;
+  // the seed pass scored the unperturbed trajectory (generate_trajectories.cu:180-191)
+  uint32_t cur_hi = (uint32_t)(__ldg(P.pend_keys + c) >> 32);
+  bool found = false;
+
+  // one d-vector of noise per sample and iteration (generate_trajectories.cu:37-44): the
+  // sample's first three threads draw one Box-Muller pair each
+  auto gen_noise = [&](uint32_t it) {
+    if (P.noise_mode == NOISE_PHILOX) {
+      if (T >= 4) {
+        if (r < 3) {
+          float a, b;
+          dm::noise_pair(P.seed_lo, P.seed_hi, P.sigma, it, c, tg, 0, r, &a, &b);
+          if (2 * r < D) seps[s * 8 + 2 * r] = a;
+          if (2 * r + 1 < D) seps[s * 8 + 2 * r + 1] = b;
+        }
+      } else if (r == 0) {
+        float e[D];
+        dm::noise_vec<D>(P.seed_lo, P.seed_hi, P.sigma, it, c, tg, 0, e);
+#pragma unroll
+        for (int j = 0; j < D; ++j) seps[s * 8 + j] = e[j];
+      }
+    } else if (r == 0) {
+#pragma unroll
+      for (int j = 0; j < D; ++j)
+        seps[s * 8 + j] =
+            P.noise_mode == NOISE_EXTERNAL
+                ? __ldg(Q.noise_base + (size_t)it * Q.noise_iter_stride +
+                        ((size_t)c * P.noise_m + (size_t)(tg - P.noise_t0)) * D + j)
+                : 0.0f;
+    }
+  };
+  gen_noise(0);
+  __syncthreads();
+
+  const uint32_t w0 = r * P.wpp;
+  const uint32_t w1 = (w0 + P.wpp) < P.n ? (w0 + P.wpp) : P.n;
+  for (uint32_t it = 0; it < Q.iters; ++it) {
+    float eps[D];
+#pragma unroll
+    for (int j = 0; j < D; ++j) eps[j] = seps[s * 8 + j];
+    auto noisy = [&](uint32_t w, int j) -> float { return dm::add_(sbase[j * P.npad + w], eps[j]); };
+    uint32_t w = w0;
+    float xprev[D], vprev[D];
+    bool fine1 = P.fast_ok != 0, fine2 = fine1;
+    if (w == 0) {
+#pragma unroll
+      for (int j = 0; j < D; ++j) {
+        xprev[j] = vprev[j] = start[j];
+        fine1 = fine1 & dm::fine_angle(start[j]);
+      }
+    } else if (w < P.n) {
+#pragma unroll
+      for (int j = 0; j < D; ++j) {
+        const float x1 = noisy(w - 1, j);
+        const float x2 = w >= 2 ? noisy(w - 2, j) : start[j];
+        xprev[j] = x1;
+        vprev[j] = dm::div_fast(dm::sub_(x1, x2), P.dt_div);
+        fine1 = fine1 & dm::fine_angle(x1);
+        fine2 = fine2 & dm::fine_angle(x2);
+      }
+    }
+    int coll = 0;
+    for (; w < w1; ++w) {
+      float x[D], vnew[D];
+#pragma unroll
+      for (int j = 0; j < D; ++j) x[j] = noisy(w, j);
+      float a2, l2;
+      int cw;
+      const bool fine0 = waypoint_cost<D, GM, FIDX, LIM, true>(P, x, xprev, vprev, vnew, &a2, &l2, &cw);
+      const bool fast_valid = fine0 & fine1 & fine2;
+      fine2 = fine1;
+      fine1 = fine0 & (P.fast_ok != 0);
+      if (!fast_valid) {
+        WpIn<D> in;
+#pragma unroll
+        for (int j = 0; j < D; ++j) {
+          in.x[j] = x[j];
+          in.xprev[j] = xprev[j];
+          in.vprev[j] = vprev[j];
+        }
+        const WpOut<D> o = waypoint_cost_general<D, GM, FIDX, LIM>(P, in);
+#pragma unroll
+        for (int j = 0; j < D; ++j) vnew[j] = o.vnew[j];
+        a2 = o.a2;
+        l2 = o.l2;
+        cw = o.coll;
+      }
+#pragma unroll
+      for (int j = 0; j < D; ++j) {
+        xprev[j] = x[j];
+        vprev[j] = vnew[j];
+      }
+      coll += cw;
+      spart[s * WS + w] = a2;
+      if (LIM) slim[s * WS + w] = l2;
+    }
+    if (coll) atomicAdd(scoll + s, coll); // integer: order-independent
+    __syncthreads();
+    if (r == 0) { // fixed order: left fold over the waypoints (oracle ORC_SUM_WAYPOINT)
+      float total = 0.0f, ltotal = 0.0f;
+      for (uint32_t ww = 0; ww < P.n; ++ww) {
+        total = dm::add_(total, spart[s * WS + ww]);
+        if (LIM) ltotal = dm::add_(ltotal, slim[s * WS + ww]);
+      }
+      const int ctot = scoll[s];
+      scoll[s] = 0;
+      float score = dm::add_((float)ctot, dm::mul_(P.smooth_scale, total));
+      if (LIM && P.limit_weight != 0.0f) score = dm::add_(score, dm::mul_(P.limit_weight, ltotal));
+      if (active)
+        atomicMin(skey, ((unsigned long long)key_hi(P.select_mode, score) << 32) | tg);
+    }
+    __syncthreads();
+    unsigned long long *kcur = Q.keys3 + (size_t)(it % 3) * k;
+    if (threadIdx.x == 0) {
+      atomicMin(kcur + c, *skey);
+      *skey = kKeyNone;
+      // re-arm the buffer of iteration it + 1: its last readers passed barrier it - 1
+      if (blockIdx.x == 0) Q.keys3[(size_t)((it + 1) % 3) * k + c] = kKeyNone;
+      grid_arrive(Q.barrier);
+    }
+    if (it + 1 < Q.iters) gen_noise(it + 1); // overlaps the barrier
+    if (threadIdx.x == 0) grid_wait(Q.barrier, (it + 1) * num_ctas);
+    __syncthreads();
+    // keep-best (generate_trajectories.cu:225-241, D5/D6 fixed): every CTA applies it to its copy
+    const unsigned long long best = __ldcg(kcur + c);
+    const uint32_t hi = (uint32_t)(best >> 32), win = (uint32_t)best;
+    if (hi < cur_hi) { // block-uniform
+      cur_hi = hi;
+      found = true;
+      if (threadIdx.x < 3) {
+        float a = 0.0f, b = 0.0f;
+        const uint32_t q = threadIdx.x;
+        if (P.noise_mode == NOISE_PHILOX) {
+          dm::noise_pair(P.seed_lo, P.seed_hi, P.sigma, it, c, win, 0, q, &a, &b);
+        } else if (P.noise_mode == NOISE_EXTERNAL) {
+          const float *pn = Q.noise_base + (size_t)it * Q.noise_iter_stride +
+                            ((size_t)c * P.noise_m + (size_t)(win - P.noise_t0)) * D;
+          a = 2 * q < D ? __ldg(pn + 2 * q) : 0.0f;
+          b = 2 * q + 1 < D ? __ldg(pn + 2 * q + 1) : 0.0f;
+        }
+        if (2 * q < D) swin[2 * q] = a;
+        if (2 * q + 1 < D) swin[2 * q + 1] = b;
+      }
+      __syncthreads();
+      for (uint32_t i = threadIdx.x; i < (uint32_t)D * P.npad; i += blockDim.x) {
+        const uint32_t j = i / P.npad;
+        if (i - j * P.npad < P.n) sbase[i] = dm::add_(sbase[i], swin[j]);
+      }
+      __syncthreads();
+    }
+  }
+  if (blockIdx.x == 0) { // the climber's final state, for the final scoring pass
+    for (uint32_t i = threadIdx.x; i < (uint32_t)D * P.npad; i += blockDim.x)
+      P.traj_next[(size_t)c * D * P.npad + i] = sbase[i];
+    if (threadIdx.x == 0) {
+      P.cur_hi_out[c] = cur_hi;
+      P.found_better[c] = found ? 1 : 0;
+    }
+  }
+}
+
 // ===================================================== packed (two samples per thread) path
 // For launches with one thread per sample, the thread walks its waypoints two at a time and
 // all fp32 arithmetic is issued as packed fma.rn.f32x2 (FFMA2 / FADD2 / FMUL2), waypoint w in
@@ -1104,6 +1315,75 @@ static int grid_mode_of(const CostParams &p) {
     if (p.grid.frame == 0 && p.grid.fast_idx) gm = p.grid.kind == 1 ? GM_U8_CDG : GM_F32_CDG;
   }
   return gm;
+}
+
+// ---- persistent planner: kernel selection, geometry, cooperative launch
+template <int D>
+static const void *persistent_kernel_of(int gm, bool lim) {
+#define DOAPP_PP(GMV) \
+  return lim ? (const void *)plan_persistent_kernel<D, GMV, true> : (const void *)plan_persistent_kernel<D, GMV, false>
+  switch (gm) {
+  case GM_U8_CDG: DOAPP_PP(GM_U8_CDG);
+  case GM_F32_CDG: DOAPP_PP(GM_F32_CDG);
+  case GM_GENERIC: DOAPP_PP(GM_GENERIC);
+  default: DOAPP_PP(GM_NONE);
+  }
+#undef DOAPP_PP
+}
+
+static size_t persistent_smem(const CostParams &p, int d, uint32_t T, uint32_t wpp) {
+  const uint32_t SB = 256 / T, WS = T * wpp;
+  size_t f = (size_t)d * p.npad + (size_t)SB * WS * (p.use_limits ? 2 : 1) + (size_t)SB * 8 + 8 +
+             ((SB + 1) & ~1u) + 2;
+  return f * sizeof(float);
+}
+
+cudaError_t persistent_plan_config(const CostParams &p, int d, int sm_count, PersistParams *q,
+                                   bool *ok) {
+  *ok = false;
+  if (p.k == 0 || p.m == 0 || p.n_noise != 1) return cudaSuccess;
+  const void *kern = d == 5 ? persistent_kernel_of<5>(grid_mode_of(p), p.use_limits != 0)
+                            : persistent_kernel_of<4>(grid_mode_of(p), p.use_limits != 0);
+  // fewest waypoints per thread (shortest dependent chain) whose grid is co-resident
+  for (uint32_t wpp = 1; wpp <= 4; wpp *= 2) {
+    const uint32_t need = (p.n + wpp - 1) / wpp;
+    uint32_t tl = 0;
+    while ((1u << tl) < need) ++tl;
+    if (tl > 8) continue;
+    const uint32_t T = 1u << tl, SB = 256 / T;
+    const size_t smem = persistent_smem(p, d, T, wpp);
+    if (smem > 200 * 1024) continue;
+    if (smem > 48 * 1024) {
+      cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e != cudaSuccess) return e;
+    }
+    int per_sm = 0;
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 256, smem);
+    if (e != cudaSuccess) return e;
+    const uint64_t ctas = (uint64_t)p.k * ((p.m + SB - 1) / SB);
+    if (ctas > (uint64_t)per_sm * sm_count) continue;
+    q->cost = p;
+    q->cost.res_div = dm::FastDiv{p.grid.res, p.grid.res_rcp, 0.0f, 0.0f};
+    q->cost.wpp = wpp;
+    q->t_log2 = tl;
+    *ok = true;
+    return cudaSuccess;
+  }
+  return cudaSuccess;
+}
+
+cudaError_t launch_persistent_plan(const PersistParams &q, int d, cudaStream_t st) {
+  const CostParams &p = q.cost;
+  const void *kern = d == 5 ? persistent_kernel_of<5>(grid_mode_of(p), p.use_limits != 0)
+                            : persistent_kernel_of<4>(grid_mode_of(p), p.use_limits != 0);
+  const uint32_t T = 1u << q.t_log2, SB = 256 / T;
+  const size_t smem = persistent_smem(p, d, T, p.wpp);
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+  }
+  void *args[] = {(void *)&q};
+  return cudaLaunchCooperativeKernel(kern, dim3((p.m + SB - 1) / SB, p.k), dim3(256), args, smem, st);
 }
 
 template <int D>

@@ -92,6 +92,20 @@ struct CostParams {
   uint32_t parts_log2, pw_log2, wpp;
 };
 
+// Persistent planner loop (plan_persistent_kernel): the whole keep-best loop of
+// generate_trajectories.cu:197-253 in ONE cooperative launch, one grid-wide barrier per
+// iteration.  `cost` carries the problem (traj = input half, traj_next = output half,
+// pend_keys = the seed pass's keys, cur_hi_out / found_better = final state).
+struct PersistParams {
+  CostParams cost;
+  uint32_t iters;
+  uint32_t t_log2;             // threads per sample = 2^t_log2, each owning cost.wpp waypoints
+  unsigned long long *keys3;   // [3][k] rotating per-iteration argmin keys (all kKeyNone at launch)
+  unsigned int *barrier;       // monotonic arrival counter, 0 at launch
+  const float *noise_base;     // external noise of iteration 0 (or nullptr: Philox)
+  uint64_t noise_iter_stride;  // elements between iterations in the external buffer
+};
+
 struct FinalParams {
   const float *traj; // [k][d][npad]
   const float *start;
@@ -127,6 +141,10 @@ struct ScatterParams {
 cudaError_t launch_cost(const CostParams &p, int d, int sm_count, cudaStream_t st);
 cudaError_t launch_verify_div(dm::FastDiv d, uint32_t lo_bits, uint32_t hi_bits, int mode,
                               unsigned long long *bad, int sm_count, cudaStream_t st);
+// geometry + co-residency check; *ok = false when the problem does not fit one cooperative wave
+cudaError_t persistent_plan_config(const CostParams &p, int d, int sm_count, PersistParams *q,
+                                   bool *ok);
+cudaError_t launch_persistent_plan(const PersistParams &q, int d, cudaStream_t st);
 cudaError_t launch_update_vector(const UpdateParams &p, int sm_count, cudaStream_t st);
 cudaError_t launch_final(const FinalParams &p, cudaStream_t st);
 cudaError_t launch_scatter(const ScatterParams &p, int sm_count, cudaStream_t st);

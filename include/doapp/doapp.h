@@ -257,7 +257,8 @@ DOAPP_API doapp_status doapp_plan_bench(doapp_ctx *ctx, uint32_t iters, uint32_t
 
 /* Profiling hook: one un-graphed pass of the staged planner loop with a CUDA
  * event pair around every cost-kernel launch on the ctx stream; returns the
- * summed cost-kernel time, the number of launches and the whole loop's time. */
+ * summed cost-kernel time, the number of launches (iters, or 1 when the whole loop
+ * runs as one persistent cooperative launch) and the whole loop's time. */
 DOAPP_API doapp_status doapp_plan_profile(doapp_ctx *ctx, uint32_t iters, float *cost_ms_total,
                                           uint32_t *cost_launches, float *loop_ms);
 

@@ -121,14 +121,19 @@ def test_replan_dynamic_matches_stepwise(capi, oracle_mod):
     ctx.close()
 
 
-@pytest.mark.parametrize("env", ["DOAPP_NO_GRAPH", "DOAPP_EXACT_DIV", "DOAPP_PK"])
-def test_alternate_paths_bit_identical(capi, monkeypatch, env):
+@pytest.mark.parametrize("env,persist", [("DOAPP_NO_GRAPH", "0"), ("DOAPP_EXACT_DIV", "0"),
+                                         ("DOAPP_EXACT_DIV", "1"), ("DOAPP_PK", "0"),
+                                         ("DOAPP_PERSIST", None)])
+def test_alternate_paths_bit_identical(capi, monkeypatch, env, persist):
     """The un-graphed launch path, the IEEE-divide kernels and the packed two-waypoints-per-step
-    kernel (fma.rn.f32x2) give the same bits as the default path."""
+    kernel (fma.rn.f32x2) give the same bits as the default path; so do the persistent
+    one-launch planner (DOAPP_PERSIST=1) and the launch-per-iteration graph (=0)."""
     k, m, n, iters = 3, 200, 64, 6
     init = capi.plan_lerp(synth.START, synth.GOALS[1], n)
     g = synth.box_grid(64, 0.02)
     out = []
+    if persist is not None:
+        monkeypatch.setenv("DOAPP_PERSIST", persist)
     for flag in ("0", "1"):
         monkeypatch.setenv(env, flag)
         with capi.Context(k=k, m=m, n=n, sigma=0.05) as ctx:
