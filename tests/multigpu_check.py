@@ -25,10 +25,24 @@ def main():
     torch.cuda.set_device(lr)
     dev = torch.device("cuda", lr)
     dist.init_process_group("nccl", device_id=dev)
+    for mode_kw in (dict(), dict(update_mode=1, update_gain=1e-3)):
+        check(rank, world, lr, dev, mode_kw)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def check(rank, world, lr, dev, mode_kw):
+    """keep-best (8*k-byte MIN all-reduce per iteration) or weighted update (plus one exact
+    int64 SUM all-reduce of the fixed-point update-vector sums)."""
+    import torch
+    import torch.distributed as dist
+    from doapp_b200 import capi, sharding
+    from tests import synth
+    import oracle
     k, mg, n, iters = 2, 1000, 64, 8
     off, cnt = sharding.shard_range(mg, rank, world)
     ctx = capi.Context(k=k, m=cnt, n=n, device=lr, sigma=0.05, select_mode=1, sample_offset=off,
-                       global_samples_per_climber=mg)
+                       global_samples_per_climber=mg, **mode_kw)
     uid = torch.zeros(capi.COMM_ID_BYTES, dtype=torch.uint8, device=dev)
     if rank == 0:
         uid = torch.frombuffer(bytearray(capi.comm_unique_id()), dtype=torch.uint8).to(dev)
@@ -53,22 +67,21 @@ def main():
     dist.all_reduce(hi, op=dist.ReduceOp.MAX)
     assert torch.equal(lo, hi), "ranks disagree on the kept trajectories"
     if rank == 0:
-        one = capi.Context(k=k, m=mg, n=n, device=lr, sigma=0.05, select_mode=1)
+        one = capi.Context(k=k, m=mg, n=n, device=lr, sigma=0.05, select_mode=1, **mode_kw)
         one.set_grid(grid, 0.01)
         r1 = one.plan(start, goal, init, iters)
         s1 = one.plan_state()
         one.close()
         assert np.array_equal(s1["trajectories"].view(np.uint32), st["trajectories"].view(np.uint32))
         assert np.float32(r1["best_score"]) == np.float32(r["best_score"])
-        orc = oracle.Oracle(k=k, m=mg, n=n, sigma=0.05, select_mode=1)
+        orc = oracle.Oracle(k=k, m=mg, n=n, sigma=0.05, select_mode=1, **mode_kw)
         orc.set_grid(grid, 0.01)
         ro = orc.plan(start, init, iters, threads=8)
         assert np.array_equal(ro["trajectories"].view(np.uint32), st["trajectories"].view(np.uint32))
         assert np.array_equal(ro["best_traj"].view(np.uint32), r["best_traj"].view(np.uint32))
-        print(f"multigpu_check ok: world={world} best_score={r['best_score']:.6f} "
+        print(f"multigpu_check ok: world={world} mode={mode_kw} best_score={r['best_score']:.6f} "
               f"found_better={st['found_better'].tolist()}", flush=True)
     dist.barrier()
-    dist.destroy_process_group()
 
 
 if __name__ == "__main__":
