@@ -251,8 +251,11 @@ def run_ours(args, w, rank, world, local_rank):
             ctx.grid_alloc(capi.GRID_U8, capi.FRAME_CDG, grid.shape[2], grid.shape[1],
                            grid.shape[0], w["res"])
         ctx.grid_broadcast(0)
+        from doapp_b200 import sharding
+        peer = sharding.connect_peers(ctx, rank, world, dev) if not os.environ.get("DOAPP_NO_PEER") else False
     else:
         ctx.set_grid(grid, w["res"])
+        peer = False
 
     # pinned host staging for the e2e leg
     h_start = torch.from_numpy(start.copy()).pin_memory().numpy()
@@ -278,6 +281,7 @@ def run_ours(args, w, rank, world, local_rank):
         flush_l2()
         ms_total += ctx.plan_bench(iters, 1)
     launches = ctx.launch_count() - l0
+    persistent = launches <= 8 * args.steps  # seed + persistent loop + final pass + selection
     barrier()
     ms_total = max_over_ranks(ms_total)
     clocks = sampler.stop()
@@ -327,7 +331,12 @@ def run_ours(args, w, rank, world, local_rank):
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": w["desc"], "samples_per_gpu": m, "waypoints": n, "joints": D,
                    "iterations_per_step": iters, "grid": f"{w['grid_n']}^3 u8",
-                   "parallelism": f"samples sharded over {world} GPU(s), grid replicated",
+                   "parallelism": f"samples sharded over {world} GPU(s), grid replicated"
+                                  + (", argmin keys merged in-kernel through NVLink peer mailboxes"
+                                     if peer and persistent else
+                                     (", NCCL MIN all-reduce per iteration" if world > 1 else "")),
+                   "planner": "one persistent cooperative launch per plan" if persistent
+                              else "one cost launch per iteration (CUDA graph)",
                    "l2": "flushed between steps (256 MiB write); within a step the grid is "
                          "L2-resident by design"},
         "iterations_per_sec": iters / (ms_step * 1e-3),

@@ -22,6 +22,7 @@ UPDATE_KEEP_BEST, UPDATE_WEIGHTED = 0, 1
 GRID_NONE, GRID_U8, GRID_F32 = 0, 1, 2
 FRAME_CDG, FRAME_OG = 0, 1
 COMM_ID_BYTES = 128
+PEER_HANDLE_BYTES = 64
 
 # every symbol include/doapp/doapp.h declares (checked by tests/test_abi.py)
 ABI_SYMBOLS = [
@@ -31,7 +32,7 @@ ABI_SYMBOLS = [
     "doapp_set_limits", "doapp_noise_generate", "doapp_cost_eval", "doapp_stage_inputs",
     "doapp_cost_eval_dev", "doapp_read_results", "doapp_plan_lerp", "doapp_plan",
     "doapp_plan_async", "doapp_plan_wait", "doapp_plan_state", "doapp_replan_dynamic",
-    "doapp_plan_bench", "doapp_plan_profile", "doapp_probe_gather", "doapp_comm_unique_id", "doapp_comm_init", "doapp_grid_broadcast",
+    "doapp_plan_bench", "doapp_plan_profile", "doapp_probe_gather", "doapp_peer_export", "doapp_peer_import", "doapp_comm_unique_id", "doapp_comm_init", "doapp_grid_broadcast",
     "doapp_launch_count", "doapp_debug_sincos", "doapp_debug_fk",
 ]
 
@@ -104,6 +105,8 @@ def load_library(path: str | None = None) -> C.CDLL:
     L.doapp_plan_bench.argtypes = [vp, C.c_uint32, C.c_uint32, vp]
     L.doapp_plan_profile.argtypes = [vp, C.c_uint32, vp, vp, vp]
     L.doapp_probe_gather.argtypes = [vp, C.c_size_t, C.c_uint32, vp]
+    L.doapp_peer_export.argtypes = [vp, vp]
+    L.doapp_peer_import.argtypes = [vp, vp, C.c_int32, C.c_int32]
     L.doapp_comm_unique_id.argtypes = [vp]
     L.doapp_comm_init.argtypes = [vp, vp, C.c_int32, C.c_int32]
     L.doapp_grid_broadcast.argtypes = [vp, C.c_int32]
@@ -324,6 +327,20 @@ class Context:
     def comm_init(self, uid: bytes, rank: int, nranks: int):
         buf = (C.c_uint8 * COMM_ID_BYTES).from_buffer_copy(uid)
         self._ck(self.L.doapp_comm_init(self.h, buf, rank, nranks))
+
+    def peer_export(self) -> bytes:
+        buf = (C.c_uint8 * PEER_HANDLE_BYTES)()
+        self._ck(self.L.doapp_peer_export(self.h, buf))
+        return bytes(buf)
+
+    def peer_import(self, handles: bytes, rank: int, nranks: int):
+        assert len(handles) == PEER_HANDLE_BYTES * nranks
+        buf = (C.c_uint8 * len(handles)).from_buffer_copy(handles)
+        self._ck(self.L.doapp_peer_import(self.h, buf, rank, nranks))
+
+    def peer_disable(self):
+        """Back to the NCCL per-iteration merge (a peer failed to map the mailboxes)."""
+        self._ck(self.L.doapp_peer_import(self.h, None, 0, 0))
 
     def grid_broadcast(self, root=0):
         self._ck(self.L.doapp_grid_broadcast(self.h, root))

@@ -90,6 +90,12 @@ struct doapp_ctx {
   DevBuf<unsigned long long> pkeys; // persistent planner: 3 x [k] rotating keys
   DevBuf<unsigned int> pbar;        // ... and its grid barrier counter
   int persist_mode = -1;            // DOAPP_PERSIST=0/1: never / whenever legal
+  // peer-memory argmin merge: own mailbox [2 epochs][3][k][8] + result [3][k], the ranks' mailboxes
+  DevBuf<unsigned long long> mailbox, presult;
+  unsigned long long *peer_mbox[8] = {};
+  bool peer_ready = false;
+  int peer_rank = 0, peer_nranks = 1;
+  uint64_t peer_epoch = 0; // persistent multi-rank launches so far (same on every rank)
   DevBuf<long long> usum; // weighted update: 2 x [k][8] integer sums (ping-pong)
   // Ping-pong state of the planner: traj holds two [k][d][npad] halves, cur_hi two [k]
   // halves, keys three [k] buffers (read / write / being re-armed).  Every launch that
@@ -338,9 +344,10 @@ doapp_status upload_start(doapp_ctx *ctx, const float *start) {
 doapp_status persistent_eligible(doapp_ctx *ctx, PersistParams *q, bool *ok) {
   *ok = false;
   const doapp_config &c = ctx->cfg;
-  if (ctx->persist_mode == 0 || ctx->comm || c.update_mode != DOAPP_UPDATE_KEEP_BEST ||
-      c.noise_waypoints != 1)
+  if (ctx->persist_mode == 0 || c.update_mode != DOAPP_UPDATE_KEEP_BEST || c.noise_waypoints != 1)
     return DOAPP_OK;
+  // several ranks: only with the peer mailboxes mapped (doapp_peer_import), else NCCL per iteration
+  if (ctx->comm && !(ctx->peer_ready && ctx->peer_nranks == ctx->nranks)) return DOAPP_OK;
   CostParams p = base_cost_params(ctx);
   CU(persistent_plan_config(p, c.waypoint_dim, ctx->sm_count, q, ok));
   return DOAPP_OK;
@@ -372,6 +379,19 @@ doapp_status enqueue_plan_persistent(doapp_ctx *ctx, PersistParams q, uint32_t i
   q.barrier = ctx->pbar.p;
   q.noise_base = noise_mode == NOISE_EXTERNAL ? ctx->noise.p : nullptr;
   q.noise_iter_stride = (uint64_t)c.num_climbers * ctx->m_global * c.waypoint_dim;
+  q.nranks = 1;
+  q.rank = 0;
+  if (ctx->comm && ctx->peer_ready) {
+    // mailbox set of this launch (sets alternate per launch; the kernel re-arms the other one)
+    const size_t set = 3 * k * 8;
+    q.nranks = (uint32_t)ctx->peer_nranks;
+    q.rank = (uint32_t)ctx->peer_rank;
+    for (int r = 0; r < ctx->peer_nranks; ++r) q.mailbox[r] = ctx->peer_mbox[r] + (ctx->peer_epoch & 1) * set;
+    q.mailbox_next = ctx->mailbox.p + ((ctx->peer_epoch + 1) & 1) * set;
+    q.result = ctx->presult.p;
+    CU(cudaMemsetAsync(ctx->presult.p, 0xFF, sizeof(unsigned long long) * 3 * k, ctx->stream));
+    ctx->peer_epoch++;
+  }
   if (ctx->profiling) CU(cudaEventRecord(ctx->prof_events[0], ctx->stream));
   CU(launch_persistent_plan(q, c.waypoint_dim, ctx->stream));
   if (ctx->profiling) CU(cudaEventRecord(ctx->prof_events[1], ctx->stream));
@@ -744,6 +764,9 @@ void doapp_destroy(doapp_ctx *ctx) {
   release(ctx->keys_float); release(ctx->cur_hi); release(ctx->found); release(ctx->grid_cells);
   release(ctx->lookup_coll); release(ctx->lookup_idx); release(ctx->dbg_a); release(ctx->dbg_b);
   release(ctx->dbg_c); release(ctx->vbad); release(ctx->usum); release(ctx->pkeys); release(ctx->pbar);
+  for (int r = 0; r < 8; ++r)
+    if (ctx->peer_ready && r != ctx->peer_rank && ctx->peer_mbox[r]) cudaIpcCloseMemHandle(ctx->peer_mbox[r]);
+  release(ctx->mailbox); release(ctx->presult);
   for (cudaEvent_t e : ctx->prof_events) cudaEventDestroy(e);
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->ev1) cudaEventDestroy(ctx->ev1);
@@ -1352,6 +1375,52 @@ doapp_status doapp_probe_gather(doapp_ctx *ctx, size_t array_bytes, uint32_t cel
 }
 
 // ------------------------------------------------------------------- multi-GPU
+
+doapp_status doapp_peer_export(doapp_ctx *ctx, uint8_t handle[DOAPP_PEER_HANDLE_BYTES]) {
+  if (!ctx) return DOAPP_INVALID_ARG;
+  if (!handle) return fail(ctx, DOAPP_INVALID_ARG, "doapp_peer_export: null handle");
+  static_assert(sizeof(cudaIpcMemHandle_t) <= DOAPP_PEER_HANDLE_BYTES, "IPC handle size");
+  CU(cudaSetDevice(ctx->cfg.device));
+  const size_t k = ctx->cfg.num_climbers, elems = 2 * 3 * k * 8;
+  ST(ensure(ctx, ctx->mailbox, elems));
+  ST(ensure(ctx, ctx->presult, 3 * k));
+  CU(cudaMemsetAsync(ctx->mailbox.p, 0xFF, elems * sizeof(unsigned long long), ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  cudaIpcMemHandle_t h;
+  CU(cudaIpcGetMemHandle(&h, ctx->mailbox.p));
+  memset(handle, 0, DOAPP_PEER_HANDLE_BYTES);
+  memcpy(handle, &h, sizeof(h));
+  return DOAPP_OK;
+}
+
+doapp_status doapp_peer_import(doapp_ctx *ctx, const uint8_t *handles, int32_t rank,
+                               int32_t nranks) {
+  if (!ctx) return DOAPP_INVALID_ARG;
+  if (!handles && nranks == 0) { // disable: back to the NCCL merge
+    ctx->peer_ready = false;
+    return DOAPP_OK;
+  }
+  if (!handles || nranks < 1 || nranks > 8 || rank < 0 || rank >= nranks)
+    return fail(ctx, DOAPP_INVALID_ARG, "doapp_peer_import: bad argument (1..8 ranks)");
+  if (!ctx->mailbox.p) return fail(ctx, DOAPP_NOT_READY, "doapp_peer_import: call doapp_peer_export first");
+  CU(cudaSetDevice(ctx->cfg.device));
+  for (int r = 0; r < nranks; ++r) {
+    if (r == rank) {
+      ctx->peer_mbox[r] = ctx->mailbox.p;
+      continue;
+    }
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handles + (size_t)r * DOAPP_PEER_HANDLE_BYTES, sizeof(h));
+    void *p = nullptr;
+    CU(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    ctx->peer_mbox[r] = (unsigned long long *)p;
+  }
+  ctx->peer_rank = rank;
+  ctx->peer_nranks = nranks;
+  ctx->peer_ready = true;
+  ctx->peer_epoch = 0;
+  return DOAPP_OK;
+}
 
 doapp_status doapp_comm_unique_id(uint8_t id[DOAPP_COMM_ID_BYTES]) {
   if (!id) return DOAPP_INVALID_ARG;

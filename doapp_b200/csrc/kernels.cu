@@ -604,6 +604,7 @@ __global__ void __launch_bounds__(256) plan_persistent_kernel(const __grid_const
   float *swin = seps + (size_t)SB * 8;                   // [8]        winner's noise
   int *scoll = (int *)(swin + 8);                        // [SB]
   unsigned long long *skey = (unsigned long long *)(scoll + ((SB + 1) & ~1u)); // [1] CTA minimum
+  unsigned long long *sbest = skey + 1;                                        // [1] merged minimum
 
   const uint32_t c = blockIdx.y, k = gridDim.y;
   const uint32_t s = threadIdx.x >> Q.t_log2, r = threadIdx.x & (T - 1);
@@ -651,6 +652,10 @@ __global__ void __launch_bounds__(256) plan_persistent_kernel(const __grid_const
                 : 0.0f;
     }
   };
+  // the mailbox set of the NEXT launch: nobody writes it before this rank's last key of this
+  // launch has left
+  if (Q.nranks > 1 && blockIdx.x == 0 && threadIdx.x < 24)
+    Q.mailbox_next[((size_t)(threadIdx.x >> 3) * k + c) * 8 + (threadIdx.x & 7)] = kKeyNone;
   gen_noise(0);
   __syncthreads();
 
@@ -741,10 +746,44 @@ __global__ void __launch_bounds__(256) plan_persistent_kernel(const __grid_const
       grid_arrive(Q.barrier);
     }
     if (it + 1 < Q.iters) gen_noise(it + 1); // overlaps the barrier
-    if (threadIdx.x == 0) grid_wait(Q.barrier, (it + 1) * num_ctas);
-    __syncthreads();
+    unsigned long long best;
+    if (Q.nranks <= 1) {
+      if (threadIdx.x == 0) grid_wait(Q.barrier, (it + 1) * num_ctas);
+      __syncthreads();
+      best = __ldcg(kcur + c);
+    } else {
+      // The climber's first CTA waits for the rank's CTAs, then stores the rank's key into the
+      // mailbox of every rank (its own included): one 8-byte store per peer over NVLink,
+      // payload = flag.  EVERY CTA polls the rank's own mailbox -- local memory -- for the
+      // nranks keys of this iteration and takes the minimum.  Buffers rotate three ways; the
+      // slots of iteration it + 1 are re-armed before this rank's key of iteration it leaves,
+      // so no peer can be writing them yet and no local CTA is still reading them.
+      const size_t cur = ((size_t)(it % 3) * k + c) * 8;
+      if (blockIdx.x == 0 && threadIdx.x < 32) {
+        const uint32_t ln = threadIdx.x;
+        if (ln == 0) grid_wait(Q.barrier, (it + 1) * num_ctas);
+        __syncwarp();
+        if (ln < Q.nranks) {
+          const unsigned long long local = __ldcg(kcur + c);
+          Q.mailbox[Q.rank][((size_t)((it + 1) % 3) * k + c) * 8 + ln] = kKeyNone;
+          asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(Q.mailbox[ln] + cur + Q.rank), "l"(local) : "memory");
+        }
+      }
+      if (threadIdx.x < 32) {
+        unsigned long long v = kKeyNone;
+        if (threadIdx.x < Q.nranks) {
+          const unsigned long long *mine = Q.mailbox[Q.rank] + cur + threadIdx.x;
+          do {
+            asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(mine) : "memory");
+          } while (v == kKeyNone);
+        }
+        v = warp_min_u64(v);
+        if (threadIdx.x == 0) *sbest = v;
+      }
+      __syncthreads();
+      best = *sbest;
+    }
     // keep-best (generate_trajectories.cu:225-241, D5/D6 fixed): every CTA applies it to its copy
-    const unsigned long long best = __ldcg(kcur + c);
     const uint32_t hi = (uint32_t)(best >> 32), win = (uint32_t)best;
     if (hi < cur_hi) { // block-uniform
       cur_hi = hi;
@@ -1334,7 +1373,7 @@ static const void *persistent_kernel_of(int gm, bool lim) {
 static size_t persistent_smem(const CostParams &p, int d, uint32_t T, uint32_t wpp) {
   const uint32_t SB = 256 / T, WS = T * wpp;
   size_t f = (size_t)d * p.npad + (size_t)SB * WS * (p.use_limits ? 2 : 1) + (size_t)SB * 8 + 8 +
-             ((SB + 1) & ~1u) + 2;
+             ((SB + 1) & ~1u) + 4;
   return f * sizeof(float);
 }
 

@@ -104,6 +104,15 @@ struct PersistParams {
   unsigned int *barrier;       // monotonic arrival counter, 0 at launch
   const float *noise_base;     // external noise of iteration 0 (or nullptr: Philox)
   uint64_t noise_iter_stride;  // elements between iterations in the external buffer
+  // Multi-GPU (nranks > 1): the ranks' argmin keys are merged through peer memory over NVLink
+  // inside the kernel, no NCCL call per iteration.  mailbox[r] is rank r's mailbox (own one
+  // included), laid out [3][k][nranks]; rank s stores its key of iteration it for climber c in
+  // mailbox[r][(it % 3)][c][s] (stride 8 ranks) of every rank r and polls its own.  result [3][k] republishes the
+  // merged key to the rank's other CTAs.  All slots are kKeyNone when the kernel starts.
+  uint32_t nranks, rank;
+  unsigned long long *mailbox[8];
+  unsigned long long *mailbox_next; // own mailbox set of the NEXT launch, re-armed at kernel start
+  unsigned long long *result;
 };
 
 struct FinalParams {

@@ -46,3 +46,33 @@ def pack_keys(scores: np.ndarray, sample_offset: int, select_mode: int) -> np.nd
 def unpack_key(key) -> tuple[int, int]:
     key = int(key)
     return key >> 32, key & 0xFFFFFFFF
+
+
+def connect_peers(ctx, rank: int, world: int, device) -> bool:
+    """Maps the ranks' argmin mailboxes into each other (doapp_peer_export / doapp_peer_import):
+    gathers the CUDA IPC handles over torch.distributed and synchronises once.  Returns False
+    (the NCCL per-iteration path stays in use) if peer mapping is not possible on this box."""
+    import torch
+    import torch.distributed as dist
+    ok = 1
+    try:
+        handle = ctx.peer_export()
+    except Exception:  # noqa: BLE001 - any failure means "no peer path"
+        handle, ok = bytes(64), 0
+    mine = torch.frombuffer(bytearray(handle), dtype=torch.uint8).to(device)
+    table = [torch.zeros_like(mine) for _ in range(world)]
+    dist.all_gather(table, mine)
+    flag = torch.tensor([ok], device=device)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    if int(flag.item()) == 1:
+        try:
+            ctx.peer_import(b"".join(bytes(t.cpu().numpy().tobytes()) for t in table), rank, world)
+        except Exception:  # noqa: BLE001
+            ok = 0
+    else:
+        ok = 0
+    flag = torch.tensor([ok], device=device)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)  # all ranks take the same path, and a barrier
+    if int(flag.item()) != 1 and ok == 1:
+        ctx.peer_disable()
+    return int(flag.item()) == 1

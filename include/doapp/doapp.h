@@ -281,6 +281,19 @@ DOAPP_API doapp_status doapp_comm_init(doapp_ctx *ctx, const uint8_t id[DOAPP_CO
                                        int32_t rank, int32_t nranks);
 DOAPP_API doapp_status doapp_grid_broadcast(doapp_ctx *ctx, int32_t root);
 
+/* Peer-memory argmin merge (NVLink P2P).  With the ranks' mailboxes mapped into each other,
+ * the persistent planner kernel trades the per-iteration argmin keys itself -- one 8-byte
+ * store per peer and iteration, inside the kernel -- instead of one NCCL all-reduce launch
+ * per iteration.  Each rank exports a CUDA IPC handle of its mailbox, the caller gathers
+ * the handles of all ranks (any transport; same role as the NCCL unique id above) and every
+ * rank imports the full table, then all ranks synchronise once on the host before the first
+ * doapp_plan.  At most 8 ranks (one NVSwitch domain).  Optional: without it multi-rank plans
+ * use the NCCL path; doapp_peer_import(ctx, NULL, 0, 0) switches back to it. */
+#define DOAPP_PEER_HANDLE_BYTES 64
+DOAPP_API doapp_status doapp_peer_export(doapp_ctx *ctx, uint8_t handle[DOAPP_PEER_HANDLE_BYTES]);
+DOAPP_API doapp_status doapp_peer_import(doapp_ctx *ctx, const uint8_t *handles /*[nranks][64]*/,
+                                         int32_t rank, int32_t nranks);
+
 /* ---- introspection ----------------------------------------------------- */
 
 /* Number of kernels this ctx has launched since creation (bench `gpu_launches`). */

@@ -25,13 +25,13 @@ def main():
     torch.cuda.set_device(lr)
     dev = torch.device("cuda", lr)
     dist.init_process_group("nccl", device_id=dev)
-    for mode_kw in (dict(), dict(update_mode=1, update_gain=1e-3)):
-        check(rank, world, lr, dev, mode_kw)
+    for mode_kw, peers in ((dict(), False), (dict(), True), (dict(update_mode=1, update_gain=1e-3), False)):
+        check(rank, world, lr, dev, mode_kw, peers)
     dist.barrier()
     dist.destroy_process_group()
 
 
-def check(rank, world, lr, dev, mode_kw):
+def check(rank, world, lr, dev, mode_kw, peers):
     """keep-best (8*k-byte MIN all-reduce per iteration) or weighted update (plus one exact
     int64 SUM all-reduce of the fixed-point update-vector sums)."""
     import torch
@@ -54,6 +54,7 @@ def check(rank, world, lr, dev, mode_kw):
     else:
         ctx.grid_alloc(capi.GRID_U8, capi.FRAME_CDG, 128, 128, 128, 0.01)
     ctx.grid_broadcast(0)
+    peer_ok = sharding.connect_peers(ctx, rank, world, dev) if peers else False
     assert np.array_equal(ctx.grid_download((128, 128, 128)), grid), "grid broadcast differs"
     start, goal = synth.START, synth.GOALS[1]
     init = capi.plan_lerp(start, goal, n)
@@ -79,7 +80,7 @@ def check(rank, world, lr, dev, mode_kw):
         ro = orc.plan(start, init, iters, threads=8)
         assert np.array_equal(ro["trajectories"].view(np.uint32), st["trajectories"].view(np.uint32))
         assert np.array_equal(ro["best_traj"].view(np.uint32), r["best_traj"].view(np.uint32))
-        print(f"multigpu_check ok: world={world} mode={mode_kw} best_score={r['best_score']:.6f} "
+        print(f"multigpu_check ok: world={world} mode={mode_kw} peer_mailboxes={peer_ok} best_score={r['best_score']:.6f} "
               f"found_better={st['found_better'].tolist()}", flush=True)
     dist.barrier()
 
