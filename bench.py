@@ -281,7 +281,8 @@ def run_ours(args, w, rank, world, local_rank):
         flush_l2()
         ms_total += ctx.plan_bench(iters, 1)
     launches = ctx.launch_count() - l0
-    persistent = launches <= 8 * args.steps  # seed + persistent loop + final pass + selection
+    persistent = bool(ctx.plan_mode() & 1)
+    peer = bool(ctx.plan_mode() & 2)
     barrier()
     ms_total = max_over_ranks(ms_total)
     clocks = sampler.stop()

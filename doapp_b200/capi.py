@@ -28,12 +28,12 @@ PEER_HANDLE_BYTES = 64
 ABI_SYMBOLS = [
     "doapp_config_init", "doapp_version", "doapp_status_str", "doapp_create", "doapp_destroy",
     "doapp_last_error", "doapp_grid_alloc", "doapp_grid_upload", "doapp_grid_download",
-    "doapp_grid_from_msg", "doapp_grid_scatter", "doapp_grid_scatter_dev", "doapp_grid_lookup",
+    "doapp_grid_from_msg", "doapp_grid_from_depth", "doapp_grid_scatter", "doapp_grid_scatter_dev", "doapp_grid_lookup",
     "doapp_set_limits", "doapp_noise_generate", "doapp_cost_eval", "doapp_stage_inputs",
     "doapp_cost_eval_dev", "doapp_read_results", "doapp_plan_lerp", "doapp_plan",
     "doapp_plan_async", "doapp_plan_wait", "doapp_plan_state", "doapp_replan_dynamic",
     "doapp_plan_bench", "doapp_plan_profile", "doapp_probe_gather", "doapp_peer_export", "doapp_peer_import", "doapp_comm_unique_id", "doapp_comm_init", "doapp_grid_broadcast",
-    "doapp_launch_count", "doapp_debug_sincos", "doapp_debug_fk",
+    "doapp_plan_mode", "doapp_launch_count", "doapp_debug_sincos", "doapp_debug_fk",
 ]
 
 
@@ -105,11 +105,15 @@ def load_library(path: str | None = None) -> C.CDLL:
     L.doapp_plan_bench.argtypes = [vp, C.c_uint32, C.c_uint32, vp]
     L.doapp_plan_profile.argtypes = [vp, C.c_uint32, vp, vp, vp]
     L.doapp_probe_gather.argtypes = [vp, C.c_size_t, C.c_uint32, vp]
+    L.doapp_grid_from_depth.argtypes = [vp, vp, C.c_uint32, C.c_uint32, C.c_uint32, vp, vp, C.c_double,
+                                        C.c_int8, C.c_int, vp]
     L.doapp_peer_export.argtypes = [vp, vp]
     L.doapp_peer_import.argtypes = [vp, vp, C.c_int32, C.c_int32]
     L.doapp_comm_unique_id.argtypes = [vp]
     L.doapp_comm_init.argtypes = [vp, vp, C.c_int32, C.c_int32]
     L.doapp_grid_broadcast.argtypes = [vp, C.c_int32]
+    L.doapp_plan_mode.argtypes = [vp]
+    L.doapp_plan_mode.restype = C.c_uint32
     L.doapp_launch_count.argtypes = [vp]
     L.doapp_launch_count.restype = C.c_uint64
     L.doapp_debug_sincos.argtypes = [vp, f32p, C.c_size_t, f32p, f32p]
@@ -317,6 +321,18 @@ class Context:
                                              C.addressof(ms)))
         return dict(best_traj=bt, best_score=bs.value, elapsed_ms=ms.value)
 
+    def grid_from_depth(self, depth, intrinsics, extrinsics, crop_size, val=1, clear_first=True) -> int:
+        """depth [cams][h][w] uint16 mm; intrinsics [cams][4] f64 fx,fy,cx,cy; extrinsics [cams][12] f32.
+        Returns the number of points that passed the crop box."""
+        depth = np.ascontiguousarray(depth, np.uint16)
+        intr = np.ascontiguousarray(intrinsics, np.float64)
+        extr = np.ascontiguousarray(extrinsics, np.float32)
+        cams, h, w = depth.shape
+        kept = C.c_uint64()
+        self._ck(self.L.doapp_grid_from_depth(self.h, _p(depth), cams, w, h, _p(intr), _p(extr),
+                                              float(crop_size), val, int(clear_first), C.addressof(kept)))
+        return int(kept.value)
+
     def probe_gather(self, array_bytes: int, cell_bytes: int = 1) -> float:
         """Random single-cell loads per second from a scratch array (roofline denominator)."""
         out = C.c_double()
@@ -346,6 +362,10 @@ class Context:
         self._ck(self.L.doapp_grid_broadcast(self.h, root))
 
     # -- introspection -----------------------------------------------------
+    def plan_mode(self) -> int:
+        """bit 0: persistent one-launch planner; bit 1: in-kernel peer-mailbox argmin merge."""
+        return int(self.L.doapp_plan_mode(self.h))
+
     def launch_count(self) -> int:
         return int(self.L.doapp_launch_count(self.h))
 

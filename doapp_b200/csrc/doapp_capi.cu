@@ -103,6 +103,7 @@ struct doapp_ctx {
   int traj_s = 0, cur_s = 0, key_w = -1;
   size_t traj_half = 0; // elements per trajectory half
   DevBuf<uint8_t> found, grid_cells, lookup_coll;
+  DevBuf<uint16_t> depth; // staged depth frames (doapp_grid_from_depth)
   DevBuf<long long> lookup_idx;
   DevBuf<float> dbg_a, dbg_b, dbg_c;
 
@@ -140,6 +141,7 @@ struct doapp_ctx {
   // per-launch CUDA-event timing of the cost kernel (doapp_plan_profile)
   std::vector<cudaEvent_t> prof_events;
   bool profiling = false;
+  uint32_t last_plan_mode = 0; // doapp_plan_mode
   uint32_t prof_launches = 0; // cost launches the last profiled plan timed
 
   std::vector<float> h_out;
@@ -381,7 +383,9 @@ doapp_status enqueue_plan_persistent(doapp_ctx *ctx, PersistParams q, uint32_t i
   q.noise_iter_stride = (uint64_t)c.num_climbers * ctx->m_global * c.waypoint_dim;
   q.nranks = 1;
   q.rank = 0;
+  ctx->last_plan_mode = 1;
   if (ctx->comm && ctx->peer_ready) {
+    ctx->last_plan_mode = 3;
     // mailbox set of this launch (sets alternate per launch; the kernel re-arms the other one)
     const size_t set = 3 * k * 8;
     q.nranks = (uint32_t)ctx->peer_nranks;
@@ -439,6 +443,7 @@ doapp_status enqueue_plan(doapp_ctx *ctx, uint32_t iters, int noise_mode, uint64
     if (persistent) return enqueue_plan_persistent(ctx, q, iters, noise_mode, kernels);
   }
   ctx->prof_launches = iters;
+  ctx->last_plan_mode = 0;
   reset_plan_state(ctx);
   CU(cudaMemsetAsync(ctx->keys.p, 0xFF, sizeof(unsigned long long) * 3 * k, ctx->stream));
   ST(launch_pass(ctx, climber_cost_params(ctx), PEND_NONE, 0, NOISE_ZERO, nullptr, true));
@@ -766,7 +771,7 @@ void doapp_destroy(doapp_ctx *ctx) {
   release(ctx->dbg_c); release(ctx->vbad); release(ctx->usum); release(ctx->pkeys); release(ctx->pbar);
   for (int r = 0; r < 8; ++r)
     if (ctx->peer_ready && r != ctx->peer_rank && ctx->peer_mbox[r]) cudaIpcCloseMemHandle(ctx->peer_mbox[r]);
-  release(ctx->mailbox); release(ctx->presult);
+  release(ctx->mailbox); release(ctx->presult); release(ctx->depth);
   for (cudaEvent_t e : ctx->prof_events) cudaEventDestroy(e);
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->ev1) cudaEventDestroy(ctx->ev1);
@@ -934,6 +939,55 @@ doapp_status doapp_grid_scatter(doapp_ctx *ctx, const float *xyz, size_t num_poi
     CU(cudaMemcpyAsync(ctx->cloud.p, xyz, num_points * 3 * sizeof(float), cudaMemcpyHostToDevice,
                        ctx->stream));
   return doapp_grid_scatter_dev(ctx, ctx->cloud.p, num_points, val, clear_first);
+}
+
+doapp_status doapp_grid_from_depth(doapp_ctx *ctx, const uint16_t *depth, uint32_t num_cams,
+                                   uint32_t width, uint32_t height, const double *intrinsics,
+                                   const float *extrinsics, double crop_size, int8_t val,
+                                   int clear_first, uint64_t *points_kept) {
+  if (!ctx) return DOAPP_INVALID_ARG;
+  if (!depth || !intrinsics || !extrinsics || num_cams == 0 || num_cams > 4 || !(crop_size > 0.0))
+    return fail(ctx, DOAPP_INVALID_ARG, "doapp_grid_from_depth: bad argument (1..4 cameras)");
+  if (ctx->grid.kind != DOAPP_GRID_U8)
+    return fail(ctx, DOAPP_NOT_READY, "doapp_grid_from_depth: needs a U8 grid");
+  CU(cudaSetDevice(ctx->cfg.device));
+  const size_t pixels = (size_t)num_cams * width * height;
+  ST(ensure(ctx, ctx->depth, pixels));
+  ST(ensure(ctx, ctx->vbad, 1));
+  CU(cudaMemcpyAsync(ctx->depth.p, depth, pixels * sizeof(uint16_t), cudaMemcpyHostToDevice,
+                     ctx->stream));
+  CU(cudaMemsetAsync(ctx->vbad.p, 0, sizeof(unsigned long long), ctx->stream));
+  if (clear_first) CU(cudaMemsetAsync(ctx->grid_cells.p, 0, ctx->grid_bytes, ctx->stream));
+  DepthParams p{};
+  p.depth = ctx->depth.p;
+  p.cams = num_cams;
+  p.w = width;
+  p.h = height;
+  for (uint32_t c = 0; c < num_cams; ++c) {
+    const double fx = intrinsics[4 * c], fy = intrinsics[4 * c + 1];
+    const double unit_scaling = (double)0.001f; // DepthTraits<uint16_t>::toMeters(1)
+    p.cam[c].cx = (float)intrinsics[4 * c + 2];   // mapping_node.cpp:97-98
+    p.cam[c].cy = (float)intrinsics[4 * c + 3];
+    p.cam[c].kx = (float)(unit_scaling / fx);     // :101-103
+    p.cam[c].ky = (float)(unit_scaling / fy);
+    for (int i = 0; i < 9; ++i) p.cam[c].r[i] = extrinsics[12 * c + i];
+    for (int i = 0; i < 3; ++i) p.cam[c].t[i] = extrinsics[12 * c + 9 + i];
+  }
+  const float half = (float)(crop_size / 2.0), full = (float)crop_size; // :262-263 (Vector4f)
+  p.crop_lo[0] = -half; p.crop_lo[1] = -half; p.crop_lo[2] = 0.0f;
+  p.crop_hi[0] = half;  p.crop_hi[1] = half;  p.crop_hi[2] = full;
+  p.grid = ctx->grid;
+  p.cells = ctx->grid_cells.p;
+  p.val = val;
+  p.kept = ctx->vbad.p;
+  CU(launch_depth_scatter(p, ctx->sm_count, ctx->stream));
+  ctx->launches += 1;
+  ctx->grid_generation++;
+  unsigned long long kept = 0;
+  CU(cudaMemcpyAsync(&kept, ctx->vbad.p, sizeof(kept), cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  if (points_kept) *points_kept = kept;
+  return DOAPP_OK;
 }
 
 doapp_status doapp_grid_lookup(doapp_ctx *ctx, const float *xyz, size_t num_points,
@@ -1478,6 +1532,7 @@ doapp_status doapp_grid_broadcast(doapp_ctx *ctx, int32_t root) {
 // --------------------------------------------------------------- introspection
 
 uint64_t doapp_launch_count(const doapp_ctx *ctx) { return ctx ? ctx->launches : 0; }
+uint32_t doapp_plan_mode(const doapp_ctx *ctx) { return ctx ? ctx->last_plan_mode : 0; }
 
 doapp_status doapp_debug_sincos(doapp_ctx *ctx, const float *angles, size_t count, float *sin_out,
                                 float *cos_out) {

@@ -1184,6 +1184,47 @@ __global__ void scatter_kernel(const __grid_constant__ ScatterParams P) {
   }
 }
 
+// ------------------------------------------------------- depth -> voxel kernel
+// One thread per pixel of every camera: deprojection exactly as convert_sensor_msg_to_pcl
+// (mapping_node.cpp:110-135: x = (u - cx) * depth * (0.001 / fx), z = depth * 0.001f, depth 0
+// skipped), rigid transform into the arm frame (:195; products summed left to right, then the
+// translation), crop box (:262-263, inclusive like pcl::CropBox), then the voxel is set as in
+// scatter_kernel.  The PCL VoxelGrid down-sampling of :190-191 has no counterpart: setting a
+// voxel is idempotent, so duplicates need no thinning.  Reads are 2-byte coalesced.
+__global__ void depth_scatter_kernel(const __grid_constant__ DepthParams P) {
+  const uint64_t per_cam = (uint64_t)P.w * P.h, total = per_cam * P.cams;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  unsigned long long kept = 0;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const uint32_t cam = (uint32_t)(i / per_cam);
+    const uint32_t pix = (uint32_t)(i - (uint64_t)cam * per_cam);
+    const uint32_t v = pix / P.w, u = pix - v * P.w;
+    const uint16_t d = __ldg(P.depth + i);
+    if (d == 0) continue;
+    const DepthCam &C = P.cam[cam];
+    const float df = (float)d;
+    const float x = dm::mul_(dm::mul_(dm::sub_((float)u, C.cx), df), C.kx);
+    const float y = dm::mul_(dm::mul_(dm::sub_((float)v, C.cy), df), C.ky);
+    const float z = dm::mul_(df, 0.001f);
+    float q[3];
+#pragma unroll
+    for (int a = 0; a < 3; ++a)
+      q[a] = dm::add_(dm::add_(dm::add_(dm::mul_(C.r[3 * a], x), dm::mul_(C.r[3 * a + 1], y)),
+                               dm::mul_(C.r[3 * a + 2], z)),
+                      C.t[a]);
+    const bool in = (q[0] >= P.crop_lo[0]) & (q[0] <= P.crop_hi[0]) & (q[1] >= P.crop_lo[1]) &
+                    (q[1] <= P.crop_hi[1]) & (q[2] >= P.crop_lo[2]) & (q[2] <= P.crop_hi[2]);
+    if (!in) continue;
+    kept += 1;
+    const long long idx = grid_index(P.grid, q[0], q[1], q[2]);
+    if (idx >= 0) P.cells[idx] = (uint8_t)P.val;
+  }
+  if (P.kept) {
+    kept = __reduce_add_sync(kFull, (unsigned)kept);
+    if ((threadIdx.x & 31) == 0 && kept) atomicAdd(P.kept, kept);
+  }
+}
+
 // ------------------------------------------------------------ gather probe
 // Roofline denominator for the collision lookups: independent random loads of one
 // cell each (one 32-byte sector per load) from an array of a chosen size, 8 in flight per
@@ -1517,6 +1558,16 @@ cudaError_t launch_update_vector(const UpdateParams &p, int sm_count, cudaStream
 
 cudaError_t launch_final(const FinalParams &p, cudaStream_t st) {
   final_kernel<<<1, 256, 0, st>>>(p);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_depth_scatter(const DepthParams &p, int sm_count, cudaStream_t st) {
+  const uint64_t total = (uint64_t)p.w * p.h * p.cams;
+  if (total == 0) return cudaSuccess;
+  unsigned blocks = blocks_for(total, 256);
+  const unsigned cap = (unsigned)sm_count * 8;
+  if (blocks > cap) blocks = cap;
+  depth_scatter_kernel<<<blocks, 256, 0, st>>>(p);
   return cudaGetLastError();
 }
 

@@ -139,6 +139,23 @@ struct UpdateParams {
   long long *usum; // [k][8] accumulated with integer atomics
 };
 
+// Depth images -> voxel occupancy in one pass (mapping_node.cpp:89-137 deprojection, :195
+// transform to the arm frame, :262-267 crop box, then OccupancyGrid::set per point).
+struct DepthCam {
+  float cx, cy, kx, ky; // principal point (float, :97-98) and unit_scaling / fx, / fy (:101-103)
+  float r[9], t[3];     // camera -> arm_bundle, row-major rotation + translation
+};
+struct DepthParams {
+  const uint16_t *depth; // [cams][h][w], millimetres, 0 = invalid (depth_traits)
+  uint32_t cams, w, h;
+  DepthCam cam[4];
+  float crop_lo[3], crop_hi[3]; // inclusive box in the arm frame (:262-263)
+  GridDev grid;
+  uint8_t *cells;
+  int8_t val;
+  unsigned long long *kept; // number of points that passed the crop (may be nullptr)
+};
+
 struct ScatterParams {
   const float *xyz;
   uint64_t num_points;
@@ -156,6 +173,7 @@ cudaError_t persistent_plan_config(const CostParams &p, int d, int sm_count, Per
 cudaError_t launch_persistent_plan(const PersistParams &q, int d, cudaStream_t st);
 cudaError_t launch_update_vector(const UpdateParams &p, int sm_count, cudaStream_t st);
 cudaError_t launch_final(const FinalParams &p, cudaStream_t st);
+cudaError_t launch_depth_scatter(const DepthParams &p, int sm_count, cudaStream_t st);
 cudaError_t launch_scatter(const ScatterParams &p, int sm_count, cudaStream_t st);
 cudaError_t launch_gather_probe(const void *cells, uint64_t num_cells, uint32_t cell_bytes,
                                 uint32_t blocks, uint32_t per_thread, uint32_t *sink,

@@ -165,6 +165,22 @@ DOAPP_API doapp_status doapp_grid_scatter(doapp_ctx *ctx, const float *xyz, size
                                           int8_t val, int clear_first);
 DOAPP_API doapp_status doapp_grid_scatter_dev(doapp_ctx *ctx, const float *xyz_dev,
                                               size_t num_points, int8_t val, int clear_first);
+/* Depth frames -> occupancy in one pass ("next" row of SURVEY 8f): the mapping node's
+ * deprojection (mapping/src/mapping_node.cpp:89-137: uint16 millimetres, 0 = invalid,
+ * x = (u - cx) * depth * (0.001 / fx)), its transform into the arm frame (:195, extrinsics
+ * :63-82 given here as a row-major rotation + translation, camera -> arm_bundle), its crop box
+ * (:262-263: |x|,|y| <= crop_size/2, 0 <= z <= crop_size) and OccupancyGrid::set per surviving
+ * point (occupancy_grid.cpp:47-58), fused so that no point cloud is materialised.
+ *   depth      [num_cams][height][width] uint16
+ *   intrinsics [num_cams][4] double  fx, fy, cx, cy   (image_geometry::PinholeCameraModel)
+ *   extrinsics [num_cams][12] float  r00..r22, tx, ty, tz
+ *   points_kept out (may be NULL): points that passed the crop box
+ * U8 grids only; 1..4 cameras. */
+DOAPP_API doapp_status doapp_grid_from_depth(doapp_ctx *ctx, const uint16_t *depth,
+                                             uint32_t num_cams, uint32_t width, uint32_t height,
+                                             const double *intrinsics, const float *extrinsics,
+                                             double crop_size, int8_t val, int clear_first,
+                                             uint64_t *points_kept);
 /* CPUDistanceGrid::operator() / OccupancyGrid::get(double...) on a batch of
  * points: writes the flat cell index (-1 if outside) and the collision
  * predicate for each point.  Debug / parity helper. */
@@ -296,6 +312,10 @@ DOAPP_API doapp_status doapp_peer_import(doapp_ctx *ctx, const uint8_t *handles 
 
 /* ---- introspection ----------------------------------------------------- */
 
+/* How the last planner loop ran: bit 0 = one persistent cooperative launch (else one cost
+ * launch per iteration), bit 1 = argmin keys merged in-kernel through the peer mailboxes
+ * (else, with several ranks, one NCCL all-reduce per iteration). */
+DOAPP_API uint32_t doapp_plan_mode(const doapp_ctx *ctx);
 /* Number of kernels this ctx has launched since creation (bench `gpu_launches`). */
 DOAPP_API uint64_t doapp_launch_count(const doapp_ctx *ctx);
 /* The deterministic sin/cos used by the FK kernels, evaluated ON THE DEVICE for

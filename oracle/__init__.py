@@ -91,6 +91,9 @@ def lib() -> C.CDLL:
         L.orc_plan.argtypes = [C.POINTER(Params), C.POINTER(Grid), C.c_void_p, C.c_void_p,
                                C.c_uint32] + [C.c_void_p] * 9 + [C.c_int]
         L.orc_update_vector.argtypes = [C.POINTER(Params)] + [C.c_void_p] * 3
+        L.orc_depth_scatter.argtypes = [C.POINTER(Grid), C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32,
+                                        C.c_void_p, C.c_void_p, C.c_double, C.c_int8, C.c_int]
+        L.orc_depth_scatter.restype = C.c_uint64
         L.orc_update_sums.argtypes = [C.POINTER(Params), C.c_int32, C.c_void_p, C.c_void_p,
                                       C.c_uint32, C.c_void_p]
         L.orc_update_from_sum.argtypes = [C.c_int64, C.c_int64]
@@ -213,6 +216,14 @@ class Oracle:
         return dict(best_traj=best_traj, best_vel=best_vel, best_score=best_score.value,
                     best_climber=best_climber.value, trajectories=ctraj, scores=cscores,
                     rounded=cround, found_better=fb)
+
+    def depth_scatter(self, depth, intrinsics, extrinsics, crop_size, val=1, clear_first=True) -> int:
+        depth = np.ascontiguousarray(depth, np.uint16)
+        intr = np.ascontiguousarray(intrinsics, np.float64)
+        extr = np.ascontiguousarray(extrinsics, np.float32)
+        cams, h, w = depth.shape
+        return int(lib().orc_depth_scatter(C.byref(self.g), _p(depth), cams, w, h, _p(intr), _p(extr),
+                                           float(crop_size), val, int(clear_first)))
 
     def update_vector(self, scores, noise):
         scores, noise = _f32(scores), _f32(noise)

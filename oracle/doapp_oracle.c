@@ -705,6 +705,47 @@ void orc_update_vector(const orc_params *p, const float *scores, const float *no
       }
 }
 
+uint64_t orc_depth_scatter(orc_grid *g, const uint16_t *depth, uint32_t cams, uint32_t w, uint32_t h,
+                           const double *intrinsics, const float *extrinsics, double crop_size,
+                           int8_t val, int clear_first) {
+  size_t cells = (size_t)g->nx * g->ny * g->nz;
+  if (clear_first) memset(g->cells, 0, cells);
+  const float half = (float)(crop_size / 2.0), full = (float)crop_size; /* map.cpp:262-263 */
+  uint64_t kept = 0;
+  for (uint32_t c = 0; c < cams; ++c) {
+    const double unit_scaling = (double)0.001f; /* DepthTraits<uint16_t>::toMeters(1) */
+    const float center_x = (float)intrinsics[4 * c + 2], center_y = (float)intrinsics[4 * c + 3];
+    const float constant_x = (float)(unit_scaling / intrinsics[4 * c]);     /* map.cpp:101-103 */
+    const float constant_y = (float)(unit_scaling / intrinsics[4 * c + 1]);
+    const float *r = extrinsics + 12 * c, *t = r + 9;
+    for (uint32_t v = 0; v < h; ++v)
+      for (uint32_t u = 0; u < w; ++u) {
+        uint16_t d = depth[((size_t)c * h + v) * w + u];
+        if (d == 0) continue; /* map.cpp:117-126, range_max == 0 */
+        float df = (float)d;
+        float x = ((float)u - center_x) * df; x = x * constant_x; /* map.cpp:130 */
+        float y = ((float)v - center_y) * df; y = y * constant_y; /* :131 */
+        float z = df * 0.001f;                                    /* :132 */
+        float q[3];
+        for (int a = 0; a < 3; ++a) {
+          float s = r[3 * a] * x;
+          float s1 = r[3 * a + 1] * y;
+          float s2 = r[3 * a + 2] * z;
+          s = s + s1;
+          s = s + s2;
+          q[a] = s + t[a];
+        }
+        if (!(q[0] >= -half && q[0] <= half && q[1] >= -half && q[1] <= half && q[2] >= 0.0f &&
+              q[2] <= full))
+          continue;
+        kept++;
+        int64_t idx = orc_grid_index(g, q[0], q[1], q[2]);
+        if (idx >= 0) ((uint8_t *)g->cells)[idx] = (uint8_t)val;
+      }
+  }
+  return kept;
+}
+
 void orc_update_sums(const orc_params *p, int32_t best_rounded, const float *scores,
                      const float *noise, uint32_t count, int64_t sums[8]) {
   /* gt.cu:128-132: weight = best_score / ceilf(our_score); term = weight * noise */

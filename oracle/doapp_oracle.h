@@ -94,6 +94,14 @@ int orc_grid_collides(const orc_grid *g, float x, float y, float z, float collis
 /* og.cpp:42-58 applied to every point of a cloud; returns #points inside */
 size_t orc_grid_scatter(orc_grid *g, const float *xyz, size_t num_points, int8_t val,
                         int clear_first);
+/* mapping/src/mapping_node.cpp:89-137 (deprojection of uint16 millimetre depth, 0 = invalid),
+ * :195 (rigid transform into the arm frame; products summed left to right, then the
+ * translation -- PCL/Eigen's own order is third-party and absent: unpinned), :262-263 (crop
+ * box, inclusive), then og.cpp:47-58 per point.  depth [cams][h][w]; intrinsics [cams][4]
+ * fx,fy,cx,cy; extrinsics [cams][12] r00..r22,tx,ty,tz.  Returns the points that passed the crop. */
+uint64_t orc_depth_scatter(orc_grid *g, const uint16_t *depth, uint32_t cams, uint32_t w, uint32_t h,
+                           const double *intrinsics, const float *extrinsics, double crop_size,
+                           int8_t val, int clear_first);
 /* gt.cu:391-466 */
 uint32_t orc_num_collisions(const orc_params *p, const orc_grid *g, const float *waypoint);
 

@@ -58,3 +58,34 @@ def cloud(num_points: int, iteration: int, size: float = 1.28, seed: int = 99):
     out = rng.random((num_points - nb, 3), np.float32) * size
     out[:, :2] -= size / 2
     return np.concatenate([pts, out]).astype(np.float32)
+
+
+def depth_rig(cams: int = 3, w: int = 480, h: int = 270, seed: int = 5):
+    """Synthetic RealSense-style rig (mapping/launch/cameras.launch:13-14: 480x270 depth):
+    uint16 millimetre depth frames [cams][h][w] (a far wall, a nearer box, 5 % invalid zeros),
+    pinhole intrinsics [cams][4] = fx, fy, cx, cy and camera -> arm extrinsics [cams][12]
+    (row-major rotation, translation) of cameras on a ring looking at the workspace centre."""
+    rng = np.random.Generator(np.random.Philox(key=seed))
+    depth = np.empty((cams, h, w), np.uint16)
+    intr = np.empty((cams, 4), np.float64)
+    extr = np.empty((cams, 12), np.float32)
+    target = np.array([0.0, 0.0, 0.3])
+    for c in range(cams):
+        d = 700.0 + 40.0 * rng.standard_normal((h, w))
+        v0, u0 = h // 4 + 10 * c, w // 3 + 15 * c
+        d[v0:v0 + h // 3, u0:u0 + w // 4] = 450.0 + 5.0 * rng.standard_normal((h // 3, w // 4))
+        d = np.clip(d, 1, 65535)
+        d[rng.random((h, w)) < 0.05] = 0
+        depth[c] = d.astype(np.uint16)
+        intr[c] = (240.0 + 3.0 * c, 241.5 + 2.0 * c, w / 2 - 0.5 + 0.25 * c, h / 2 - 0.5 - 0.25 * c)
+        ang = 2.0 * np.pi * c / cams + 0.3
+        pos = np.array([0.6 * np.cos(ang), 0.6 * np.sin(ang), 0.55])
+        zc = target - pos
+        zc /= np.linalg.norm(zc)                       # optical axis
+        xc = np.cross(zc, np.array([0.0, 0.0, 1.0]))
+        xc /= np.linalg.norm(xc)
+        yc = np.cross(zc, xc)
+        rot = np.stack([xc, yc, zc], axis=1)           # columns: camera axes in the arm frame
+        extr[c, :9] = rot.astype(np.float32).ravel()
+        extr[c, 9:] = pos.astype(np.float32)
+    return depth, intr, extr
