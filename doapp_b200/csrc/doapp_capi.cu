@@ -134,6 +134,14 @@ struct doapp_ctx {
   uint64_t graph_kernels = 0;
   int graph_end_traj_s = 0, graph_end_cur_s = 0, graph_end_key_w = -1;
   bool use_graph = true;
+  // cached graph of the dynamic-obstacle replan loop (doapp_replan_dynamic)
+  cudaGraphExec_t replan_exec = nullptr;
+  uint32_t replan_iters = 0;
+  size_t replan_points = 0;
+  const float *replan_cloud = nullptr;
+  const uint8_t *replan_cells = nullptr;
+  uint64_t replan_kernels = 0;
+  int replan_end[3] = {0, 0, -1};
 
   ncclComm_t comm = nullptr;
   int rank = 0, nranks = 1;
@@ -197,6 +205,10 @@ template <typename T> void release(DevBuf<T> &b) {
 }
 
 void invalidate_graph(doapp_ctx *ctx) {
+  if (ctx->replan_exec) {
+    cudaGraphExecDestroy(ctx->replan_exec);
+    ctx->replan_exec = nullptr;
+  }
   if (ctx->graph_exec) {
     cudaGraphExecDestroy(ctx->graph_exec);
     ctx->graph_exec = nullptr;
@@ -1304,33 +1316,32 @@ doapp_status doapp_replan_dynamic(doapp_ctx *ctx, const float *start, const floa
   CU(cudaStreamSynchronize(ctx->stream));
   CU(cudaEventRecord(ctx->ev0, ctx->stream));
   const size_t k = c.num_climbers;
-  reset_plan_state(ctx);
-  CU(cudaMemsetAsync(ctx->keys.p, 0xFF, sizeof(unsigned long long) * 3 * k, ctx->stream));
-  auto rebuild = [&](uint32_t it) -> doapp_status {
-    CU(cudaMemsetAsync(ctx->grid_cells.p, 0, ctx->grid_bytes, ctx->stream));
-    ScatterParams sp{};
-    sp.xyz = ctx->cloud.p + (size_t)it * num_points * 3;
-    sp.num_points = num_points;
-    sp.grid = ctx->grid;
-    sp.cells = ctx->grid_cells.p;
-    sp.val = 1;
-    CU(launch_scatter(sp, ctx->sm_count, ctx->stream));
-    if (num_points) ctx->launches += 1;
-    return DOAPP_OK;
-  };
-  for (uint32_t it = 0; it < iters; ++it) {
-    ST(rebuild(it));
-    // the world moved: apply the previous iteration's keep-best, then re-score the kept
-    // trajectories against the new grid (their key seeds cur_hi for this iteration)
-    ST(launch_pass(ctx, climber_cost_params(ctx), it ? PEND_KEEP_BEST : PEND_NONE, it ? it - 1 : 0,
-                   NOISE_PHILOX, nullptr, true));
-    CostParams p = base_cost_params(ctx);
-    p.noise_mode = NOISE_PHILOX;
-    p.iteration = it;
-    ST(launch_pass(ctx, p, PEND_SEED, 0, NOISE_PHILOX, nullptr, true));
-    ctx->launches += 2;
-  }
-  {
+  // the whole loop (per iteration: clear + scatter + re-score + cost pass) as one sequence;
+  // captured once into a CUDA graph and replayed while shapes and buffers stay the same
+  auto enqueue = [&](uint64_t *kernels) -> doapp_status {
+    uint64_t nk = 0;
+    reset_plan_state(ctx);
+    CU(cudaMemsetAsync(ctx->keys.p, 0xFF, sizeof(unsigned long long) * 3 * k, ctx->stream));
+    for (uint32_t it = 0; it < iters; ++it) {
+      CU(cudaMemsetAsync(ctx->grid_cells.p, 0, ctx->grid_bytes, ctx->stream));
+      ScatterParams sp{};
+      sp.xyz = ctx->cloud.p + (size_t)it * num_points * 3;
+      sp.num_points = num_points;
+      sp.grid = ctx->grid;
+      sp.cells = ctx->grid_cells.p;
+      sp.val = 1;
+      CU(launch_scatter(sp, ctx->sm_count, ctx->stream));
+      if (num_points) nk += 1;
+      // the world moved: apply the previous iteration's keep-best, then re-score the kept
+      // trajectories against the new grid (their key seeds cur_hi for this iteration)
+      ST(launch_pass(ctx, climber_cost_params(ctx), it ? PEND_KEEP_BEST : PEND_NONE,
+                     it ? it - 1 : 0, NOISE_PHILOX, nullptr, true));
+      CostParams p = base_cost_params(ctx);
+      p.noise_mode = NOISE_PHILOX;
+      p.iteration = it;
+      ST(launch_pass(ctx, p, PEND_SEED, 0, NOISE_PHILOX, nullptr, true));
+      nk += 2;
+    }
     CostParams p = climber_cost_params(ctx);
     p.scores = ctx->final_scores.p;
     p.collisions = ctx->final_coll.p;
@@ -1350,7 +1361,50 @@ doapp_status doapp_replan_dynamic(doapp_ctx *ctx, const float *start, const floa
     f.dt = c.delta_t;
     f.out = ctx->out.p;
     CU(launch_final(f, ctx->stream));
-    ctx->launches += 2;
+    nk += 2;
+    *kernels = nk;
+    return DOAPP_OK;
+  };
+  if (!ctx->use_graph) {
+    uint64_t nk = 0;
+    ST(enqueue(&nk));
+    ctx->launches += nk;
+  } else {
+    const bool hit = ctx->replan_exec && ctx->replan_iters == iters &&
+                     ctx->replan_points == num_points && ctx->replan_cloud == ctx->cloud.p &&
+                     ctx->replan_cells == ctx->grid_cells.p;
+    if (!hit) {
+      if (ctx->replan_exec) cudaGraphExecDestroy(ctx->replan_exec);
+      ctx->replan_exec = nullptr;
+      cudaGraph_t graph = nullptr;
+      CU(cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal));
+      uint64_t nk = 0;
+      doapp_status st = enqueue(&nk);
+      cudaError_t ce = cudaStreamEndCapture(ctx->stream, &graph);
+      if (st != DOAPP_OK) {
+        if (graph) cudaGraphDestroy(graph);
+        return st;
+      }
+      if (ce != cudaSuccess)
+        return fail(ctx, DOAPP_CUDA_ERROR, "cudaStreamEndCapture: %s", cudaGetErrorString(ce));
+      ce = cudaGraphInstantiate(&ctx->replan_exec, graph, 0);
+      cudaGraphDestroy(graph);
+      if (ce != cudaSuccess)
+        return fail(ctx, DOAPP_CUDA_ERROR, "cudaGraphInstantiate: %s", cudaGetErrorString(ce));
+      ctx->replan_iters = iters;
+      ctx->replan_points = num_points;
+      ctx->replan_cloud = ctx->cloud.p;
+      ctx->replan_cells = ctx->grid_cells.p;
+      ctx->replan_kernels = nk;
+      ctx->replan_end[0] = ctx->traj_s;
+      ctx->replan_end[1] = ctx->cur_s;
+      ctx->replan_end[2] = ctx->key_w;
+    }
+    CU(cudaGraphLaunch(ctx->replan_exec, ctx->stream));
+    ctx->traj_s = ctx->replan_end[0];
+    ctx->cur_s = ctx->replan_end[1];
+    ctx->key_w = ctx->replan_end[2];
+    ctx->launches += ctx->replan_kernels;
   }
   CU(cudaEventRecord(ctx->ev1, ctx->stream));
   ctx->plan_pending = true;

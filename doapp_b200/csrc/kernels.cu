@@ -1,21 +1,27 @@
 // kernels.cu — hand-written sm_100a kernels of the perturbator hot path.
 //
 // Stage map:
-//   cost_kernel     a1 (Philox noise, fused) + a2 perturb + a3 derivatives +
-//                   a4 FK + a5 grid gathers + a6 score + a7 per-climber argmin keys
-//                   + a7 keep-best of the previous launch, applied while staging
-//                   (generate_trajectories.cu:225-241, D5/D6 fixed)
-//   final_kernel    host argmin of planning_state.cu:113-127 + velocities
-//   scatter_kernel  a10 point cloud -> voxel occupancy (occupancy_grid.cpp:42-58)
+//   cost_kernel            a1 (Philox noise, fused) + a2 perturb + a3 derivatives + a4 FK +
+//                          a5 grid gathers + a6 score + a7 per-climber argmin keys + the pending
+//                          update of the previous launch applied while staging
+//                          (generate_trajectories.cu:225-241 keep-best, D5/D6 fixed; or the
+//                          weighted update of :117-142).  Thread = sample x run of waypoints,
+//                          1..32 threads per sample (clusters + DSMEM when > 4).
+//   cost_kernel_pk         the same pass, one thread per sample, two waypoints per step in
+//                          packed fma.rn.f32x2 (FFMA2): half the issue slots for the fp32 work
+//   plan_persistent_kernel the whole keep-best loop of :197-253 in ONE cooperative launch
+//                          (small problems), argmin keys merged across GPUs through NVLink
+//                          peer mailboxes inside the kernel
+//   update_vector_kernel   a8 compute_update_vector (:117-133), order-independent integer sums
+//   final_kernel           host argmin of planning_state.cu:113-127 + velocities
+//   scatter_kernel         a10 point cloud -> voxel occupancy (occupancy_grid.cpp:42-58)
+//   depth_scatter_kernel   depth frames -> voxel occupancy (mapping_node.cpp:89-137,195,262-263)
 //
-// Work decomposition of cost_kernel: one warp owns one sample at a time; lane l
-// owns waypoints l, l+32, l+64, ...  The noisy trajectory, velocities and
-// accelerations the reference materialises in three global arrays
-// (generate_trajectories.cu:202-210) live only in registers; neighbouring
-// waypoints are exchanged with warp shuffles.  Sums over waypoints use a fixed
-// order (lane-strided partials, then an xor butterfly) instead of the
-// reference's unordered float atomicAdd (generate_trajectories.cu:73-77), so
-// scores and the argmin are reproducible bit for bit.
+// The noisy trajectory, velocities and accelerations the reference materialises in three
+// global arrays per iteration (generate_trajectories.cu:202-210) live only in registers.  Sums
+// over waypoints use one fixed order (per-waypoint sums, left fold over the waypoints) instead
+// of the reference's unordered float atomicAdd (:73-77), so scores and the argmin are
+// reproducible bit for bit and independent of the launch geometry.
 #include "kernels.cuh"
 
 #include <cooperative_groups.h>
@@ -1173,15 +1179,51 @@ __global__ void final_kernel(const __grid_constant__ FinalParams P) {
 
 // ------------------------------------------------------------- scatter kernel
 // OccupancyGrid::set(double,double,double,val) for every point of a cloud
-// (occupancy_grid.cpp:47-58).  One thread per point, 12-byte coalesced reads,
-// one byte store; equal values make concurrent stores to a voxel benign.
-__global__ void scatter_kernel(const __grid_constant__ ScatterParams P) {
-  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
-  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < P.num_points; i += stride) {
-    float x = __ldg(P.xyz + 3 * i), y = __ldg(P.xyz + 3 * i + 1), z = __ldg(P.xyz + 3 * i + 2);
-    long long idx = grid_index(P.grid, x, y, z);
+// (occupancy_grid.cpp:47-58).  Four points per thread: three 16-byte coalesced loads bring 48
+// contiguous bytes, the index math is that of the lookups (threshold compares + verified
+// reciprocal divides when the grid has them, else grid_index), one byte store per point;
+// equal values make concurrent stores to a voxel benign.
+template <bool FAST>
+__device__ __forceinline__ void scatter_point(const ScatterParams &P, float x, float y, float z) {
+  if (FAST) {
+    const GridDev &g = P.grid;
+    const float ax = dm::add_(x, g.x_off), ay = dm::add_(y, g.y_off), az = dm::add_(z, 0.0f);
+    const bool in = (__float_as_uint(ax) < g.tx_bits) & (__float_as_uint(ay) < g.ty_bits) &
+                    (__float_as_uint(az) < g.tz_bits);
+    const dm::FastDiv rd{g.res, g.res_rcp, 0.0f, 0.0f};
+    const uint32_t ix = __float2uint_rz(dm::div_fast_unguarded(ax, rd));
+    const uint32_t iy = __float2uint_rz(dm::div_fast_unguarded(ay, rd));
+    const uint32_t iz = __float2uint_rz(dm::div_fast_unguarded(az, rd));
+    if (in) P.cells[(iz * g.ny + iy) * g.nx + ix] = (uint8_t)P.val;
+  } else {
+    const long long idx = grid_index(P.grid, x, y, z);
     if (idx >= 0) P.cells[idx] = (uint8_t)P.val;
   }
+}
+
+template <bool FAST>
+__global__ void __launch_bounds__(256) scatter_kernel(const __grid_constant__ ScatterParams P) {
+  const uint64_t groups = P.num_points / 4; // xyz is 16-byte aligned (launch_scatter checks)
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  const float4 *v = reinterpret_cast<const float4 *>(P.xyz);
+  for (uint64_t g = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; g < groups; g += stride) {
+    const float4 a = __ldg(v + 3 * g), b = __ldg(v + 3 * g + 1), c = __ldg(v + 3 * g + 2);
+    scatter_point<FAST>(P, a.x, a.y, a.z);
+    scatter_point<FAST>(P, a.w, b.x, b.y);
+    scatter_point<FAST>(P, b.z, b.w, c.x);
+    scatter_point<FAST>(P, c.y, c.z, c.w);
+  }
+  const uint64_t t = groups * 4 + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < P.num_points) // tail
+    scatter_point<FAST>(P, __ldg(P.xyz + 3 * t), __ldg(P.xyz + 3 * t + 1), __ldg(P.xyz + 3 * t + 2));
+}
+
+// unaligned clouds: one point per thread
+template <bool FAST>
+__global__ void scatter_kernel_scalar(const __grid_constant__ ScatterParams P) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < P.num_points; i += stride)
+    scatter_point<FAST>(P, __ldg(P.xyz + 3 * i), __ldg(P.xyz + 3 * i + 1), __ldg(P.xyz + 3 * i + 2));
 }
 
 // ------------------------------------------------------- depth -> voxel kernel
@@ -1573,10 +1615,24 @@ cudaError_t launch_depth_scatter(const DepthParams &p, int sm_count, cudaStream_
 
 cudaError_t launch_scatter(const ScatterParams &p, int sm_count, cudaStream_t st) {
   if (p.num_points == 0) return cudaSuccess;
-  unsigned blocks = blocks_for(p.num_points, 256);
-  unsigned cap = (unsigned)sm_count * 8;
-  if (blocks > cap) blocks = cap;
-  scatter_kernel<<<blocks, 256, 0, st>>>(p);
+  const bool fast = p.grid.frame == 0 && p.grid.fast_idx;
+  const bool aligned = ((uintptr_t)p.xyz & 15u) == 0;
+  const unsigned cap = (unsigned)sm_count * 8;
+  if (aligned) {
+    unsigned blocks = blocks_for((p.num_points + 3) / 4, 256);
+    if (blocks > cap) blocks = cap;
+    if (fast)
+      scatter_kernel<true><<<blocks, 256, 0, st>>>(p);
+    else
+      scatter_kernel<false><<<blocks, 256, 0, st>>>(p);
+  } else {
+    unsigned blocks = blocks_for(p.num_points, 256);
+    if (blocks > cap) blocks = cap;
+    if (fast)
+      scatter_kernel_scalar<true><<<blocks, 256, 0, st>>>(p);
+    else
+      scatter_kernel_scalar<false><<<blocks, 256, 0, st>>>(p);
+  }
   return cudaGetLastError();
 }
 

@@ -83,6 +83,12 @@ def test_scatter_parity(capi, oracle_mod, frame, n, res):
     assert np.array_equal(ctx.grid_download((n, n, n)), orc.cells)
     ctx.scatter(np.zeros((0, 3), np.float32), 1, True)
     assert ctx.grid_download((n, n, n)).sum() == 0
+    orc.scatter(np.zeros((0, 3), np.float32), 1, True)
+    for cnt in (1, 3, 5, 4099):  # tails of the four-points-per-thread loads
+        p3 = synth.cloud(cnt + 10, 11 + cnt, size=n * res)[:cnt]
+        ctx.scatter(p3, 2, False)
+        orc.scatter(p3, 2, False)
+        assert np.array_equal(ctx.grid_download((n, n, n)), orc.cells)
     ctx.close()
 
 
