@@ -15,6 +15,7 @@
 #include <dlfcn.h>
 #include <new>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include <cuda_runtime.h>
@@ -999,6 +1000,43 @@ doapp_status doapp_grid_from_depth(doapp_ctx *ctx, const uint16_t *depth, uint32
   CU(cudaMemcpyAsync(&kept, ctx->vbad.p, sizeof(kept), cudaMemcpyDeviceToHost, ctx->stream));
   CU(cudaStreamSynchronize(ctx->stream));
   if (points_kept) *points_kept = kept;
+  return DOAPP_OK;
+}
+
+doapp_status doapp_grid_distance_field(doapp_ctx *ctx) {
+  if (!ctx) return DOAPP_INVALID_ARG;
+  if (ctx->grid.kind != DOAPP_GRID_U8)
+    return fail(ctx, DOAPP_NOT_READY, "doapp_grid_distance_field: needs a U8 grid");
+  const GridDev &g0 = ctx->grid;
+  if (g0.nx > kEdtMaxDim || g0.ny > kEdtMaxDim || g0.nz > kEdtMaxDim)
+    return fail(ctx, DOAPP_INVALID_ARG, "doapp_grid_distance_field: dimensions above %u", kEdtMaxDim);
+  CU(cudaSetDevice(ctx->cfg.device));
+  const size_t cells = (size_t)g0.nx * g0.ny * g0.nz;
+  DevBuf<int32_t> ta, tb;
+  DevBuf<uint8_t> dist;
+  doapp_status st = [&]() -> doapp_status {
+    ST(ensure(ctx, ta, cells));
+    ST(ensure(ctx, tb, cells));
+    ST(ensure(ctx, dist, cells * sizeof(float)));
+    CU(launch_distance_field(ctx->grid_cells.p, g0.nx, g0.ny, g0.nz, g0.res, ta.p, tb.p,
+                             (float *)dist.p, ctx->stream));
+    ctx->launches += 3;
+    CU(cudaStreamSynchronize(ctx->stream));
+    return DOAPP_OK;
+  }();
+  release(ta);
+  release(tb);
+  if (st != DOAPP_OK) {
+    release(dist);
+    return st;
+  }
+  std::swap(ctx->grid_cells, dist); // the distance field replaces the occupancy cells
+  release(dist);
+  ctx->grid.cells = ctx->grid_cells.p;
+  ctx->grid.kind = DOAPP_GRID_F32;
+  ctx->grid_bytes = cells * sizeof(float);
+  ctx->grid_generation++;
+  invalidate_graph(ctx);
   return DOAPP_OK;
 }
 

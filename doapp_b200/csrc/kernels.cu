@@ -1226,6 +1226,107 @@ __global__ void scatter_kernel_scalar(const __grid_constant__ ScatterParams P) {
     scatter_point<FAST>(P, __ldg(P.xyz + 3 * i), __ldg(P.xyz + 3 * i + 1), __ldg(P.xyz + 3 * i + 2));
 }
 
+// ------------------------------------------------- Euclidean distance transform
+// Exact EDT of the occupancy grid (oracle: orc_distance_field; replaces the host KD-tree fill
+// CPUDistanceGrid::update, cpu_distance_grid.cu:87-202).  Squared distances are integers in
+// voxel units, so the result is bit-identical to the CPU restatement.
+//
+// Rows: one warp per row.  The row's occupancy becomes a bitmask, one 32-voxel word per lane
+// (ballot); the nearest occupied voxel to the left / right of a voxel is a clz / ffs inside its
+// word or a carry from the nearest non-empty word (warp scans).  Coalesced reads and writes.
+__global__ void __launch_bounds__(128) edt_rows_kernel(const uint8_t *occ, uint32_t nx,
+                                                       uint64_t rows, int32_t *out) {
+  const uint64_t row = (uint64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int lane = threadIdx.x & 31;
+  const uint8_t *r = occ + row * nx;
+  const uint32_t chunks = (nx + 31) / 32; // <= 32 (nx <= kEdtMaxDim)
+  uint32_t mine = 0;                      // occupancy word of chunk `lane`
+  for (uint32_t c = 0; c < chunks; ++c) {
+    const uint32_t x = c * 32 + lane;
+    const uint32_t m = __ballot_sync(kFull, x < nx && __ldg(r + x) != 0);
+    if ((uint32_t)lane == c) mine = m;
+  }
+  // nearest occupied x in the chunks strictly before / after this lane's chunk
+  int lastl = mine ? lane * 32 + 31 - __clz(mine) : -kEdtInf;
+  int firstr = mine ? lane * 32 + __ffs(mine) - 1 : kEdtInf;
+  int cl = lastl, cr = firstr;
+#pragma unroll
+  for (int off = 1; off < 32; off <<= 1) {
+    const int a = __shfl_up_sync(kFull, cl, off), b = __shfl_down_sync(kFull, cr, off);
+    if (lane >= off) cl = max(cl, a);
+    if (lane + off < 32) cr = min(cr, b);
+  }
+  int carry_l = __shfl_up_sync(kFull, cl, 1), carry_r = __shfl_down_sync(kFull, cr, 1);
+  if (lane == 0) carry_l = -kEdtInf;
+  if (lane == 31) carry_r = kEdtInf;
+  for (uint32_t c = 0; c < chunks; ++c) {
+    const uint32_t m = __shfl_sync(kFull, mine, c);
+    const int kl = __shfl_sync(kFull, carry_l, c), kr = __shfl_sync(kFull, carry_r, c);
+    const int x = (int)(c * 32) + lane;
+    const uint32_t le = m & (0xFFFFFFFFu >> (31 - lane)), ge = m & (0xFFFFFFFFu << lane);
+    const int xl = le ? (int)(c * 32) + 31 - __clz(le) : kl;
+    const int xr = ge ? (int)(c * 32) + __ffs(ge) - 1 : kr;
+    const int dl = xl < 0 ? kEdtInf : x - xl, dr = xr >= kEdtInf ? kEdtInf : xr - x;
+    const int d = min(dl, dr);
+    if ((uint32_t)x < nx) out[row * nx + x] = d >= kEdtInf ? kEdtInf : d * d;
+  }
+}
+
+// Lines along y or z: one thread per line, the 32 lanes of the block on 32 consecutive x
+// (coalesced), lower-envelope scan of Meijster et al. with the line's values and the two stacks
+// in shared memory.  in/out element u of the line of lane l: base + u * stride + l.
+template <bool TO_FLOAT>
+__global__ void __launch_bounds__(32) edt_lines_kernel(const int32_t *in, void *out_v, uint32_t nx,
+                                                       uint32_t n, uint64_t stride,
+                                                       uint64_t line_stride, float res) {
+  extern __shared__ __align__(16) unsigned char edt_smem[];
+  int32_t *g = reinterpret_cast<int32_t *>(edt_smem);           // [n][32]
+  uint16_t *s = reinterpret_cast<uint16_t *>(g + (size_t)n * 32); // [n][32]
+  uint16_t *t = s + (size_t)n * 32;                              // [n][32]
+  const int lane = threadIdx.x;
+  const uint32_t x = blockIdx.x * 32 + lane;
+  const bool live = x < nx;
+  const uint64_t base = (uint64_t)blockIdx.y * line_stride + (live ? x : nx - 1);
+  for (uint32_t u = 0; u < n; ++u) g[u * 32 + lane] = __ldg(in + base + (uint64_t)u * stride);
+  auto f = [&](int xx, int i) -> long long {
+    return (long long)(xx - i) * (xx - i) + g[i * 32 + lane];
+  };
+  int q = 0;
+  s[lane] = 0;
+  t[lane] = 0;
+  for (int u = 1; u < (int)n; ++u) {
+    while (q >= 0 && f(t[q * 32 + lane], s[q * 32 + lane]) > f(t[q * 32 + lane], u)) --q;
+    if (q < 0) {
+      q = 0;
+      s[lane] = (uint16_t)u;
+    } else {
+      const long long i = s[q * 32 + lane];
+      const long long num = (long long)u * u - i * i + g[u * 32 + lane] - g[i * 32 + lane];
+      const long long den = 2 * (u - i);
+      long long w = num / den;
+      if ((num % den != 0) && (num < 0)) --w; // floor division
+      w += 1;
+      if (w < (long long)n) {
+        ++q;
+        s[q * 32 + lane] = (uint16_t)u;
+        t[q * 32 + lane] = (uint16_t)w;
+      }
+    }
+  }
+  for (int u = (int)n - 1; u >= 0; --u) {
+    const long long v = f(u, s[q * 32 + lane]);
+    if (live) {
+      if (TO_FLOAT)
+        reinterpret_cast<float *>(out_v)[base + (uint64_t)u * stride] =
+            v >= kEdtInf ? INFINITY : dm::mul_(sqrtf((float)v), res);
+      else
+        reinterpret_cast<int32_t *>(out_v)[base + (uint64_t)u * stride] = v >= kEdtInf ? kEdtInf : (int32_t)v;
+    }
+    if (u == (int)t[q * 32 + lane]) --q;
+  }
+}
+
 // ------------------------------------------------------- depth -> voxel kernel
 // One thread per pixel of every camera: deprojection exactly as convert_sensor_msg_to_pcl
 // (mapping_node.cpp:110-135: x = (u - cx) * depth * (0.001 / fx), z = depth * 0.001f, depth 0
@@ -1600,6 +1701,31 @@ cudaError_t launch_update_vector(const UpdateParams &p, int sm_count, cudaStream
 
 cudaError_t launch_final(const FinalParams &p, cudaStream_t st) {
   final_kernel<<<1, 256, 0, st>>>(p);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_distance_field(const uint8_t *occ, uint32_t nx, uint32_t ny, uint32_t nz,
+                                  float res, int32_t *tmp_a, int32_t *tmp_b, float *out,
+                                  cudaStream_t st) {
+  const uint64_t rows = (uint64_t)ny * nz;
+  edt_rows_kernel<<<(unsigned)((rows + 3) / 4), 128, 0, st>>>(occ, nx, rows, tmp_a);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  auto smem_of = [](uint32_t n) { return (size_t)n * 32 * (4 + 2 + 2); };
+  const size_t sy = smem_of(ny), sz = smem_of(nz);
+  if (sy > 48 * 1024 &&
+      (e = cudaFuncSetAttribute(edt_lines_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sy)) != cudaSuccess)
+    return e;
+  if (sz > 48 * 1024 &&
+      (e = cudaFuncSetAttribute(edt_lines_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sz)) != cudaSuccess)
+    return e;
+  // along y: lines of plane z, element stride nx
+  edt_lines_kernel<false><<<dim3((nx + 31) / 32, nz), 32, sy, st>>>(tmp_a, tmp_b, nx, ny, nx,
+                                                                  (uint64_t)nx * ny, res);
+  if ((e = cudaGetLastError()) != cudaSuccess) return e;
+  // along z: lines of row y, element stride nx * ny
+  edt_lines_kernel<true><<<dim3((nx + 31) / 32, ny), 32, sz, st>>>(tmp_b, out, nx, nz,
+                                                                 (uint64_t)nx * ny, nx, res);
   return cudaGetLastError();
 }
 

@@ -173,6 +173,13 @@ cudaError_t persistent_plan_config(const CostParams &p, int d, int sm_count, Per
 cudaError_t launch_persistent_plan(const PersistParams &q, int d, cudaStream_t st);
 cudaError_t launch_update_vector(const UpdateParams &p, int sm_count, cudaStream_t st);
 cudaError_t launch_final(const FinalParams &p, cudaStream_t st);
+// Occupancy (u8) -> exact Euclidean distance field (f32): three launches (rows, then a
+// lower-envelope scan along y and along z); tmp_a / tmp_b hold squared distances (int32).
+constexpr int kEdtInf = 1 << 29;
+constexpr uint32_t kEdtMaxDim = 768; // scan state of a line lives in shared memory
+cudaError_t launch_distance_field(const uint8_t *occ, uint32_t nx, uint32_t ny, uint32_t nz,
+                                  float res, int32_t *tmp_a, int32_t *tmp_b, float *out,
+                                  cudaStream_t st);
 cudaError_t launch_depth_scatter(const DepthParams &p, int sm_count, cudaStream_t st);
 cudaError_t launch_scatter(const ScatterParams &p, int sm_count, cudaStream_t st);
 cudaError_t launch_gather_probe(const void *cells, uint64_t num_cells, uint32_t cell_bytes,

@@ -181,6 +181,14 @@ DOAPP_API doapp_status doapp_grid_from_depth(doapp_ctx *ctx, const uint16_t *dep
                                              const double *intrinsics, const float *extrinsics,
                                              double crop_size, int8_t val, int clear_first,
                                              uint64_t *points_kept);
+/* Occupancy -> distance field ("next" row of SURVEY 8f): replaces the host KD-tree fill
+ * CPUDistanceGrid::update (cpu_distance_grid.cu:87-202, one nanoflann query per voxel on the
+ * host) by an exact Euclidean distance transform on the device.  The ctx's U8 grid becomes an
+ * F32 grid of the same frame and dimensions whose cell v holds the distance from v's centre to
+ * the centre of the nearest occupied voxel (+inf if none), so that the collision predicate is
+ * the reference's `distance <= collision_distance` (generate_trajectories.cu:389,412).
+ * Every dimension must be <= 768. */
+DOAPP_API doapp_status doapp_grid_distance_field(doapp_ctx *ctx);
 /* CPUDistanceGrid::operator() / OccupancyGrid::get(double...) on a batch of
  * points: writes the flat cell index (-1 if outside) and the collision
  * predicate for each point.  Debug / parity helper. */

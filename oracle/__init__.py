@@ -94,6 +94,8 @@ def lib() -> C.CDLL:
         L.orc_depth_scatter.argtypes = [C.POINTER(Grid), C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32,
                                         C.c_void_p, C.c_void_p, C.c_double, C.c_int8, C.c_int]
         L.orc_depth_scatter.restype = C.c_uint64
+        L.orc_distance_field.argtypes = [C.POINTER(Grid), C.c_void_p]
+        L.orc_distance_field_brute.argtypes = [C.POINTER(Grid), C.c_void_p]
         L.orc_update_sums.argtypes = [C.POINTER(Params), C.c_int32, C.c_void_p, C.c_void_p,
                                       C.c_uint32, C.c_void_p]
         L.orc_update_from_sum.argtypes = [C.c_int64, C.c_int64]
@@ -224,6 +226,12 @@ class Oracle:
         cams, h, w = depth.shape
         return int(lib().orc_depth_scatter(C.byref(self.g), _p(depth), cams, w, h, _p(intr), _p(extr),
                                            float(crop_size), val, int(clear_first)))
+
+    def distance_field(self, brute=False) -> np.ndarray:
+        """Exact Euclidean distance field [nz][ny][nx] f32 of the current U8 grid."""
+        out = np.empty((self.g.nz, self.g.ny, self.g.nx), np.float32)
+        (lib().orc_distance_field_brute if brute else lib().orc_distance_field)(C.byref(self.g), _p(out))
+        return out
 
     def update_vector(self, scores, noise):
         scores, noise = _f32(scores), _f32(noise)

@@ -705,6 +705,106 @@ void orc_update_vector(const orc_params *p, const float *scores, const float *no
       }
 }
 
+/* ---- exact Euclidean distance transform ------------------------------------------------ */
+#define ORC_EDT_INF (1 << 29)
+static int64_t orc_floordiv(int64_t a, int64_t b) { /* b > 0 */
+  int64_t q = a / b;
+  if ((a % b != 0) && (a < 0)) --q;
+  return q;
+}
+/* one line of the lower-envelope scan: g[] squared distances so far, out[] their 1-D transform */
+static void orc_edt_line(const int32_t *g, int32_t *out, int32_t n, int32_t *s, int32_t *t) {
+  int32_t q = 0;
+  s[0] = 0;
+  t[0] = 0;
+#define ORC_F(x, i) ((int64_t)((x) - (i)) * ((x) - (i)) + g[i])
+  for (int32_t u = 1; u < n; ++u) {
+    while (q >= 0 && ORC_F(t[q], s[q]) > ORC_F(t[q], u)) --q;
+    if (q < 0) {
+      q = 0;
+      s[0] = u;
+    } else {
+      int64_t i = s[q];
+      int64_t w = 1 + orc_floordiv((int64_t)u * u - i * i + g[u] - g[i], 2 * (u - i));
+      if (w < n) {
+        ++q;
+        s[q] = u;
+        t[q] = (int32_t)w;
+      }
+    }
+  }
+  for (int32_t u = n - 1; u >= 0; --u) {
+    int64_t f = ORC_F(u, s[q]);
+    out[u] = f >= ORC_EDT_INF ? ORC_EDT_INF : (int32_t)f;
+    if (u == t[q]) --q;
+  }
+#undef ORC_F
+}
+
+void orc_distance_field(const orc_grid *occ, float *out) {
+  const int32_t nx = (int32_t)occ->nx, ny = (int32_t)occ->ny, nz = (int32_t)occ->nz;
+  const size_t cells = (size_t)nx * ny * nz;
+  const uint8_t *c = (const uint8_t *)occ->cells;
+  int32_t *a = (int32_t *)malloc(sizeof(int32_t) * cells), *b = (int32_t *)malloc(sizeof(int32_t) * cells);
+  int32_t nmax = nx > ny ? nx : ny;
+  if (nz > nmax) nmax = nz;
+  int32_t *g = (int32_t *)malloc(sizeof(int32_t) * nmax * 4), *o = g + nmax, *s = o + nmax, *t = s + nmax;
+  /* along x: distance to the nearest occupied voxel of the row, squared */
+  for (size_t row = 0; row < (size_t)ny * nz; ++row) {
+    const uint8_t *r = c + row * nx;
+    int32_t *d = a + row * nx;
+    int32_t last = -ORC_EDT_INF;
+    for (int32_t x = 0; x < nx; ++x) {
+      if (r[x]) last = x;
+      d[x] = last < 0 ? ORC_EDT_INF : x - last;
+    }
+    last = ORC_EDT_INF;
+    for (int32_t x = nx - 1; x >= 0; --x) {
+      if (r[x]) last = x;
+      int32_t dr = last >= ORC_EDT_INF ? ORC_EDT_INF : last - x;
+      int32_t m = d[x] < dr ? d[x] : dr;
+      d[x] = m >= ORC_EDT_INF ? ORC_EDT_INF : m * m;
+    }
+  }
+  /* along y, then along z */
+  for (int32_t z = 0; z < nz; ++z)
+    for (int32_t x = 0; x < nx; ++x) {
+      for (int32_t y = 0; y < ny; ++y) g[y] = a[((size_t)z * ny + y) * nx + x];
+      orc_edt_line(g, o, ny, s, t);
+      for (int32_t y = 0; y < ny; ++y) b[((size_t)z * ny + y) * nx + x] = o[y];
+    }
+  const float res = (float)occ->resolution;
+  for (int32_t y = 0; y < ny; ++y)
+    for (int32_t x = 0; x < nx; ++x) {
+      for (int32_t z = 0; z < nz; ++z) g[z] = b[((size_t)z * ny + y) * nx + x];
+      orc_edt_line(g, o, nz, s, t);
+      for (int32_t z = 0; z < nz; ++z)
+        out[((size_t)z * ny + y) * nx + x] = o[z] >= ORC_EDT_INF ? INFINITY : sqrtf((float)o[z]) * res;
+    }
+  free(a);
+  free(b);
+  free(g);
+}
+
+void orc_distance_field_brute(const orc_grid *occ, float *out) {
+  const int32_t nx = (int32_t)occ->nx, ny = (int32_t)occ->ny, nz = (int32_t)occ->nz;
+  const uint8_t *c = (const uint8_t *)occ->cells;
+  const float res = (float)occ->resolution;
+  for (int32_t z = 0; z < nz; ++z)
+    for (int32_t y = 0; y < ny; ++y)
+      for (int32_t x = 0; x < nx; ++x) {
+        int64_t best = -1;
+        for (int32_t k = 0; k < nz; ++k)
+          for (int32_t j = 0; j < ny; ++j)
+            for (int32_t i = 0; i < nx; ++i)
+              if (c[((size_t)k * ny + j) * nx + i]) {
+                int64_t d = (int64_t)(x - i) * (x - i) + (int64_t)(y - j) * (y - j) + (int64_t)(z - k) * (z - k);
+                if (best < 0 || d < best) best = d;
+              }
+        out[((size_t)z * ny + y) * nx + x] = best < 0 ? INFINITY : sqrtf((float)best) * res;
+      }
+}
+
 uint64_t orc_depth_scatter(orc_grid *g, const uint16_t *depth, uint32_t cams, uint32_t w, uint32_t h,
                            const double *intrinsics, const float *extrinsics, double crop_size,
                            int8_t val, int clear_first) {

@@ -102,6 +102,14 @@ size_t orc_grid_scatter(orc_grid *g, const float *xyz, size_t num_points, int8_t
 uint64_t orc_depth_scatter(orc_grid *g, const uint16_t *depth, uint32_t cams, uint32_t w, uint32_t h,
                            const double *intrinsics, const float *extrinsics, double crop_size,
                            int8_t val, int clear_first);
+/* Occupancy -> exact Euclidean distance field ("next" row 2 of SURVEY 8f; replaces the host
+ * KD-tree fill CPUDistanceGrid::update, cdg.cu:87-202, whose per-voxel nearest-neighbour
+ * distance this computes for points = centres of the occupied voxels).  Squared distances are
+ * exact integers in voxel units (separable lower-envelope scan, Meijster et al. 2000);
+ * out[v] = sqrtf((float)d2) * resolution, +inf when the grid is empty.  occ is a U8 grid. */
+void orc_distance_field(const orc_grid *occ, float *out);
+/* the same by exhaustive search (small grids only): the check of the scan above */
+void orc_distance_field_brute(const orc_grid *occ, float *out);
 /* gt.cu:391-466 */
 uint32_t orc_num_collisions(const orc_params *p, const orc_grid *g, const float *waypoint);
 
