@@ -100,22 +100,25 @@ def make_inputs(w):
     return grid, start, goal
 
 
-def cpu_plan_rate(w, iters, threads, reps=1):
+def cpu_plan_rate(w, iters, threads, reps=1, min_seconds=0.0):
     """The oracle's planner loop (CPU restatement of the reference arithmetic) on the same
-    workload, `iters` iterations, all host threads; returns (wps/s, seconds, sample text)."""
+    workload, `iters` iterations, all host threads; repeated until `min_seconds` of CPU work have
+    been timed; returns (wps/s of the best repetition, its seconds, sample text)."""
     import oracle
     oracle.build()
     grid, start, goal = make_inputs(w)
     orc = oracle.Oracle(k=1, m=w["m"], n=w["n"], d=D, sigma=w["sigma"], select_mode=1)
     orc.set_grid(grid, w["res"])
     init = oracle.plan_lerp(start, goal, w["n"])
-    best = float("inf")
-    for _ in range(reps):
+    best, total, done = float("inf"), 0.0, 0
+    while done < reps or total < min_seconds:
         t0 = time.perf_counter()
         orc.plan(start, init, iters, None, threads=threads)
-        best = min(best, time.perf_counter() - t0)
+        dt = time.perf_counter() - t0
+        best, total, done = min(best, dt), total + dt, done + 1
     wps = w["m"] * w["n"] * iters
-    return wps / best, best, f"{iters} iterations x {w['m']} samples x {w['n']} waypoints"
+    return wps / best, best, (f"{iters} iterations x {w['m']} samples x {w['n']} waypoints, best of "
+                              f"{done} repetitions ({total:.1f} s of CPU work)")
 
 
 def run_reference(args, w, rank):
@@ -369,7 +372,7 @@ def run_ours(args, w, rank, world, local_rank):
     if rank == 0 and world == 1 and not args.no_cpu:
         threads = os.cpu_count() or 1
         cpu_iters = iters
-        val, secs, sample = cpu_plan_rate(w, cpu_iters, threads)
+        val, secs, sample = cpu_plan_rate(w, cpu_iters, threads, min_seconds=10.0)
         line["cpu_baseline"] = {"value": val, "unit": UNIT, "cores": threads, "kind": "port",
                                 "sample": sample, "seconds": secs}
     if rank == 0:

@@ -52,6 +52,7 @@ PlanningState::~PlanningState() { doapp_destroy(ctx); }
 
 void PlanningState::updateArmState(const doapp_host::JointState::ConstPtr &msg) {
   current_state = std::vector<float>(msg->position.begin(), msg->position.end());
+  reported_state = current_state;
   current_state.resize(waypoint_dim); // planning_state.cuh:32 (num_joints there, d here: D3)
   DOAPP_ASSERT(current_state.size() == waypoint_dim);
 }
@@ -131,6 +132,12 @@ void PlanningState::publish_trajectory(doapp_host::Publisher &pub) {
     point.velocities.push_back(0);
   }
   msg.points.push_back(point); // keeps the last waypoint's stamp, as in the reference
+  if (follower_joints > d) // trajectory_follower.cpp:176-178 reads 6 entries per point
+    for (auto &pt : msg.points)
+      for (size_t j = d; j < follower_joints; ++j) {
+        pt.positions.push_back(j < reported_state.size() ? reported_state[j] : 0.0f);
+        pt.velocities.push_back(0);
+      }
   pub.publish(std::move(msg));
   _have_goal = false;
 }
@@ -151,6 +158,31 @@ void PlanningState::updateOccupancyGrid(const doapp_host::OccupancyGridMsg &msg)
       doapp_grid_from_msg(ctx, msg.size, msg.granularity, msg.grid.data(), msg.grid.size());
   DOAPP_ASSERT(st == DOAPP_OK);
   have_u8_grid = true;
+}
+
+void PlanningState::updateDepthFrames(const uint16_t *depth, unsigned int num_cams,
+                                      unsigned int width, unsigned int height,
+                                      const double *intrinsics, const float *extrinsics,
+                                      double crop_size, bool clear_first) {
+  synchronize();
+  if (!have_u8_grid) {
+    doapp_status st = doapp_grid_alloc(ctx, DOAPP_GRID_U8, DOAPP_FRAME_CDG, (uint32_t)dims.length,
+                                       (uint32_t)dims.width, (uint32_t)dims.height,
+                                       dims.resolution);
+    DOAPP_ASSERT(st == DOAPP_OK);
+    have_u8_grid = true;
+  }
+  doapp_status st = doapp_grid_from_depth(ctx, depth, num_cams, width, height, intrinsics,
+                                          extrinsics, crop_size, 1, clear_first ? 1 : 0, nullptr);
+  DOAPP_ASSERT(st == DOAPP_OK);
+}
+
+void PlanningState::buildDistanceField() {
+  synchronize();
+  DOAPP_ASSERT(have_u8_grid);
+  doapp_status st = doapp_grid_distance_field(ctx);
+  DOAPP_ASSERT(st == DOAPP_OK);
+  have_u8_grid = false; // the grid now holds float distances
 }
 
 void PlanningState::updatePointCloud(const doapp_host::PointCloudXYZ &cloud, bool clear_first) {

@@ -8,6 +8,7 @@
 #pragma once
 
 #include <cstddef>
+#include <cstdint>
 #include <vector>
 
 #include "doapp/doapp.h"
@@ -54,6 +55,19 @@ public:
   // scattered into a uint8 occupancy grid of the constructor's dimensions
   void updateOccupancyGrid(const doapp_host::OccupancyGridMsg &msg);
   void updatePointCloud(const doapp_host::PointCloudXYZ &cloud, bool clear_first = true);
+  // depth frames -> occupancy in one kernel (mapping_node.cpp:89-137,195,262-263): see
+  // doapp_grid_from_depth for the argument layout
+  void updateDepthFrames(const uint16_t *depth, unsigned int num_cams, unsigned int width,
+                         unsigned int height, const double *intrinsics, const float *extrinsics,
+                         double crop_size, bool clear_first = true);
+  // occupancy -> exact Euclidean distance field: what updateDistanceGrid(KDTree) was meant to
+  // produce on the host (cpu_distance_grid.cu:87-202); the sphere test of gt.cu:412 then applies
+  void buildDistanceField();
+  // The follower indexes positions[i] / velocities[i] for i < 6 servo ids
+  // (dynamixel_driver/src/trajectory_follower.cpp:176-178,194-199) while the planner emits d
+  // entries per point: with n > d the published points are padded to n entries,
+  // holding the extra servos at their last reported position with zero velocity.
+  void setFollowerJoints(unsigned int n) { follower_joints = n; }
   void setIterations(unsigned int iters) { iterations = iters; }
   float last_cost() const { return last_best_score; }
   doapp_ctx *handle() { return ctx; }
@@ -69,4 +83,6 @@ private:
   doapp_ctx *ctx = nullptr;
   float last_best_score = 0.0f;
   bool have_u8_grid = false;
+  unsigned int follower_joints = 0;
+  std::vector<float> reported_state; // every joint of the last joint_state message
 };

@@ -1,7 +1,7 @@
 // planning_state_test.cpp — drives PlanningState the way perturbator/src/main.cu:24-43 does
 // (joint_state + goal_state callbacks, plan(), publish_trajectory()) without ROS, and prints the
 // published JointTrajectory as JSON for tests/test_host_gpu.py to check against the oracle.
-//   planning_state_test k m n d grid_n resolution iterations cloud.bin|- 
+//   planning_state_test k m n d grid_n resolution iterations cloud.bin|- [follower_joints [edt]]
 #include <cstdio>
 #include <cstdlib>
 #include <memory>
@@ -20,6 +20,7 @@ int main(int argc, char **argv) {
   const doapp::cpu_distance_grid::Dimensions dims = {gn, gn, gn, res};
   PlanningState planning_state(k, m, n, d, dims);
   planning_state.setIterations(iters);
+  if (argc > 9) planning_state.setFollowerJoints(std::atoi(argv[9]));
 
   if (argv[8][0] != '-') { // the grid feed: an xyz cloud scattered into the grid
     FILE *f = std::fopen(argv[8], "rb");
@@ -32,6 +33,7 @@ int main(int argc, char **argv) {
     if (std::fread(cloud.xyz.data(), 1, bytes, f) != (size_t)bytes) return 3;
     std::fclose(f);
     planning_state.updatePointCloud(cloud);
+    if (argc > 10) planning_state.buildDistanceField(); // sphere test on the derived distance grid
   }
 
   auto state = std::make_shared<doapp_host::JointState>();
