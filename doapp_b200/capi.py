@@ -29,11 +29,12 @@ ABI_SYMBOLS = [
     "doapp_config_init", "doapp_version", "doapp_status_str", "doapp_create", "doapp_destroy",
     "doapp_last_error", "doapp_grid_alloc", "doapp_grid_upload", "doapp_grid_download",
     "doapp_grid_from_msg", "doapp_grid_from_depth", "doapp_grid_distance_field", "doapp_grid_scatter", "doapp_grid_scatter_dev", "doapp_grid_lookup",
-    "doapp_set_limits", "doapp_noise_generate", "doapp_cost_eval", "doapp_stage_inputs",
+    "doapp_set_limits", "doapp_fk_model_rexarm", "doapp_set_fk_model", "doapp_noise_generate", "doapp_cost_eval", "doapp_stage_inputs",
     "doapp_cost_eval_dev", "doapp_read_results", "doapp_plan_lerp", "doapp_plan",
     "doapp_plan_async", "doapp_plan_wait", "doapp_plan_state", "doapp_replan_dynamic",
     "doapp_plan_bench", "doapp_plan_profile", "doapp_probe_gather", "doapp_peer_export", "doapp_peer_import", "doapp_comm_unique_id", "doapp_comm_init", "doapp_grid_broadcast",
     "doapp_plan_mode", "doapp_launch_count", "doapp_debug_sincos", "doapp_debug_fk",
+    "doapp_debug_fk_model",
 ]
 
 
@@ -48,6 +49,20 @@ class Config(C.Structure):
         ("seed", C.c_uint64), ("sample_offset", C.c_uint64),
         ("global_samples_per_climber", C.c_uint64),
     ]
+
+
+FK_MAX_SPHERES = 16
+
+
+class FkSphere(C.Structure):
+    _fields_ = [("link", C.c_int32), ("centre", C.c_float * 3), ("radius", C.c_float)]
+
+
+class FkModel(C.Structure):
+    """doapp_fk_model: URDF joint origins / axes + per-link collision spheres."""
+    _fields_ = [("struct_size", C.c_uint32), ("joint_origin", (C.c_float * 3) * 5),
+                ("joint_axis", C.c_int32 * 5), ("num_spheres", C.c_uint32),
+                ("spheres", FkSphere * FK_MAX_SPHERES)]
 
 
 class DoappError(RuntimeError):
@@ -90,6 +105,10 @@ def load_library(path: str | None = None) -> C.CDLL:
     L.doapp_grid_scatter_dev.argtypes = [vp, vp, C.c_size_t, C.c_int8, C.c_int]
     L.doapp_grid_lookup.argtypes = [vp, f32p, C.c_size_t, vp, vp]
     L.doapp_set_limits.argtypes = [vp, f32p, f32p]
+    L.doapp_fk_model_rexarm.argtypes = [C.POINTER(FkModel)]
+    L.doapp_fk_model_rexarm.restype = None
+    L.doapp_set_fk_model.argtypes = [vp, C.POINTER(FkModel)]
+    L.doapp_debug_fk_model.argtypes = [vp, f32p, C.c_size_t, f32p]
     L.doapp_noise_generate.argtypes = [vp, C.c_uint32, f32p]
     L.doapp_cost_eval.argtypes = [vp, f32p, f32p, f32p, C.c_uint32, f32p, vp, vp, vp]
     L.doapp_stage_inputs.argtypes = [vp, f32p, f32p, f32p]
@@ -130,6 +149,12 @@ def _p(a):
 
 def _f32(a):
     return None if a is None else np.ascontiguousarray(a, dtype=np.float32)
+
+
+def fk_model_rexarm() -> FkModel:
+    m = FkModel()
+    load_library().doapp_fk_model_rexarm(C.byref(m))
+    return m
 
 
 def default_config() -> Config:
@@ -236,6 +261,18 @@ class Context:
     def set_limits(self, lo, hi):
         lo, hi = _f32(lo), _f32(hi)
         self._ck(self.L.doapp_set_limits(self.h, _p(lo), _p(hi)))
+
+    def set_fk_model(self, model):
+        """FkModel -> URDF-correct chain with per-link spheres (rexarm.urdf:61-149);
+        None -> the chain of generate_trajectories.cu:397-463."""
+        self._fk_spheres = model.num_spheres if model is not None else 0
+        self._ck(self.L.doapp_set_fk_model(self.h, C.byref(model) if model is not None else None))
+
+    def debug_fk_model(self, waypoints):
+        wp = _f32(waypoints).reshape(-1, self.d)
+        out = np.empty((wp.shape[0], self._fk_spheres, 3), np.float32)
+        self._ck(self.L.doapp_debug_fk_model(self.h, _p(wp), wp.shape[0], _p(out)))
+        return out
 
     # -- stages ------------------------------------------------------------
     def noise(self, iteration=0) -> np.ndarray:

@@ -115,6 +115,9 @@ struct doapp_ctx {
   float lim_min[kMaxJoints]{}, lim_max[kMaxJoints]{};
   int use_limits = 0;
   float rpy_s = 0.0f, rpy_c = 0.0f;
+  DevBuf<FkModelDev> fk_dev;       // doapp_set_fk_model (URDF chain + spheres); fk_on selects it
+  bool fk_on = false;
+  uint32_t fk_spheres = 0;
   dm::FastDiv dt_div{};            // verified at create (verify_fast_div)
   int pk_mode = -1;                // DOAPP_PK=0/1 forces the scalar / packed cost kernel
   bool dt_fast_ok = false;         // ... and delta_t inside [kFastDtLo, kFastDtHi]
@@ -269,6 +272,7 @@ CostParams base_cost_params(doapp_ctx *ctx) {
   p.select_mode = c.select_mode;
   p.rpy_s = ctx->rpy_s;
   p.rpy_c = ctx->rpy_c;
+  p.fk_model = ctx->fk_on ? ctx->fk_dev.p : nullptr;
   p.grid = ctx->grid;
   p.dt_div = ctx->dt_div;
   p.fast_ok = ctx->dt_fast_ok ? 1 : 0;
@@ -361,6 +365,7 @@ doapp_status persistent_eligible(doapp_ctx *ctx, PersistParams *q, bool *ok) {
   const doapp_config &c = ctx->cfg;
   if (ctx->persist_mode == 0 || c.update_mode != DOAPP_UPDATE_KEEP_BEST || c.noise_waypoints != 1)
     return DOAPP_OK;
+  if (ctx->fk_on && ctx->grid.kind != DOAPP_GRID_NONE) return DOAPP_OK; // FK model: cost_kernel only
   // several ranks: only with the peer mailboxes mapped (doapp_peer_import), else NCCL per iteration
   if (ctx->comm && !(ctx->peer_ready && ctx->peer_nranks == ctx->nranks)) return DOAPP_OK;
   CostParams p = base_cost_params(ctx);
@@ -784,7 +789,7 @@ void doapp_destroy(doapp_ctx *ctx) {
   release(ctx->dbg_c); release(ctx->vbad); release(ctx->usum); release(ctx->pkeys); release(ctx->pbar);
   for (int r = 0; r < 8; ++r)
     if (ctx->peer_ready && r != ctx->peer_rank && ctx->peer_mbox[r]) cudaIpcCloseMemHandle(ctx->peer_mbox[r]);
-  release(ctx->mailbox); release(ctx->presult); release(ctx->depth);
+  release(ctx->mailbox); release(ctx->presult); release(ctx->depth); release(ctx->fk_dev);
   for (cudaEvent_t e : ctx->prof_events) cudaEventDestroy(e);
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->ev1) cudaEventDestroy(ctx->ev1);
@@ -1076,6 +1081,96 @@ doapp_status doapp_set_limits(doapp_ctx *ctx, const float *min_d, const float *m
     ctx->use_limits = 1;
   }
   invalidate_graph(ctx);
+  return DOAPP_OK;
+}
+
+// -------------------------------------------------------------------- FK model
+
+void doapp_fk_model_rexarm(doapp_fk_model *m) {
+  if (!m) return;
+  memset(m, 0, sizeof(*m));
+  m->struct_size = sizeof(*m);
+  const float origin[5][3] = {{0.0f, -0.0015f, 0.0715f}, // rexarm.urdf:64
+                              {0.0f, 0.0f, 0.045f},      // :83
+                              {0.0f, 0.0f, 0.1f},        // :109
+                              {0.0f, 0.0f, 0.1f},        // :128
+                              {0.0f, -0.0125f, 0.08f}};  // :147
+  const int32_t axis[5] = {2, 1, 1, 1, 2};               // :65,84,110,129,148
+  memcpy(m->joint_origin, origin, sizeof(origin));
+  memcpy(m->joint_axis, axis, sizeof(axis));
+  // every link box (visual origin o, size b) gets two spheres on its long side at o -+ long/4
+  // with radius max(short sides)/2; the fingers box likewise; one sphere at gripper_center
+  struct Box { int link; double o[3]; double b[3]; };
+  const Box boxes[6] = {{0, {0.0, 0.0, 0.031}, {0.035, 0.03, 0.05}},        // :52,55
+                        {1, {0.0, 0.0, 0.086}, {0.035, 0.03, 0.05}},        // :71,74
+                        {2, {0.0, 0.0, 0.08575}, {0.032, 0.031, 0.05}},     // :97,100
+                        {3, {0.0, -0.00175, 0.0645}, {0.032, 0.05, 0.031}}, // :116,119
+                        {4, {0.0, 0.00125, 0.019}, {0.031, 0.05, 0.031}},   // :135,138
+                        {4, {0.0, 0.01, 0.07}, {0.0275, 0.01, 0.07}}};      // :180,189
+  uint32_t q = 0;
+  for (const Box &bx : boxes) {
+    int lg = 0;
+    for (int i = 1; i < 3; ++i)
+      if (bx.b[i] > bx.b[lg]) lg = i;
+    double rad = 0.0;
+    for (int i = 0; i < 3; ++i)
+      if (i != lg && bx.b[i] > rad) rad = bx.b[i];
+    for (int sgn = -1; sgn <= 1; sgn += 2) {
+      doapp_fk_sphere &sp = m->spheres[q++];
+      sp.link = bx.link;
+      for (int i = 0; i < 3; ++i) sp.centre[i] = (float)bx.o[i];
+      sp.centre[lg] = (float)(bx.o[lg] + sgn * 0.25 * bx.b[lg]);
+      sp.radius = (float)(0.5 * rad);
+    }
+  }
+  m->spheres[q++] = doapp_fk_sphere{4, {0.0f, -0.005f, 0.07f}, 0.01f}; // :197
+  m->num_spheres = q;
+}
+
+doapp_status doapp_set_fk_model(doapp_ctx *ctx, const doapp_fk_model *m) {
+  if (!ctx) return DOAPP_INVALID_ARG;
+  CU(cudaSetDevice(ctx->cfg.device));
+  CU(cudaStreamSynchronize(ctx->stream));
+  invalidate_graph(ctx);
+  if (!m) {
+    ctx->fk_on = false;
+    return DOAPP_OK;
+  }
+  if (m->struct_size != sizeof(doapp_fk_model))
+    return fail(ctx, DOAPP_INVALID_ARG, "doapp_set_fk_model: struct_size %u != %zu", m->struct_size,
+                sizeof(doapp_fk_model));
+  if (m->num_spheres == 0 || m->num_spheres > DOAPP_FK_MAX_SPHERES)
+    return fail(ctx, DOAPP_INVALID_ARG, "doapp_set_fk_model: num_spheres %u not in 1..%d",
+                m->num_spheres, DOAPP_FK_MAX_SPHERES);
+  FkModelDev h{};
+  for (int l = 0; l < 5; ++l) {
+    if (m->joint_axis[l] < 0 || m->joint_axis[l] > 2)
+      return fail(ctx, DOAPP_INVALID_ARG, "doapp_set_fk_model: joint_axis[%d] = %d", l, m->joint_axis[l]);
+    h.axis[l] = m->joint_axis[l];
+    for (int i = 0; i < 3; ++i) h.origin[l][i] = m->joint_origin[l][i];
+  }
+  uint32_t q = 0;
+  for (int l = 0; l < 5; ++l) { // stable sort by link
+    h.first[l] = q;
+    for (uint32_t i = 0; i < m->num_spheres; ++i) {
+      const doapp_fk_sphere &sp = m->spheres[i];
+      if (sp.link < 0 || sp.link > 4 || !(sp.radius >= 0.0f))
+        return fail(ctx, DOAPP_INVALID_ARG, "doapp_set_fk_model: sphere %u link %d radius %g", i,
+                    sp.link, (double)sp.radius);
+      if (sp.link != l) continue;
+      h.order[q] = i;
+      for (int a = 0; a < 3; ++a) h.centre[q][a] = sp.centre[a];
+      volatile float thr = sp.radius + ctx->cfg.collision_distance; // one fp32 add, as the oracle
+      h.thr[q] = thr;
+      ++q;
+    }
+  }
+  h.first[5] = q;
+  ST(ensure(ctx, ctx->fk_dev, 1));
+  CU(cudaMemcpyAsync(ctx->fk_dev.p, &h, sizeof(h), cudaMemcpyHostToDevice, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  ctx->fk_on = true;
+  ctx->fk_spheres = m->num_spheres;
   return DOAPP_OK;
 }
 
@@ -1663,6 +1758,27 @@ doapp_status doapp_debug_fk(doapp_ctx *ctx, const float *waypoints, size_t count
   ctx->launches += 1;
   CU(cudaMemcpyAsync(points_out, ctx->dbg_b.p, count * 15 * sizeof(float), cudaMemcpyDeviceToHost,
                      ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  return DOAPP_OK;
+}
+
+doapp_status doapp_debug_fk_model(doapp_ctx *ctx, const float *waypoints, size_t count,
+                                  float *centres_out) {
+  if (!ctx) return DOAPP_INVALID_ARG;
+  if (!ctx->fk_on) return fail(ctx, DOAPP_NOT_READY, "doapp_debug_fk_model: no FK model set");
+  if (count == 0) return DOAPP_OK;
+  if (!waypoints || !centres_out) return fail(ctx, DOAPP_INVALID_ARG, "null argument");
+  CU(cudaSetDevice(ctx->cfg.device));
+  const size_t d = ctx->cfg.waypoint_dim, per = (size_t)ctx->fk_spheres * 3;
+  ST(ensure(ctx, ctx->dbg_a, count * d));
+  ST(ensure(ctx, ctx->dbg_b, count * per));
+  CU(cudaMemcpyAsync(ctx->dbg_a.p, waypoints, count * d * sizeof(float), cudaMemcpyHostToDevice,
+                     ctx->stream));
+  CU(launch_debug_fk_model(ctx->fk_dev.p, ctx->dbg_a.p, count, (int)d, ctx->fk_spheres,
+                           ctx->dbg_b.p, ctx->stream));
+  ctx->launches += 1;
+  CU(cudaMemcpyAsync(centres_out, ctx->dbg_b.p, count * per * sizeof(float),
+                     cudaMemcpyDeviceToHost, ctx->stream));
   CU(cudaStreamSynchronize(ctx->stream));
   return DOAPP_OK;
 }

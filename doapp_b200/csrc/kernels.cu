@@ -175,10 +175,12 @@ constexpr int kMaxCostThreads = 512;
 // Grid modes the kernel is specialised for.
 enum : int { GM_NONE = 0, GM_U8_CDG = 1, GM_F32_CDG = 2, GM_GENERIC = 3 };
 
+// thr: a distance cell collides when it is <= thr (collision_distance for the reference's point
+// links, radius + collision_distance for the spheres of an FK model)
 template <int GM, bool FIDX>
-__device__ __forceinline__ int collides(const CostParams &P, P3 p) {
+__device__ __forceinline__ int collides(const CostParams &P, P3 p, float thr) {
   if (GM == GM_NONE) return 0;
-  if (GM == GM_GENERIC) return grid_collides(P.grid, p.x, p.y, p.z, P.coll_dist);
+  if (GM == GM_GENERIC) return grid_collides(P.grid, p.x, p.y, p.z, thr);
   const GridDev &g = P.grid;
   const float ax = dm::add_(p.x, g.x_off), ay = dm::add_(p.y, g.y_off);
   if (FIDX) {
@@ -198,7 +200,7 @@ __device__ __forceinline__ int collides(const CostParams &P, P3 p) {
     if (GM == GM_U8_CDG) {
       if (in) hit = __ldg((const uint8_t *)g.cells + lin) != 0;
     } else {
-      if (in) hit = __ldg((const float *)g.cells + lin) <= P.coll_dist; // generate_trajectories.cu:412
+      if (in) hit = __ldg((const float *)g.cells + lin) <= thr; // generate_trajectories.cu:412
     }
     return hit;
   }
@@ -209,7 +211,72 @@ __device__ __forceinline__ int collides(const CostParams &P, P3 p) {
   in = in & (ix < g.nx) & (iy < g.ny) & (iz < g.nz);
   const uint32_t lin = in ? (iz * g.ny + iy) * g.nx + ix : 0u;
   if (GM == GM_U8_CDG) return in & (__ldg((const uint8_t *)g.cells + lin) != 0);
-  return in & (__ldg((const float *)g.cells + lin) <= P.coll_dist);
+  return in & (__ldg((const float *)g.cells + lin) <= thr);
+}
+
+// ---- URDF-correct chain with per-link spheres ---------------------
+// Link frames accumulate as rexarm.urdf:61-66,80-85,106-111,125-130,144-149 define them:
+//   p_i = p_{i-1} + R_{i-1} * origin_i,   R_i = R_{i-1} * Rot(axis_i, theta_i),
+// a sphere of link i sits at p_i + R_i * centre.  R is kept as three columns; R * v is
+// fma(col2, v.z, fma(col1, v.y, col0 * v.x)) per component; a rotation about axis a with cyclic
+// successors (b, c) replaces col_b <- fma(s, col_c, c * col_b), col_c <- fma(c, col_c, -s * col_b)
+// (DESIGN.md "FK model" fixes this operation order; the parity tests hold both sides to it).
+__device__ __forceinline__ P3 frame_apply(const P3 &c0, const P3 &c1, const P3 &c2, const P3 &pos,
+                                          float vx, float vy, float vz) {
+  P3 o;
+  o.x = dm::add_(pos.x, dm::fma_(c2.x, vz, dm::fma_(c1.x, vy, dm::mul_(c0.x, vx))));
+  o.y = dm::add_(pos.y, dm::fma_(c2.y, vz, dm::fma_(c1.y, vy, dm::mul_(c0.y, vx))));
+  o.z = dm::add_(pos.z, dm::fma_(c2.z, vz, dm::fma_(c1.z, vy, dm::mul_(c0.z, vx))));
+  return o;
+}
+__device__ __forceinline__ void frame_rotate(float s, float c, P3 &b, P3 &cc) {
+  const P3 nb{dm::fma_(s, cc.x, dm::mul_(c, b.x)), dm::fma_(s, cc.y, dm::mul_(c, b.y)),
+              dm::fma_(s, cc.z, dm::mul_(c, b.z))};
+  const P3 nc{dm::fma_(c, cc.x, dm::mul_(-s, b.x)), dm::fma_(c, cc.y, dm::mul_(-s, b.y)),
+              dm::fma_(c, cc.z, dm::mul_(-s, b.z))};
+  b = nb;
+  cc = nc;
+}
+// visit(q, centre) for every sphere, in link order.  The model reads are warp-uniform.
+template <int D, bool FAST, typename Visit>
+__device__ __forceinline__ void fk_model_walk(const FkModelDev &M, const float (&th)[D],
+                                              Visit &&visit) {
+  P3 c0{1.0f, 0.0f, 0.0f}, c1{0.0f, 1.0f, 0.0f}, c2{0.0f, 0.0f, 1.0f}, pos{0.0f, 0.0f, 0.0f};
+  uint32_t q = 0;
+#pragma unroll
+  for (int l = 0; l < 5; ++l) {
+    pos = frame_apply(c0, c1, c2, pos, __ldg(&M.origin[l][0]), __ldg(&M.origin[l][1]),
+                      __ldg(&M.origin[l][2]));
+    const float a = l < D ? th[l < D ? l : 0] : 0.0f; // no wrist_rotate angle with d = 4 (D3)
+    float s, c;
+    if (FAST)
+      dm::sincos_small(a, &s, &c);
+    else
+      dm::sincos(a, &s, &c);
+    const int ax = __ldg(&M.axis[l]);
+    if (ax == 0)
+      frame_rotate(s, c, c1, c2);
+    else if (ax == 1)
+      frame_rotate(s, c, c2, c0);
+    else
+      frame_rotate(s, c, c0, c1);
+    const uint32_t qe = __ldg(&M.first[l + 1]);
+    for (; q < qe; ++q)
+      visit(q, frame_apply(c0, c1, c2, pos, __ldg(&M.centre[q][0]), __ldg(&M.centre[q][1]),
+                           __ldg(&M.centre[q][2])));
+  }
+}
+template <int D> struct WpX {
+  float x[D];
+};
+template <int D, int GM, bool FIDX, bool FAST>
+__device__ __forceinline__ int model_collisions(const CostParams &P, WpX<D> in) {
+  int cnt = 0;
+  const FkModelDev &M = *P.fk_model;
+  fk_model_walk<D, FAST>(M, in.x, [&](uint32_t q, P3 sp) {
+    cnt += collides<GM, FIDX>(P, sp, __ldg(&M.thr[q]));
+  });
+  return cnt;
 }
 
 // One waypoint of one sample: derivatives, smoothness / limit terms and the collision count
@@ -219,7 +286,7 @@ __device__ __forceinline__ int collides(const CostParams &P, P3 p) {
 // this and the two previous waypoints are (device_math.cuh), otherwise the caller redoes the
 // waypoint with FAST = false (IEEE divides, full-range sin/cos).  Both produce the same bits
 // wherever FAST is valid.  vnew = this waypoint's velocities (the caller commits them).
-template <int D, int GM, bool FIDX, bool LIM, bool FAST>
+template <int D, int GM, bool FIDX, bool LIM, bool FAST, bool FKM = false>
 __device__ __forceinline__ bool waypoint_cost(const CostParams &P, const float (&x)[D],
                                               const float (&xprev)[D], const float (&vprev)[D],
                                               float (&vnew)[D], float *a2_out, float *l2_out,
@@ -245,10 +312,17 @@ __device__ __forceinline__ bool waypoint_cost(const CostParams &P, const float (
   }
   int cnt = 0;
   if (GM != GM_NONE) {
-    P3 pts[5];
-    fk_points<D, FAST>(x, P.rpy_s, P.rpy_c, pts);
+    if (FKM) { // FK model kernels only: the reference-chain kernels keep their register budget
+      WpX<D> in;
 #pragma unroll
-    for (int l = 0; l < 5; ++l) cnt += collides<GM, FIDX && FAST>(P, pts[l]);
+      for (int j = 0; j < D; ++j) in.x[j] = x[j];
+      cnt = model_collisions<D, GM, FIDX && FAST, FAST>(P, in);
+    } else {
+      P3 pts[5];
+      fk_points<D, FAST>(x, P.rpy_s, P.rpy_c, pts);
+#pragma unroll
+      for (int l = 0; l < 5; ++l) cnt += collides<GM, FIDX && FAST>(P, pts[l], P.coll_dist);
+    }
   }
   *a2_out = a2;
   *l2_out = l2;
@@ -264,10 +338,10 @@ template <int D> struct WpOut {
   float vnew[D], a2, l2;
   int coll;
 };
-template <int D, int GM, bool FIDX, bool LIM>
+template <int D, int GM, bool FIDX, bool LIM, bool FKM = false>
 __device__ __noinline__ WpOut<D> waypoint_cost_general(const CostParams &P, WpIn<D> in) {
   WpOut<D> o;
-  waypoint_cost<D, GM, FIDX, LIM, false>(P, in.x, in.xprev, in.vprev, o.vnew, &o.a2, &o.l2,
+  waypoint_cost<D, GM, FIDX, LIM, false, FKM>(P, in.x, in.xprev, in.vprev, o.vnew, &o.a2, &o.l2,
                                          &o.coll);
   return o;
 }
@@ -380,7 +454,7 @@ __device__ __forceinline__ void stage_trajectory(const CostParams &P, uint32_t c
   __syncthreads();
 }
 
-template <int D, int GM, bool NPW, bool FIDX, bool LIM>
+template <int D, int GM, bool NPW, bool FIDX, bool LIM, bool FKM>
 __global__ void __launch_bounds__(kMaxCostThreads)
     cost_kernel(const __grid_constant__ CostParams P) {
   namespace cg = cooperative_groups;
@@ -507,7 +581,7 @@ __global__ void __launch_bounds__(kMaxCostThreads)
     for (int j = 0; j < D; ++j) x[j] = noisy(w, j);
     float a2, l2;
     int cw;
-    const bool fine0 = waypoint_cost<D, GM, FIDX, LIM, true>(P, x, xprev, vprev, vnew, &a2, &l2, &cw);
+    const bool fine0 = waypoint_cost<D, GM, FIDX, LIM, true, FKM>(P, x, xprev, vprev, vnew, &a2, &l2, &cw);
     const bool fast_valid = fine0 & fine1 & fine2;
     fine2 = fine1;
     fine1 = fine0 & (P.fast_ok != 0);
@@ -519,7 +593,7 @@ __global__ void __launch_bounds__(kMaxCostThreads)
         in.xprev[j] = xprev[j];
         in.vprev[j] = vprev[j];
       }
-      const WpOut<D> o = waypoint_cost_general<D, GM, FIDX, LIM>(P, in);
+      const WpOut<D> o = waypoint_cost_general<D, GM, FIDX, LIM, FKM>(P, in);
 #pragma unroll
       for (int j = 0; j < D; ++j) vnew[j] = o.vnew[j];
       a2 = o.a2;
@@ -1434,6 +1508,22 @@ __global__ void debug_sincos_kernel(const float *x, uint64_t count, float *s, fl
 }
 
 template <int D>
+__global__ void debug_fk_model_kernel(const FkModelDev *model, const float *wp, uint64_t count,
+                                      uint32_t num_spheres, float *out) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= count) return;
+  float th[D];
+#pragma unroll
+  for (int j = 0; j < D; ++j) th[j] = wp[i * D + j];
+  fk_model_walk<D, false>(*model, th, [&](uint32_t q, P3 sp) {
+    float *o = out + (i * num_spheres + model->order[q]) * 3;
+    o[0] = sp.x;
+    o[1] = sp.y;
+    o[2] = sp.z;
+  });
+}
+
+template <int D>
 __global__ void debug_fk_kernel(const float *wp, uint64_t count, float rpy_s, float rpy_c,
                                 float *out) {
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -1478,13 +1568,13 @@ inline unsigned blocks_for(uint64_t total, unsigned threads) {
 
 void host_sincos(float x, float *s, float *c) { dm::sincos(x, s, c); }
 
-template <int D, int GM, bool NPW, bool LIM>
+template <int D, int GM, bool NPW, bool LIM, bool FKM = false>
 static cudaError_t launch_cost_t(const CostParams &p, dim3 grid, unsigned threads, size_t smem,
                                  unsigned cluster, cudaStream_t st) {
   // the specialised CDG kernels exist only with the verified reciprocal index divide; a grid
   // whose verification failed (or DOAPP_EXACT_DIV=1) runs the generic kernel (IEEE divides)
   constexpr bool FIDX = GM == GM_U8_CDG || GM == GM_F32_CDG;
-  auto kern = cost_kernel<D, GM, NPW, FIDX, LIM>;
+  auto kern = cost_kernel<D, GM, NPW, FIDX, LIM, FKM>;
   if (smem > 48 * 1024) {
     cudaError_t e =
         cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -1620,6 +1710,19 @@ static cudaError_t launch_cost_d(const CostParams &p, dim3 grid, unsigned thread
                     : launch_cost_t<D, GMV, true, false>(p, grid, threads, smem, cluster, st)) \
              : (lim ? launch_cost_t<D, GMV, false, true>(p, grid, threads, smem, cluster, st) \
                     : launch_cost_t<D, GMV, false, false>(p, grid, threads, smem, cluster, st))
+#define DOAPP_GO_FK(GMV)                                                                          \
+  return npw ? (lim ? launch_cost_t<D, GMV, true, true, true>(p, grid, threads, smem, cluster, st)  \
+                    : launch_cost_t<D, GMV, true, false, true>(p, grid, threads, smem, cluster, st)) \
+             : (lim ? launch_cost_t<D, GMV, false, true, true>(p, grid, threads, smem, cluster, st) \
+                    : launch_cost_t<D, GMV, false, false, true>(p, grid, threads, smem, cluster, st))
+  if (p.fk_model) { // URDF chain + spheres (doapp_set_fk_model): its own kernel instances
+    switch (gm) {
+    case GM_U8_CDG: DOAPP_GO_FK(GM_U8_CDG);
+    case GM_F32_CDG: DOAPP_GO_FK(GM_F32_CDG);
+    case GM_GENERIC: DOAPP_GO_FK(GM_GENERIC);
+    default: break; // no grid: no collision term, either chain
+    }
+  }
   switch (gm) {
   case GM_U8_CDG: DOAPP_GO(GM_U8_CDG);
   case GM_F32_CDG: DOAPP_GO(GM_F32_CDG);
@@ -1627,6 +1730,7 @@ static cudaError_t launch_cost_d(const CostParams &p, dim3 grid, unsigned thread
   default: DOAPP_GO(GM_NONE);
   }
 #undef DOAPP_GO
+#undef DOAPP_GO_FK
 }
 
 cudaError_t launch_cost(const CostParams &p_in, int d, int sm_count, cudaStream_t st) {
@@ -1663,7 +1767,7 @@ cudaError_t launch_cost(const CostParams &p_in, int d, int sm_count, cudaStream_
     bool pk = lg == 0;
     if (p.pk_mode == 1) pk = true;
     if (p.pk_mode == 0) pk = false;
-    if (pk && !npw && gm != GM_GENERIC && p.fast_ok)
+    if (pk && !npw && gm != GM_GENERIC && p.fast_ok && !p.fk_model) // packed FK: reference chain only
       return d == 5 ? launch_cost_pk_d<5>(p, gm, st) : launch_cost_pk_d<4>(p, gm, st);
   }
   p.parts_log2 = lg;
@@ -1800,6 +1904,16 @@ cudaError_t launch_debug_sincos(const float *x, uint64_t count, float *s, float 
                                 cudaStream_t st) {
   if (count == 0) return cudaSuccess;
   debug_sincos_kernel<<<blocks_for(count, 256), 256, 0, st>>>(x, count, s, c);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_debug_fk_model(const FkModelDev *model, const float *wp, uint64_t count, int d,
+                                  uint32_t num_spheres, float *out, cudaStream_t st) {
+  if (count == 0 || num_spheres == 0) return cudaSuccess;
+  if (d == 5)
+    debug_fk_model_kernel<5><<<blocks_for(count, 128), 128, 0, st>>>(model, wp, count, num_spheres, out);
+  else
+    debug_fk_model_kernel<4><<<blocks_for(count, 128), 128, 0, st>>>(model, wp, count, num_spheres, out);
   return cudaGetLastError();
 }
 

@@ -44,7 +44,21 @@ struct GridDev {
   uint32_t tx_bits, ty_bits, tz_bits;
 };
 
+// URDF-correct chain with per-link collision spheres (doapp_fk_model in
+// doapp.h).  Spheres are sorted by link; first[l] .. first[l+1] are link l's; order[q] is the
+// caller's index of sorted sphere q; thr = radius + collision_distance (fp32 add, host).
+constexpr int kFkMaxSpheres = 16;
+struct FkModelDev {
+  float origin[5][3];
+  int axis[5];
+  uint32_t first[6];
+  uint32_t order[kFkMaxSpheres];
+  float centre[kFkMaxSpheres][3];
+  float thr[kFkMaxSpheres];
+};
+
 struct CostParams {
+  const FkModelDev *fk_model; // device; nullptr = the chain of generate_trajectories.cu:397-463
   // trajectories, structure-of-arrays: traj[c][j][npad]
   const float *traj;
   const float *start; // [d] device
@@ -192,6 +206,8 @@ cudaError_t launch_aos_to_soa(const float *aos, float *soa, uint32_t k, uint32_t
                               uint32_t d, int broadcast_first, cudaStream_t st);
 cudaError_t launch_debug_sincos(const float *x, uint64_t count, float *s, float *c,
                                 cudaStream_t st);
+cudaError_t launch_debug_fk_model(const FkModelDev *model, const float *wp, uint64_t count, int d,
+                                  uint32_t num_spheres, float *out, cudaStream_t st);
 cudaError_t launch_debug_fk(const float *wp, uint64_t count, int d, float rpy_s, float rpy_c,
                             float *out, cudaStream_t st);
 cudaError_t launch_reduce_keys_float(const unsigned long long *keys, uint32_t k,

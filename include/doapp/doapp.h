@@ -200,6 +200,34 @@ DOAPP_API doapp_status doapp_grid_lookup(doapp_ctx *ctx, const float *xyz, size_
 /* min_joint_angles / max_joint_angles (perturbator/src/common.cu:7-15). */
 DOAPP_API doapp_status doapp_set_limits(doapp_ctx *ctx, const float *min_d, const float *max_d);
 
+/* ---- URDF-correct forward kinematics with per-link collision spheres ---------------
+ * The reference's chain (generate_trajectories.cu:397-463) rotates a point base->tip about
+ * y,z,y,y,y; the arm's description says z,y,y,y,z with accumulated link frames
+ * (rexarm_description/robots/rexarm.urdf:61-66,80-85,106-111,125-130,144-149).
+ * With a model set, the collision term of every cost evaluation walks the URDF chain
+ *   p_i = p_{i-1} + R_{i-1} * origin_i,   R_i = R_{i-1} * Rot(axis_i, theta_i)
+ * and counts the spheres (fixed points of the link frames, sized from the link boxes of
+ * rexarm.urdf:49-58,68-77,94-103,113-122,132-141,174-183) that collide: occupancy cell at the
+ * centre != 0, or distance cell at the centre <= radius + collision_distance. */
+#define DOAPP_FK_MAX_SPHERES 16
+typedef struct doapp_fk_sphere {
+  int32_t link;    /* frame after joint `link`, 0..4 */
+  float centre[3]; /* in that frame, metres */
+  float radius;
+} doapp_fk_sphere;
+typedef struct doapp_fk_model {
+  uint32_t struct_size;      /* = sizeof(doapp_fk_model) */
+  float joint_origin[5][3];  /* rexarm.urdf:64,83,109,128,147 */
+  int32_t joint_axis[5];     /* 0 = x, 1 = y, 2 = z; rexarm.urdf:65,84,110,129,148 */
+  uint32_t num_spheres;      /* 1..DOAPP_FK_MAX_SPHERES */
+  doapp_fk_sphere spheres[DOAPP_FK_MAX_SPHERES];
+} doapp_fk_model;
+/* The Rexarm of rexarm.urdf: 5 joints, two spheres along every link box, two along the
+ * fingers, one at gripper_center (13 spheres). */
+DOAPP_API void doapp_fk_model_rexarm(doapp_fk_model *model);
+/* model == NULL returns to the reference's chain (the default). */
+DOAPP_API doapp_status doapp_set_fk_model(doapp_ctx *ctx, const doapp_fk_model *model);
+
 /* ---- stage 1: noise --------------------------------------------------- */
 
 /* Philox4x32-10 + Box-Muller replacement for init_cudarand / curand_normal
@@ -334,6 +362,10 @@ DOAPP_API doapp_status doapp_debug_sincos(doapp_ctx *ctx, const float *angles, s
  * ([count][d] in, [count][5][3] out), evaluated on the device. */
 DOAPP_API doapp_status doapp_debug_fk(doapp_ctx *ctx, const float *waypoints, size_t count,
                                       float *points_out);
+/* Sphere centres of the FK model set with doapp_set_fk_model ([count][d] in,
+ * [count][num_spheres][3] out, the caller's sphere order), evaluated on the device. */
+DOAPP_API doapp_status doapp_debug_fk_model(doapp_ctx *ctx, const float *waypoints, size_t count,
+                                            float *centres_out);
 
 #ifdef __cplusplus
 }

@@ -33,7 +33,38 @@ class Params(C.Structure):
                 ("select_mode", C.c_int32), ("sum_order", C.c_int32), ("limit_weight", C.c_float),
                 ("limit_min", C.c_void_p), ("limit_max", C.c_void_p), ("sigma", C.c_float),
                 ("seed", C.c_uint64), ("sample_offset", C.c_uint64), ("m_global", C.c_uint64),
-                ("update_mode", C.c_int32), ("update_gain", C.c_float)]
+                ("update_mode", C.c_int32), ("update_gain", C.c_float),
+                ("fk_model", C.c_void_p)]
+
+
+FK_MAX_SPHERES = 16
+
+
+class FkSphere(C.Structure):
+    _fields_ = [("link", C.c_int32), ("centre", C.c_float * 3), ("radius", C.c_float)]
+
+
+class FkModel(C.Structure):
+    """orc_fk_model: URDF joint origins / axes + per-link collision spheres."""
+    _fields_ = [("joint_origin", (C.c_float * 3) * 5), ("joint_axis", C.c_int32 * 5),
+                ("num_spheres", C.c_uint32), ("spheres", FkSphere * FK_MAX_SPHERES)]
+
+
+def fk_model_rexarm() -> FkModel:
+    m = FkModel()
+    lib().orc_fk_model_rexarm(C.byref(m))
+    return m
+
+
+def fk_model_points(model: FkModel, waypoints) -> np.ndarray:
+    """[count][num_spheres][3] sphere centres of the URDF-correct chain."""
+    wp = _f32(waypoints)
+    wp = wp.reshape(-1, wp.shape[-1])
+    out = np.empty((wp.shape[0], model.num_spheres, 3), np.float32)
+    for i in range(wp.shape[0]):
+        lib().orc_fk_model_points(C.byref(model), wp[i].ctypes.data_as(C.c_void_p), wp.shape[1],
+                                  out[i].ctypes.data_as(C.c_void_p))
+    return out
 
 
 def _digest() -> str:
@@ -75,6 +106,8 @@ def lib() -> C.CDLL:
         L.orc_philox4x32_10.argtypes = [C.c_void_p] * 3
         L.orc_noise_fill.argtypes = [C.POINTER(Params), C.c_uint32, C.c_void_p]
         L.orc_fk_points.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p]
+        L.orc_fk_model_rexarm.argtypes = [C.c_void_p]
+        L.orc_fk_model_points.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
         L.orc_fk_points_as_shipped_matvec.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p]
         L.orc_grid_index.argtypes = [C.POINTER(Grid), C.c_float, C.c_float, C.c_float]
         L.orc_grid_index.restype = C.c_int64
@@ -123,13 +156,15 @@ class Oracle:
         self.p.k, self.p.m, self.p.n, self.p.d, self.p.n_noise = k, m, n, d, n_noise
         self._keep = {}
         for key, val in kw.items():
-            if key in ("limit_min", "limit_max"):
+            if key in ("limit_min", "limit_max", "fk_model"):
                 continue
             if not hasattr(self.p, key):
                 raise AttributeError(key)
             setattr(self.p, key, val)
         if "limit_min" in kw:
             self.set_limits(kw["limit_min"], kw["limit_max"])
+        if kw.get("fk_model") is not None:
+            self.set_fk_model(kw["fk_model"])
         self.g = Grid()
         self.g.kind = GRID_NONE
         self.cells = None
@@ -138,6 +173,11 @@ class Oracle:
         self._keep["lo"], self._keep["hi"] = _f32(lo), _f32(hi)
         self.p.limit_min = self._keep["lo"].ctypes.data
         self.p.limit_max = self._keep["hi"].ctypes.data
+
+    def set_fk_model(self, model):
+        """FkModel -> URDF-correct chain with per-link spheres; None -> the reference's chain."""
+        self._keep["fk"] = model
+        self.p.fk_model = C.addressof(model) if model is not None else None
 
     def set_grid(self, cells: np.ndarray, resolution: float, frame=FRAME_CDG):
         """cells indexed [iz, iy, ix] (flat ix + nx*iy + nx*ny*iz), uint8/int8 or float32."""

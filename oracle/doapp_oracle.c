@@ -298,6 +298,71 @@ void orc_fk_points_as_shipped_matvec(const float *waypoint, uint32_t d, float ou
 }
 
 /* ------------------------------------------------------------------------
+ * URDF-correct FK with per-link spheres.  Not in the
+ * reference's code: its chain (above) rotates a point, base->tip, about the
+ * wrong axes (D14).  Here the link frames accumulate as the URDF defines them,
+ *   p_i = p_{i-1} + R_{i-1} * origin_i,   R_i = R_{i-1} * Rot(axis_i, theta_i),
+ * and a sphere of link i sits at p_i + R_i * centre.  Arithmetic spec (shared
+ * with the CUDA kernels): R is kept as three columns; R * v is
+ * fma(col2, v.z, fma(col1, v.y, col0 * v.x)) per component; a rotation about
+ * axis a with cyclic successors (b, c) replaces
+ *   col_b <- fma(s, col_c, c * col_b),  col_c <- fma(c, col_c, (-s) * col_b).
+ * ---------------------------------------------------------------------- */
+void orc_fk_model_rexarm(orc_fk_model *m) {
+  static const float origin[5][3] = {{0.0f, -0.0015f, 0.0715f}, /* rexarm.urdf:64 */
+                                     {0.0f, 0.0f, 0.045f},      /* :83 */
+                                     {0.0f, 0.0f, 0.1f},        /* :109 */
+                                     {0.0f, 0.0f, 0.1f},        /* :128 */
+                                     {0.0f, -0.0125f, 0.08f}};  /* :147 */
+  static const int32_t axis[5] = {2, 1, 1, 1, 2};               /* :65,84,110,129,148 */
+  /* two spheres along the long side of every link box (centre -+ a quarter of the long
+   * side, radius = half the larger short side), two along the fingers, one at the
+   * gripper centre */
+  static const orc_fk_sphere sph[13] = {
+      {0, {0.0f, 0.0f, 0.0185f}, 0.0175f},      {0, {0.0f, 0.0f, 0.0435f}, 0.0175f},     /* :52,55 */
+      {1, {0.0f, 0.0f, 0.0735f}, 0.0175f},      {1, {0.0f, 0.0f, 0.0985f}, 0.0175f},     /* :71,74 */
+      {2, {0.0f, 0.0f, 0.07325f}, 0.016f},      {2, {0.0f, 0.0f, 0.09825f}, 0.016f},     /* :97,100 */
+      {3, {0.0f, -0.01425f, 0.0645f}, 0.016f},  {3, {0.0f, 0.01075f, 0.0645f}, 0.016f},  /* :116,119 */
+      {4, {0.0f, -0.01125f, 0.019f}, 0.0155f},  {4, {0.0f, 0.01375f, 0.019f}, 0.0155f},  /* :135,138 */
+      {4, {0.0f, 0.01f, 0.0525f}, 0.01375f},    {4, {0.0f, 0.01f, 0.0875f}, 0.01375f},   /* :180,189 */
+      {4, {0.0f, -0.005f, 0.07f}, 0.01f}};                                               /* :197 */
+  memset(m, 0, sizeof(*m));
+  memcpy(m->joint_origin, origin, sizeof(origin));
+  memcpy(m->joint_axis, axis, sizeof(axis));
+  m->num_spheres = 13;
+  memcpy(m->spheres, sph, sizeof(sph));
+}
+
+static void orc_frame_apply(float col[3][3], const float pos[3], const float v[3], float out[3]) {
+  for (int i = 0; i < 3; ++i) {
+    float t = col[0][i] * v[0];
+    t = fmaf(col[1][i], v[1], t);
+    t = fmaf(col[2][i], v[2], t);
+    out[i] = pos[i] + t;
+  }
+}
+
+void orc_fk_model_points(const orc_fk_model *m, const float *waypoint, uint32_t d, float (*out)[3]) {
+  float col[3][3] = {{1.0f, 0.0f, 0.0f}, {0.0f, 1.0f, 0.0f}, {0.0f, 0.0f, 1.0f}}; /* col[j][i] = R[i][j] */
+  float pos[3] = {0.0f, 0.0f, 0.0f};
+  for (int link = 0; link < 5; ++link) {
+    float np[3];
+    orc_frame_apply(col, pos, m->joint_origin[link], np);
+    memcpy(pos, np, sizeof(pos));
+    float th = (uint32_t)link < d ? waypoint[link] : 0.0f, s, c;
+    orc_sincosf(th, &s, &c);
+    int a = m->joint_axis[link], b = (a + 1) % 3, cc = (a + 2) % 3;
+    for (int i = 0; i < 3; ++i) {
+      float cb = col[b][i], cv = col[cc][i];
+      col[b][i] = fmaf(s, cv, c * cb);
+      col[cc][i] = fmaf(c, cv, (-s) * cb);
+    }
+    for (uint32_t q = 0; q < m->num_spheres; ++q)
+      if (m->spheres[q].link == link) orc_frame_apply(col, pos, m->spheres[q].centre, out[q]);
+  }
+}
+
+/* ------------------------------------------------------------------------
  * Stage 3: grid lookup.  CDG frame: cdg.cu:69-82 (offsets) and :113-126
  * (bounds, fp32 add, IEEE fp32 divide, truncation).  OG frame: og.cpp:29-40
  * (fp64).  Deviations: dense pitch; half-open bounds, and an
@@ -355,9 +420,17 @@ size_t orc_grid_scatter(orc_grid *g, const float *xyz, size_t num_points, int8_t
 uint32_t orc_num_collisions(const orc_params *p, const orc_grid *g, const float *waypoint) {
   if (p->collision_mode == ORC_COLLISION_AS_SHIPPED) return 0; /* gt.cu:394 */
   if (!g || g->kind == ORC_GRID_NONE) return 0;
+  uint32_t cnt = 0;
+  if (p->fk_model) { /* SURVEY 8f row 3 */
+    float sp[ORC_FK_MAX_SPHERES][3];
+    orc_fk_model_points(p->fk_model, waypoint, p->d, sp);
+    for (uint32_t q = 0; q < p->fk_model->num_spheres; ++q)
+      cnt += (uint32_t)orc_grid_collides(g, sp[q][0], sp[q][1], sp[q][2],
+                                         p->fk_model->spheres[q].radius + p->collision_distance);
+    return cnt;
+  }
   float pts[5][3];
   orc_fk_points(waypoint, p->d, pts);
-  uint32_t cnt = 0;
   for (int l = 0; l < 5; ++l)
     cnt += (uint32_t)orc_grid_collides(g, pts[l][0], pts[l][1], pts[l][2], p->collision_distance);
   return cnt;

@@ -67,7 +67,30 @@ typedef struct orc_params {
   uint64_t sample_offset, m_global;
   int32_t update_mode; /* ORC_UPDATE_* */
   float update_gain;   /* 10000.0f, gt.cu:140 */
+  const struct orc_fk_model *fk_model; /* NULL: the chain of gt.cu:397-463; else SURVEY 8f row 3 */
 } orc_params;
+
+/* URDF-correct forward kinematics with per-link collision spheres:
+ * accumulated transforms T_i = T_{i-1} * Trans(origin_i) * Rot(axis_i, theta_i), joint origins
+ * and axes from rexarm_description/robots/rexarm.urdf:61-66,80-85,106-111,125-130,144-149;
+ * spheres are fixed points of the link frames placed along the link boxes (:49-58,68-77,
+ * 94-103,113-122,132-141,174-183,194-198).  A sphere collides when the occupancy cell at its
+ * centre is set (U8 grid) or when the distance cell there is <= radius + collision_distance. */
+#define ORC_FK_MAX_SPHERES 16
+typedef struct orc_fk_sphere {
+  int32_t link;    /* frame after joint `link`, 0..4 */
+  float centre[3]; /* in that frame */
+  float radius;
+} orc_fk_sphere;
+typedef struct orc_fk_model {
+  float joint_origin[5][3];
+  int32_t joint_axis[5]; /* 0 = x, 1 = y, 2 = z */
+  uint32_t num_spheres;
+  orc_fk_sphere spheres[ORC_FK_MAX_SPHERES];
+} orc_fk_model;
+void orc_fk_model_rexarm(orc_fk_model *m);
+/* out[num_spheres][3]; a 4-joint waypoint has wrist_rotate = 0 */
+void orc_fk_model_points(const orc_fk_model *m, const float *waypoint, uint32_t d, float (*out)[3]);
 
 void orc_params_init(orc_params *p);
 
