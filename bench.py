@@ -44,6 +44,10 @@ WORKLOADS = {
     "c4m": dict(desc="C4 (whole 1M-sample config on each GPU): 128 waypoints x 1048576 samples/GPU, "
                      "128^3 u8 grid, 2 iterations per step",
                 grid_n=128, res=0.01, n=128, m=1048576, iters=2, sigma=0.05, fill=0.0),
+    "c4u": dict(desc="C4 with the URDF-correct FK model (SURVEY 8f row 3): 13 collision spheres per "
+                     "waypoint instead of 5 link points; 128 waypoints x 131072 samples/GPU, 128^3 u8 "
+                     "grid, 4 iterations per step",
+                grid_n=128, res=0.01, n=128, m=131072, iters=4, sigma=0.05, fill=0.0, fk_model=True),
     "c5": dict(desc="C5: 512^3 u8 grid (128 MiB, L2-spill), 128 waypoints x 16384 samples/GPU, "
                     "4 iterations per step",
                grid_n=512, res=0.0025, n=128, m=16384, iters=4, sigma=0.5, fill=0.05),
@@ -52,10 +56,13 @@ D = 5
 LINKS = 5
 
 
-def alg_bytes_per_wps(n: int, cell_bytes: int = 1) -> float:
-    """5 gathers x cell bytes + the sample's noise vector and its score/collision
-    outputs amortised over its n waypoints."""
-    return LINKS * cell_bytes + (4 * D + 8) / n
+FK_MODEL_SPHERES = 13  # doapp_fk_model_rexarm
+
+
+def alg_bytes_per_wps(n: int, cell_bytes: int = 1, links: int = LINKS) -> float:
+    """5 gathers (13 with the FK model) x cell bytes + the sample's noise vector and
+    its score/collision outputs amortised over its n waypoints."""
+    return links * cell_bytes + (4 * D + 8) / n
 
 
 class ClockSampler(threading.Thread):
@@ -107,7 +114,8 @@ def cpu_plan_rate(w, iters, threads, reps=1, min_seconds=0.0):
     import oracle
     oracle.build()
     grid, start, goal = make_inputs(w)
-    orc = oracle.Oracle(k=1, m=w["m"], n=w["n"], d=D, sigma=w["sigma"], select_mode=1)
+    orc = oracle.Oracle(k=1, m=w["m"], n=w["n"], d=D, sigma=w["sigma"], select_mode=1,
+                        fk_model=oracle.fk_model_rexarm() if w.get("fk_model") else None)
     orc.set_grid(grid, w["res"])
     init = oracle.plan_lerp(start, goal, w["n"])
     best, total, done = float("inf"), 0.0, 0
@@ -259,6 +267,10 @@ def run_ours(args, w, rank, world, local_rank):
     else:
         ctx.set_grid(grid, w["res"])
         peer = False
+    links = LINKS
+    if w.get("fk_model"):
+        ctx.set_fk_model(capi.fk_model_rexarm())
+        links = FK_MODEL_SPHERES
 
     # pinned host staging for the e2e leg
     h_start = torch.from_numpy(start.copy()).pin_memory().numpy()
@@ -326,8 +338,10 @@ def run_ours(args, w, rank, world, local_rank):
     per_launch_s = cost_ms * 1e-3 / max(1, cost_launches)
     # one launch per iteration, or ONE persistent launch running all the iterations
     units_per_launch = m * n * iters / max(1, cost_launches)
-    alg = alg_bytes_per_wps(n) * units_per_launch
+    alg = alg_bytes_per_wps(n, links=links) * units_per_launch
     kernel_name = "plan_persistent_kernel" if cost_launches == 1 and iters > 1 else "cost_kernel"
+    if w.get("fk_model"):
+        kernel_name = "cost_kernel<FK model>"
     achieved = alg / per_launch_s / 1e9
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
@@ -335,6 +349,7 @@ def run_ours(args, w, rank, world, local_rank):
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": w["desc"], "samples_per_gpu": m, "waypoints": n, "joints": D,
                    "iterations_per_step": iters, "grid": f"{w['grid_n']}^3 u8",
+                   "lookups_per_waypoint": links,
                    "parallelism": f"samples sharded over {world} GPU(s), grid replicated"
                                   + (", argmin keys merged in-kernel through NVLink peer mailboxes"
                                      if peer and persistent else
@@ -359,7 +374,7 @@ def run_ours(args, w, rank, world, local_rank):
         "clocks": clocks,
         "best_score": r["best_score"],
     }
-    gathers_per_s = LINKS * units_per_launch / per_launch_s
+    gathers_per_s = links * units_per_launch / per_launch_s
     line["gather_roofline"] = {
         "what": "north_star's L2/HBM gather roofline: collision lookups per second of the cost "
                 "kernel against the measured rate of independent random one-sector loads "

@@ -74,7 +74,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
     host_src = os.path.join(host_dir, "planning_state.cpp")
     if os.path.exists(host_src):
         hdeps = [host_src, os.path.join(host_dir, "planning_state.hpp"),
-                 os.path.join(host_dir, "ros_mirror.hpp"), LIB]
+                 os.path.join(host_dir, "ros_mirror.hpp"),
+                 os.path.join(host_dir, "follower_check.hpp"), LIB]
         cxx = shutil.which("g++") or "g++"
         common = ["-O2", "-std=c++17", "-fPIC", "-I", os.path.join(ROOT, "include"), "-I", host_dir]
         if force or _stale(HOST_LIB, hdeps):

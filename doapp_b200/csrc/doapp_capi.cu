@@ -116,6 +116,7 @@ struct doapp_ctx {
   int use_limits = 0;
   float rpy_s = 0.0f, rpy_c = 0.0f;
   DevBuf<FkModelDev> fk_dev;       // doapp_set_fk_model (URDF chain + spheres); fk_on selects it
+  FkModelDev fk_host{};            // the same, for the kernels' parameter block
   bool fk_on = false;
   uint32_t fk_spheres = 0;
   dm::FastDiv dt_div{};            // verified at create (verify_fast_div)
@@ -272,7 +273,8 @@ CostParams base_cost_params(doapp_ctx *ctx) {
   p.select_mode = c.select_mode;
   p.rpy_s = ctx->rpy_s;
   p.rpy_c = ctx->rpy_c;
-  p.fk_model = ctx->fk_on ? ctx->fk_dev.p : nullptr;
+  p.fk_on = ctx->fk_on ? 1 : 0;
+  if (ctx->fk_on) p.fk = ctx->fk_host;
   p.grid = ctx->grid;
   p.dt_div = ctx->dt_div;
   p.fast_ok = ctx->dt_fast_ok ? 1 : 0;
@@ -1170,6 +1172,7 @@ doapp_status doapp_set_fk_model(doapp_ctx *ctx, const doapp_fk_model *m) {
   CU(cudaMemcpyAsync(ctx->fk_dev.p, &h, sizeof(h), cudaMemcpyHostToDevice, ctx->stream));
   CU(cudaStreamSynchronize(ctx->stream));
   ctx->fk_on = true;
+  ctx->fk_host = h;
   ctx->fk_spheres = m->num_spheres;
   return DOAPP_OK;
 }

@@ -237,7 +237,8 @@ __device__ __forceinline__ void frame_rotate(float s, float c, P3 &b, P3 &cc) {
   b = nb;
   cc = nc;
 }
-// visit(q, centre) for every sphere, in link order.  The model reads are warp-uniform.
+// visit(q, centre) for every sphere, in link order.  The model reads are warp-uniform (constant
+// bank operands in the cost kernels, where the model is part of the parameter block).
 template <int D, bool FAST, typename Visit>
 __device__ __forceinline__ void fk_model_walk(const FkModelDev &M, const float (&th)[D],
                                               Visit &&visit) {
@@ -245,25 +246,23 @@ __device__ __forceinline__ void fk_model_walk(const FkModelDev &M, const float (
   uint32_t q = 0;
 #pragma unroll
   for (int l = 0; l < 5; ++l) {
-    pos = frame_apply(c0, c1, c2, pos, __ldg(&M.origin[l][0]), __ldg(&M.origin[l][1]),
-                      __ldg(&M.origin[l][2]));
+    pos = frame_apply(c0, c1, c2, pos, M.origin[l][0], M.origin[l][1], M.origin[l][2]);
     const float a = l < D ? th[l < D ? l : 0] : 0.0f; // no wrist_rotate angle with d = 4 (D3)
     float s, c;
     if (FAST)
       dm::sincos_small(a, &s, &c);
     else
       dm::sincos(a, &s, &c);
-    const int ax = __ldg(&M.axis[l]);
+    const int ax = M.axis[l];
     if (ax == 0)
       frame_rotate(s, c, c1, c2);
     else if (ax == 1)
       frame_rotate(s, c, c2, c0);
     else
       frame_rotate(s, c, c0, c1);
-    const uint32_t qe = __ldg(&M.first[l + 1]);
+    const uint32_t qe = M.first[l + 1];
     for (; q < qe; ++q)
-      visit(q, frame_apply(c0, c1, c2, pos, __ldg(&M.centre[q][0]), __ldg(&M.centre[q][1]),
-                           __ldg(&M.centre[q][2])));
+      visit(q, frame_apply(c0, c1, c2, pos, M.centre[q][0], M.centre[q][1], M.centre[q][2]));
   }
 }
 template <int D> struct WpX {
@@ -272,9 +271,9 @@ template <int D> struct WpX {
 template <int D, int GM, bool FIDX, bool FAST>
 __device__ __forceinline__ int model_collisions(const CostParams &P, WpX<D> in) {
   int cnt = 0;
-  const FkModelDev &M = *P.fk_model;
+  const FkModelDev &M = P.fk;
   fk_model_walk<D, FAST>(M, in.x, [&](uint32_t q, P3 sp) {
-    cnt += collides<GM, FIDX>(P, sp, __ldg(&M.thr[q]));
+    cnt += collides<GM, FIDX>(P, sp, M.thr[q]);
   });
   return cnt;
 }
@@ -962,7 +961,8 @@ __device__ __forceinline__ void fk_points2(const dm::f2 (&th)[D], float rpy_s, f
 
 // collides<GM, true> on two points (threshold form, see GridDev::tx_bits)
 template <int GM>
-__device__ __forceinline__ void collides2(const CostParams &P, P3v p, int *hit_lo, int *hit_hi) {
+__device__ __forceinline__ void collides2(const CostParams &P, P3v p, float thr, int *hit_lo,
+                                          int *hit_hi) {
   using namespace dm;
   const GridDev &g = P.grid;
   const f2 ax = f2_add(p.x, f2_splat(g.x_off)), ay = f2_add(p.y, f2_splat(g.y_off));
@@ -978,7 +978,7 @@ __device__ __forceinline__ void collides2(const CostParams &P, P3v p, int *hit_l
     if (GM == GM_U8_CDG) {
       if (in) hit = __ldg((const uint8_t *)g.cells + lin) != 0;
     } else {
-      if (in) hit = __ldg((const float *)g.cells + lin) <= P.coll_dist;
+      if (in) hit = __ldg((const float *)g.cells + lin) <= thr;
     }
     return hit;
   };
@@ -986,10 +986,66 @@ __device__ __forceinline__ void collides2(const CostParams &P, P3v p, int *hit_l
   *hit_hi = half(f2_hi(ax), f2_hi(ay), f2_hi(az), f2_hi(fx), f2_hi(fy), f2_hi(fz));
 }
 
+// fk_model_walk<D, true> + the sphere lookups on two waypoints (frame_apply / frame_rotate in
+// packed form: the same multiplies, FMAs and adds per half)
+__device__ __forceinline__ P3v frame_apply2(const P3v &c0, const P3v &c1, const P3v &c2,
+                                            const P3v &pos, float vx, float vy, float vz) {
+  using namespace dm;
+  const f2 x2 = f2_splat(vx), y2 = f2_splat(vy), z2 = f2_splat(vz);
+  P3v o;
+  o.x = f2_add(pos.x, f2_fma(c2.x, z2, f2_fma(c1.x, y2, f2_mul(c0.x, x2))));
+  o.y = f2_add(pos.y, f2_fma(c2.y, z2, f2_fma(c1.y, y2, f2_mul(c0.y, x2))));
+  o.z = f2_add(pos.z, f2_fma(c2.z, z2, f2_fma(c1.z, y2, f2_mul(c0.z, x2))));
+  return o;
+}
+__device__ __forceinline__ void frame_rotate2(dm::f2 s, dm::f2 c, P3v &b, P3v &cc) {
+  using namespace dm;
+  const f2 ns = f2_neg(s);
+  const P3v nb{f2_fma(s, cc.x, f2_mul(c, b.x)), f2_fma(s, cc.y, f2_mul(c, b.y)),
+               f2_fma(s, cc.z, f2_mul(c, b.z))};
+  const P3v nc{f2_fma(c, cc.x, f2_mul(ns, b.x)), f2_fma(c, cc.y, f2_mul(ns, b.y)),
+               f2_fma(c, cc.z, f2_mul(ns, b.z))};
+  b = nb;
+  cc = nc;
+}
+template <int D, int GM>
+__device__ __forceinline__ void model_collisions2(const CostParams &P, const dm::f2 (&th)[D],
+                                                  int *c_lo, int *c_hi) {
+  using namespace dm;
+  const FkModelDev &M = P.fk;
+  const f2 one = f2_splat(1.0f), zero = f2_splat(0.0f);
+  P3v c0{one, zero, zero}, c1{zero, one, zero}, c2{zero, zero, one}, pos{zero, zero, zero};
+  int lo = 0, hi = 0;
+  uint32_t q = 0;
+#pragma unroll
+  for (int l = 0; l < 5; ++l) {
+    pos = frame_apply2(c0, c1, c2, pos, M.origin[l][0], M.origin[l][1], M.origin[l][2]);
+    f2 s, c;
+    f2_sincos_small(l < D ? th[l < D ? l : 0] : zero, &s, &c); // no wrist_rotate angle with d = 4
+    const int ax = M.axis[l];
+    if (ax == 0)
+      frame_rotate2(s, c, c1, c2);
+    else if (ax == 1)
+      frame_rotate2(s, c, c2, c0);
+    else
+      frame_rotate2(s, c, c0, c1);
+    const uint32_t qe = M.first[l + 1];
+    for (; q < qe; ++q) {
+      int h0, h1;
+      collides2<GM>(P, frame_apply2(c0, c1, c2, pos, M.centre[q][0], M.centre[q][1], M.centre[q][2]),
+                    M.thr[q], &h0, &h1);
+      lo += h0;
+      hi += h1;
+    }
+  }
+  *c_lo = lo;
+  *c_hi = hi;
+}
+
 // waypoint_cost<..., FAST = true> on two CONSECUTIVE WAYPOINTS (lo = w, hi = w + 1) of one
 // sample.  xprev / vprev are waypoint w - 1's angles and velocities; the hi half's priors are
 // the lo half's own results.  fine_lo / fine_hi as waypoint_cost's return value.
-template <int D, int GM, bool LIM>
+template <int D, int GM, bool LIM, bool FKM>
 __device__ __forceinline__ void waypoint_cost2(const CostParams &P, const dm::f2 (&x)[D],
                                                const float (&xprev)[D], const float (&vprev)[D],
                                                dm::f2 (&vnew)[D], dm::f2 *a2_out, dm::f2 *l2_out,
@@ -1016,13 +1072,15 @@ __device__ __forceinline__ void waypoint_cost2(const CostParams &P, const dm::f2
     }
   }
   int c_lo = 0, c_hi = 0;
-  if (GM != GM_NONE) {
+  if (GM != GM_NONE && FKM) {
+    model_collisions2<D, GM>(P, x, &c_lo, &c_hi);
+  } else if (GM != GM_NONE) {
     P3v pts[5];
     fk_points2<D>(x, P.rpy_s, P.rpy_c, pts);
 #pragma unroll
     for (int l = 0; l < 5; ++l) {
       int h0, h1;
-      collides2<GM>(P, pts[l], &h0, &h1);
+      collides2<GM>(P, pts[l], P.coll_dist, &h0, &h1);
       c_lo += h0;
       c_hi += h1;
     }
@@ -1043,7 +1101,7 @@ constexpr int kPkThreads = 128;
 // One thread = one sample, TWO consecutive waypoints per step in the two halves of packed
 // registers.  Same sample-to-lane mapping, noise, staging prologue and outputs as cost_kernel
 // with one thread per sample.
-template <int D, int GM, bool LIM>
+template <int D, int GM, bool LIM, bool FKM>
 __global__ void __launch_bounds__(kPkThreads, DOAPP_PK_MINBLOCKS)
     cost_kernel_pk(const __grid_constant__ CostParams P) {
   using namespace dm;
@@ -1094,7 +1152,7 @@ __global__ void __launch_bounds__(kPkThreads, DOAPP_PK_MINBLOCKS)
     f2 a2, l2;
     int cw0, cw1;
     bool f0, f1;
-    waypoint_cost2<D, GM, LIM>(P, x, xprev, vprev, vnew, &a2, &l2, &cw0, &cw1, &f0, &f1);
+    waypoint_cost2<D, GM, LIM, FKM>(P, x, xprev, vprev, vnew, &a2, &l2, &cw0, &cw1, &f0, &f1);
     const bool valid0 = f0 & fine1 & fine2, valid1 = f1 & f0 & fine1;
     fine2 = f0 & (P.fast_ok != 0);
     fine1 = f1 & (P.fast_ok != 0);
@@ -1109,7 +1167,7 @@ __global__ void __launch_bounds__(kPkThreads, DOAPP_PK_MINBLOCKS)
           in.xprev[j] = h ? f2_lo(x[j]) : xprev[j];
           in.vprev[j] = h ? f2_lo(vnew[j]) : vprev[j];
         }
-        const WpOut<D> o = waypoint_cost_general<D, GM, true, LIM>(P, in);
+        const WpOut<D> o = waypoint_cost_general<D, GM, true, LIM, FKM>(P, in);
 #pragma unroll
         for (int j = 0; j < D; ++j)
           vnew[j] = h ? f2_pack(f2_lo(vnew[j]), o.vnew[j]) : f2_pack(o.vnew[j], f2_hi(vnew[j]));
@@ -1595,10 +1653,10 @@ static cudaError_t launch_cost_t(const CostParams &p, dim3 grid, unsigned thread
   return cudaLaunchKernelEx(&cfg, kern, p);
 }
 
-template <int D, int GM, bool LIM>
+template <int D, int GM, bool LIM, bool FKM = false>
 static cudaError_t launch_cost_pk_t(const CostParams &p, cudaStream_t st) {
   const size_t smem = ((size_t)D * (p.npad + 2) + 8) * sizeof(float);
-  auto kern = cost_kernel_pk<D, GM, LIM>;
+  auto kern = cost_kernel_pk<D, GM, LIM, FKM>;
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
@@ -1613,12 +1671,19 @@ static cudaError_t launch_cost_pk_d(const CostParams &p, int gm, cudaStream_t st
   const bool lim = p.use_limits != 0;
 #define DOAPP_PK(GMV)                                                                 \
   return lim ? launch_cost_pk_t<D, GMV, true>(p, st) : launch_cost_pk_t<D, GMV, false>(p, st)
+#define DOAPP_PK_FK(GMV)                                                              \
+  return lim ? launch_cost_pk_t<D, GMV, true, true>(p, st) : launch_cost_pk_t<D, GMV, false, true>(p, st)
+  if (p.fk_on) { // URDF chain + spheres
+    if (gm == GM_U8_CDG) DOAPP_PK_FK(GM_U8_CDG);
+    if (gm == GM_F32_CDG) DOAPP_PK_FK(GM_F32_CDG);
+  }
   switch (gm) {
   case GM_U8_CDG: DOAPP_PK(GM_U8_CDG);
   case GM_F32_CDG: DOAPP_PK(GM_F32_CDG);
   default: DOAPP_PK(GM_NONE);
   }
 #undef DOAPP_PK
+#undef DOAPP_PK_FK
 }
 
 static int grid_mode_of(const CostParams &p) {
@@ -1715,7 +1780,7 @@ static cudaError_t launch_cost_d(const CostParams &p, dim3 grid, unsigned thread
                     : launch_cost_t<D, GMV, true, false, true>(p, grid, threads, smem, cluster, st)) \
              : (lim ? launch_cost_t<D, GMV, false, true, true>(p, grid, threads, smem, cluster, st) \
                     : launch_cost_t<D, GMV, false, false, true>(p, grid, threads, smem, cluster, st))
-  if (p.fk_model) { // URDF chain + spheres (doapp_set_fk_model): its own kernel instances
+  if (p.fk_on) { // URDF chain + spheres (doapp_set_fk_model): its own kernel instances
     switch (gm) {
     case GM_U8_CDG: DOAPP_GO_FK(GM_U8_CDG);
     case GM_F32_CDG: DOAPP_GO_FK(GM_F32_CDG);
@@ -1767,7 +1832,7 @@ cudaError_t launch_cost(const CostParams &p_in, int d, int sm_count, cudaStream_
     bool pk = lg == 0;
     if (p.pk_mode == 1) pk = true;
     if (p.pk_mode == 0) pk = false;
-    if (pk && !npw && gm != GM_GENERIC && p.fast_ok && !p.fk_model) // packed FK: reference chain only
+    if (pk && !npw && gm != GM_GENERIC && p.fast_ok)
       return d == 5 ? launch_cost_pk_d<5>(p, gm, st) : launch_cost_pk_d<4>(p, gm, st);
   }
   p.parts_log2 = lg;

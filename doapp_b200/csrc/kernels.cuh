@@ -58,7 +58,10 @@ struct FkModelDev {
 };
 
 struct CostParams {
-  const FkModelDev *fk_model; // device; nullptr = the chain of generate_trajectories.cu:397-463
+  // fk_on = 0: the chain of generate_trajectories.cu:397-463.  1: the model below, carried by
+  // value so the kernels read it from the constant bank (warp-uniform operands, no loads)
+  int fk_on;
+  FkModelDev fk;
   // trajectories, structure-of-arrays: traj[c][j][npad]
   const float *traj;
   const float *start; // [d] device

@@ -185,6 +185,14 @@ void PlanningState::buildDistanceField() {
   have_u8_grid = false; // the grid now holds float distances
 }
 
+void PlanningState::useUrdfKinematics(bool on) {
+  synchronize();
+  doapp_fk_model model;
+  doapp_fk_model_rexarm(&model);
+  doapp_status st = doapp_set_fk_model(ctx, on ? &model : nullptr);
+  DOAPP_ASSERT(st == DOAPP_OK);
+}
+
 void PlanningState::updatePointCloud(const doapp_host::PointCloudXYZ &cloud, bool clear_first) {
   synchronize();
   if (!have_u8_grid) {

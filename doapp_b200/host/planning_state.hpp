@@ -63,6 +63,9 @@ public:
   // occupancy -> exact Euclidean distance field: what updateDistanceGrid(KDTree) was meant to
   // produce on the host (cpu_distance_grid.cu:87-202); the sphere test of gt.cu:412 then applies
   void buildDistanceField();
+  // collision term on the arm's real kinematic chain (rexarm.urdf:61-149, 13 spheres along the
+  // link boxes) instead of the point chain of generate_trajectories.cu:397-463
+  void useUrdfKinematics(bool on);
   // The follower indexes positions[i] / velocities[i] for i < 6 servo ids
   // (dynamixel_driver/src/trajectory_follower.cpp:176-178,194-199) while the planner emits d
   // entries per point: with n > d the published points are padded to n entries,

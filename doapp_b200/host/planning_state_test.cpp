@@ -1,12 +1,13 @@
 // planning_state_test.cpp — drives PlanningState the way perturbator/src/main.cu:24-43 does
 // (joint_state + goal_state callbacks, plan(), publish_trajectory()) without ROS, and prints the
 // published JointTrajectory as JSON for tests/test_host_gpu.py to check against the oracle.
-//   planning_state_test k m n d grid_n resolution iterations cloud.bin|- [follower_joints [edt]]
+//   planning_state_test k m n d grid_n resolution iterations cloud.bin|- [follower_joints [edt|- [urdf]]]
 #include <cstdio>
 #include <cstdlib>
 #include <memory>
 #include <vector>
 
+#include "follower_check.hpp"
 #include "planning_state.hpp"
 
 int main(int argc, char **argv) {
@@ -33,8 +34,10 @@ int main(int argc, char **argv) {
     if (std::fread(cloud.xyz.data(), 1, bytes, f) != (size_t)bytes) return 3;
     std::fclose(f);
     planning_state.updatePointCloud(cloud);
-    if (argc > 10) planning_state.buildDistanceField(); // sphere test on the derived distance grid
+    if (argc > 10 && argv[10][0] != '-')
+      planning_state.buildDistanceField(); // sphere test on the derived distance grid
   }
+  if (argc > 11) planning_state.useUrdfKinematics(true);
 
   auto state = std::make_shared<doapp_host::JointState>();
   state->position = {0.0, 0.0, 0.0, 0.0, 0.0, 0.7}; // 6 servos reported, truncated to d
@@ -62,6 +65,22 @@ int main(int argc, char **argv) {
       std::printf("%s%.9g", j ? ", " : "", p.velocities[j]);
     std::printf("]}");
   }
-  std::printf("]}\n");
+  std::printf("]");
+  // the consumer's side: replay trajectory_follower.cpp:148-215 at its 100 Hz tick
+  const size_t servos = argc > 9 ? (size_t)std::atoi(argv[9]) : d;
+  for (int intended = 0; intended < 2; ++intended) {
+    const doapp_host::FollowerReplay r =
+        doapp_host::replay_follower(msg, servos > d ? servos : d, d, 0.01, intended != 0);
+    std::printf(", \"follower_%s\": {\"well_formed\": %d, \"ticks\": %zu, \"duration\": %.9g, "
+                "\"max_command_step\": %.9g, \"max_interp_gap\": %.9g, "
+                "\"max_velocity_mismatch\": %.9g, \"max_lead\": %.9g, \"last_command\": [",
+                intended ? "intended" : "as_shipped", r.well_formed ? 1 : 0, r.ticks, r.duration,
+                r.max_command_step, r.max_interp_gap, r.max_velocity_mismatch, r.max_lead);
+    if (!r.commanded.empty())
+      for (size_t j = 0; j < r.commanded.back().size(); ++j)
+        std::printf("%s%.9g", j ? ", " : "", r.commanded.back()[j]);
+    std::printf("]}");
+  }
+  std::printf("}\n");
   return 0;
 }

@@ -82,3 +82,59 @@ def test_follower_padding_and_distance_field(capi, oracle_mod, tmp_path):
     assert np.array_equal(pos[:, :d].view(np.uint32), epos.view(np.uint32))
     assert np.array_equal(vel[:, :d].view(np.uint32), evel.view(np.uint32))
     assert np.float32(msg["cost"]) == np.float32(r["best_score"])
+    # the consumer's side (trajectory_follower.cpp:148-215 replayed at 100 Hz): the message is
+    # well formed for 6 servos, ends on the goal, and its velocities are the finite differences
+    times = [p["t"] for p in msg["points"]]
+    for key, intended in (("follower_as_shipped", False), ("follower_intended", True)):
+        f = msg[key]
+        ticks, now = _replay_ticks(times, intended)
+        assert f["well_formed"] == 1 and f["ticks"] == ticks and abs(f["duration"] - now) < 1e-6
+        assert f["max_interp_gap"] <= 1e-12 and f["max_velocity_mismatch"] < 1e-4
+        assert np.array_equal(np.array(f["last_command"], np.float32), pos[-1])
+        step = np.abs(np.diff(pos.astype(np.float64), axis=0)).max()
+        assert f["max_command_step"] <= step + 1e-12
+    # as shipped the segment end is the previous point's stamp: the commanded point runs up to
+    # one segment (delta_t) ahead of the clock; with the intended end it never leads
+    assert 0.08 < msg["follower_as_shipped"]["max_lead"] < 0.1 + 1e-9
+    assert msg["follower_intended"]["max_lead"] <= 1e-12
+    assert 0 <= msg["follower_intended"]["ticks"] - msg["follower_as_shipped"]["ticks"] <= 2
+
+
+def _replay_ticks(t, intended, tick=0.01):
+    """trajectory_follower.cpp:139-144,157-160,206-211: index stepping only."""
+    prev, nxt, now, ticks = 0, (1 if len(t) > 1 else 0), 0.0, 0
+    while True:
+        ticks += 1
+        if prev + 1 == len(t):
+            break
+        if now > (t[nxt] if intended else t[prev]):
+            prev = nxt
+            if nxt + 1 < len(t):
+                nxt += 1
+        now += tick
+    return ticks, now
+
+
+@pytest.mark.gpu
+def test_urdf_kinematics_through_planning_state(capi, oracle_mod, tmp_path):
+    """PlanningState::useUrdfKinematics: the whole host path on the URDF chain + spheres
+     equals the oracle with the same FK model."""
+    k, m, n, d, iters, gn, res = 1, 128, 32, 5, 5, 64, 0.02
+    cloud = synth.cloud(30000, 0)
+    path = tmp_path / "cloud.bin"
+    cloud.astype(np.float32).tofile(path)
+    out = subprocess.run([BIN, str(k), str(m), str(n), str(d), str(gn), str(res), str(iters), str(path),
+                          "5", "-", "urdf"], capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0, out.stderr
+    msg = json.loads(out.stdout)
+    pos = np.array([p["positions"] for p in msg["points"]], np.float32)
+    orc = oracle_mod.Oracle(k=k, m=m, n=n, d=d, select_mode=oracle_mod.SELECT_CEIL_INT,
+                            fk_model=oracle_mod.fk_model_rexarm())
+    orc.set_grid(np.zeros((gn, gn, gn), np.uint8), res)
+    orc.scatter(cloud, 1, True)
+    cur = np.zeros(d, np.float32)
+    goal = np.array([0.0, -1.0, 1.5, -1.5, 0.0], np.float32)
+    r = orc.plan(cur, oracle_mod.plan_lerp(cur, goal, n), iters)
+    epos, _, _ = oracle_mod.build_message(cur, goal, r["best_traj"], r["best_vel"], 0.1)
+    assert np.array_equal(pos.view(np.uint32), epos.view(np.uint32))
+    assert np.float32(msg["cost"]) == np.float32(r["best_score"])
