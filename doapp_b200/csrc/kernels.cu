@@ -1094,14 +1094,17 @@ __device__ __forceinline__ void waypoint_cost2(const CostParams &P, const dm::f2
 }
 
 constexpr int kPkThreads = 128;
+constexpr uint32_t kPkMaxPartN = 256; // T > 1: 32 KB of per-waypoint sums per CTA at most
 #ifndef DOAPP_PK_MINBLOCKS
 #define DOAPP_PK_MINBLOCKS 4
 #endif
 
-// One thread = one sample, TWO consecutive waypoints per step in the two halves of packed
-// registers.  Same sample-to-lane mapping, noise, staging prologue and outputs as cost_kernel
-// with one thread per sample.
-template <int D, int GM, bool LIM, bool FKM>
+// One thread = one sample (or one of 2 / 4 runs of a sample's waypoints, P.parts_log2), TWO
+// consecutive waypoints per step in the two halves of packed registers.  Same sample-to-lane
+// mapping, noise, staging prologue, sum order and outputs as cost_kernel.  With T = 2 or 4
+// parts per sample the 4 warps of a CTA are 4 / T sample-warps x T parts; every part leaves
+// its per-waypoint sums in shared memory and part 0 folds them in waypoint order.
+template <int D, int GM, bool LIM, bool FKM, bool MP>
 __global__ void __launch_bounds__(kPkThreads, DOAPP_PK_MINBLOCKS)
     cost_kernel_pk(const __grid_constant__ CostParams P) {
   using namespace dm;
@@ -1109,9 +1112,18 @@ __global__ void __launch_bounds__(kPkThreads, DOAPP_PK_MINBLOCKS)
   const uint32_t NP = P.npad + 2;
   float *sbase = smem;                     // [D][NP], waypoint n duplicates n - 1
   float *swin = sbase + (size_t)D * NP;    // [8] pending winner's noise / update vector
+  // MP (multi-part) instances: 2 or 4 parts per sample; the one-part instances fold T == 1
+  const uint32_t TL = MP ? P.parts_log2 : 0u;
+  const uint32_t T = 1u << TL;             // 1, 2 or 4 parts per sample
+  const uint32_t WS = T * P.wpp;           // waypoint slots per sample (>= n), T > 1 only
+  const uint32_t SW = (kPkThreads >> 5) >> TL; // sample-warps per CTA
+  float *spart = swin + 8;                                      // [SW][WS][32]
+  float *slim = spart + (T > 1 ? (size_t)SW * WS * 32 : 0);     // [SW][WS][32] (limits)
+  int *scoll = (int *)(slim + (T > 1 && LIM ? (size_t)SW * WS * 32 : 0)); // [4][32]
   const uint32_t c = blockIdx.y;
   const int lane = threadIdx.x & 31;
-  uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t warp = threadIdx.x >> 5, part = warp & (T - 1), swi = warp >> TL;
+  uint32_t t = blockIdx.x * (SW * 32) + swi * 32 + lane;
   const bool active = t < P.m;
   t = active ? t : P.m - 1; // idle lanes shadow the last sample (no divergence, no stores)
   const uint32_t tg = (uint32_t)(P.sample_offset + t);
@@ -1131,18 +1143,35 @@ __global__ void __launch_bounds__(kPkThreads, DOAPP_PK_MINBLOCKS)
   }
   stage_trajectory<D, 0, true>(P, c, pd, swin, sbase);
 
+  // this part's run of waypoints (wpp is even: pairs never straddle two parts) and its
+  // priors: the initial waypoint for both derivative passes at w = 0
+  // (generate_trajectories.cu:285), else recomputed from the two waypoints before
+  const uint32_t w0 = MP ? part * P.wpp : 0u;
+  const uint32_t w_end = MP ? ((w0 + P.wpp) < P.n ? (w0 + P.wpp) : P.n) : P.n;
   float xprev[D], vprev[D];
   bool fine1 = P.fast_ok != 0, fine2 = fine1;
+  if (!MP || w0 == 0) {
 #pragma unroll
-  for (int j = 0; j < D; ++j) { // generate_trajectories.cu:285, SURVEY D7
-    xprev[j] = vprev[j] = __ldg(P.start + j);
-    fine1 = fine1 & fine_angle(xprev[j]);
+    for (int j = 0; j < D; ++j) {
+      xprev[j] = vprev[j] = __ldg(P.start + j);
+      fine1 = fine1 & fine_angle(xprev[j]);
+    }
+  } else if (w0 < P.n) {
+#pragma unroll
+    for (int j = 0; j < D; ++j) {
+      const float x1 = add_(sbase[j * NP + w0 - 1], eps[j]);
+      const float x2 = add_(sbase[j * NP + w0 - 2], eps[j]); // w0 >= 2
+      xprev[j] = x1;
+      vprev[j] = div_fast(sub_(x1, x2), P.dt_div);
+      fine1 = fine1 & fine_angle(x1);
+      fine2 = fine2 & fine_angle(x2);
+    }
   }
 
   float total = 0.0f, ltotal = 0.0f;
   int coll = 0;
-  for (uint32_t w = 0; w < P.n; w += 2) {
-    const bool has_hi = w + 1 < P.n;
+  for (uint32_t w = w0; w < w_end; w += 2) {
+    const bool has_hi = w + 1 < w_end;
     f2 x[D], vnew[D];
 #pragma unroll
     for (int j = 0; j < D; ++j) { // generate_trajectories.cu:53-57
@@ -1181,14 +1210,35 @@ __global__ void __launch_bounds__(kPkThreads, DOAPP_PK_MINBLOCKS)
       xprev[j] = f2_hi(x[j]);
       vprev[j] = f2_hi(vnew[j]);
     }
-    // fixed order: left fold over the waypoints (oracle ORC_SUM_WAYPOINT)
     coll += cw0;
-    total = add_(total, f2_lo(a2));
-    if (LIM) ltotal = add_(ltotal, f2_lo(l2));
-    if (has_hi) {
-      coll += cw1;
-      total = add_(total, f2_hi(a2));
-      if (LIM) ltotal = add_(ltotal, f2_hi(l2));
+    if (has_hi) coll += cw1;
+    if (!MP) { // fixed order: left fold over the waypoints (oracle ORC_SUM_WAYPOINT)
+      total = add_(total, f2_lo(a2));
+      if (LIM) ltotal = add_(ltotal, f2_lo(l2));
+      if (has_hi) {
+        total = add_(total, f2_hi(a2));
+        if (LIM) ltotal = add_(ltotal, f2_hi(l2));
+      }
+    } else { // slot w + 1 <= WS - 1 always exists
+      float *sp = spart + ((size_t)swi * WS + w) * 32 + lane;
+      sp[0] = f2_lo(a2);
+      sp[32] = f2_hi(a2);
+      if (LIM) {
+        float *sl = slim + ((size_t)swi * WS + w) * 32 + lane;
+        sl[0] = f2_lo(l2);
+        sl[32] = f2_hi(l2);
+      }
+    }
+  }
+  if (MP) {
+    scoll[warp * 32 + lane] = coll;
+    __syncthreads();
+    if (part != 0) return;
+    coll = 0;
+    for (uint32_t q = 0; q < T; ++q) coll += scoll[(swi * T + q) * 32 + lane];
+    for (uint32_t ww = 0; ww < P.n; ++ww) { // the same left fold, waypoint 0 first
+      total = add_(total, spart[((size_t)swi * WS + ww) * 32 + lane]);
+      if (LIM) ltotal = add_(ltotal, slim[((size_t)swi * WS + ww) * 32 + lane]);
     }
   }
 
@@ -1653,17 +1703,26 @@ static cudaError_t launch_cost_t(const CostParams &p, dim3 grid, unsigned thread
   return cudaLaunchKernelEx(&cfg, kern, p);
 }
 
-template <int D, int GM, bool LIM, bool FKM = false>
-static cudaError_t launch_cost_pk_t(const CostParams &p, cudaStream_t st) {
-  const size_t smem = ((size_t)D * (p.npad + 2) + 8) * sizeof(float);
-  auto kern = cost_kernel_pk<D, GM, LIM, FKM>;
+template <int D, int GM, bool LIM, bool FKM, bool MP>
+static cudaError_t launch_cost_pk_m(const CostParams &p, cudaStream_t st) {
+  const uint32_t T = 1u << p.parts_log2, SW = (kPkThreads / 32) >> p.parts_log2;
+  size_t smem = ((size_t)D * (p.npad + 2) + 8) * sizeof(float);
+  if (MP) smem += ((size_t)SW * T * p.wpp * 32 * (LIM ? 2 : 1) + 4 * 32) * sizeof(float);
+  auto kern = cost_kernel_pk<D, GM, LIM, FKM, MP>;
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
   }
-  const dim3 grid((p.m + kPkThreads - 1) / kPkThreads, p.k);
+  const uint32_t spb = SW * 32; // samples per CTA
+  const dim3 grid((p.m + spb - 1) / spb, p.k);
   kern<<<grid, kPkThreads, smem, st>>>(p);
   return cudaGetLastError();
+}
+
+template <int D, int GM, bool LIM, bool FKM = false>
+static cudaError_t launch_cost_pk_t(const CostParams &p, cudaStream_t st) {
+  return p.parts_log2 ? launch_cost_pk_m<D, GM, LIM, FKM, true>(p, st)
+                      : launch_cost_pk_m<D, GM, LIM, FKM, false>(p, st);
 }
 
 template <int D>
@@ -1829,11 +1888,19 @@ cudaError_t launch_cost(const CostParams &p_in, int d, int sm_count, cudaStream_
     // the samples alone fill the chip (DOAPP_PK=0/1 forces the choice where it is legal).
     const bool npw = p.n_noise != 1 && p.noise_mode != NOISE_ZERO;
     const int gm = grid_mode_of(p);
-    bool pk = lg == 0;
+    // Up to 4 parts per sample stay inside one CTA of the packed kernel (its per-waypoint sums
+    // live in shared memory: n <= kPkMaxPartN); more parts need the scalar kernel's clusters.
+    uint32_t plg = lg <= 2 ? lg : 2;
+    if (p.n > kPkMaxPartN || p.n < 4) plg = 0;
+    bool pk = lg == plg;
     if (p.pk_mode == 1) pk = true;
     if (p.pk_mode == 0) pk = false;
-    if (pk && !npw && gm != GM_GENERIC && p.fast_ok)
+    if (pk && !npw && gm != GM_GENERIC && p.fast_ok) {
+      p.parts_log2 = plg;
+      const uint32_t per = (p.n + (1u << plg) - 1) >> plg; // waypoints per part, rounded up to even
+      p.wpp = (per + 1) & ~1u;
       return d == 5 ? launch_cost_pk_d<5>(p, gm, st) : launch_cost_pk_d<4>(p, gm, st);
+    }
   }
   p.parts_log2 = lg;
   const uint32_t T = 1u << lg;

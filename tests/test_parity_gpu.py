@@ -170,6 +170,12 @@ PK_CASES = [  # (k, m, n, d, grid, sigma, limits)
     (1, 1000, 64, 5, "f32", 0.5, False),
     (3, 129, 33, 5, "u8", 0.3, True),      # odd n: the last step's high half is idle
     (1, 256, 128, 5, "none", 0.2, False),
+    # the three geometries of the packed kernel on a 148-SM part: small m above runs 4 parts per
+    # sample; these fill the chip with 1 and 2 parts per sample
+    (1, 57000, 8, 5, "u8", 0.3, False),
+    (1, 30000, 16, 4, "f32", 0.3, True),
+    (2, 700, 250, 5, "u8", 0.05, True),    # 4 parts x 64 waypoints (62 in the last), limits
+    (1, 40, 6, 5, "u8", 0.3, False),       # 4 parts x 2 waypoints, the last part idle
 ]
 
 
