@@ -44,6 +44,9 @@ WORKLOADS = {
     "c4m": dict(desc="C4 (whole 1M-sample config on each GPU): 128 waypoints x 1048576 samples/GPU, "
                      "128^3 u8 grid, 2 iterations per step",
                 grid_n=128, res=0.01, n=128, m=1048576, iters=2, sigma=0.05, fill=0.0),
+    "c2u": dict(desc="C2 with the URDF-correct FK model (13 collision spheres per waypoint): 128^3 u8 "
+                     "grid, 64 waypoints x 1024 samples/GPU, 100 optimizer iterations per step",
+                grid_n=128, res=0.01, n=64, m=1024, iters=100, sigma=0.05, fill=0.0, fk_model=True),
     "c4u": dict(desc="C4 with the URDF-correct FK model (SURVEY 8f row 3): 13 collision spheres per "
                      "waypoint instead of 5 link points; 128 waypoints x 131072 samples/GPU, 128^3 u8 "
                      "grid, 4 iterations per step",
@@ -341,7 +344,7 @@ def run_ours(args, w, rank, world, local_rank):
     alg = alg_bytes_per_wps(n, links=links) * units_per_launch
     kernel_name = "plan_persistent_kernel" if cost_launches == 1 and iters > 1 else "cost_kernel"
     if w.get("fk_model"):
-        kernel_name = "cost_kernel<FK model>"
+        kernel_name += "<FK model>"
     achieved = alg / per_launch_s / 1e9
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,

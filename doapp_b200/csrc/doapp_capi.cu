@@ -367,7 +367,6 @@ doapp_status persistent_eligible(doapp_ctx *ctx, PersistParams *q, bool *ok) {
   const doapp_config &c = ctx->cfg;
   if (ctx->persist_mode == 0 || c.update_mode != DOAPP_UPDATE_KEEP_BEST || c.noise_waypoints != 1)
     return DOAPP_OK;
-  if (ctx->fk_on && ctx->grid.kind != DOAPP_GRID_NONE) return DOAPP_OK; // FK model: cost_kernel only
   // several ranks: only with the peer mailboxes mapped (doapp_peer_import), else NCCL per iteration
   if (ctx->comm && !(ctx->peer_ready && ctx->peer_nranks == ctx->nranks)) return DOAPP_OK;
   CostParams p = base_cost_params(ctx);

@@ -669,7 +669,7 @@ __device__ __forceinline__ void grid_wait(const unsigned int *counter, unsigned 
   } while (v < target);
 }
 
-template <int D, int GM, bool LIM>
+template <int D, int GM, bool LIM, bool FKM>
 __global__ void __launch_bounds__(256) plan_persistent_kernel(const __grid_constant__ PersistParams Q) {
   const CostParams &P = Q.cost;
   constexpr bool FIDX = GM == GM_U8_CDG || GM == GM_F32_CDG;
@@ -772,7 +772,7 @@ __global__ void __launch_bounds__(256) plan_persistent_kernel(const __grid_const
       for (int j = 0; j < D; ++j) x[j] = noisy(w, j);
       float a2, l2;
       int cw;
-      const bool fine0 = waypoint_cost<D, GM, FIDX, LIM, true>(P, x, xprev, vprev, vnew, &a2, &l2, &cw);
+      const bool fine0 = waypoint_cost<D, GM, FIDX, LIM, true, FKM>(P, x, xprev, vprev, vnew, &a2, &l2, &cw);
       const bool fast_valid = fine0 & fine1 & fine2;
       fine2 = fine1;
       fine1 = fine0 & (P.fast_ok != 0);
@@ -784,7 +784,7 @@ __global__ void __launch_bounds__(256) plan_persistent_kernel(const __grid_const
           in.xprev[j] = xprev[j];
           in.vprev[j] = vprev[j];
         }
-        const WpOut<D> o = waypoint_cost_general<D, GM, FIDX, LIM>(P, in);
+        const WpOut<D> o = waypoint_cost_general<D, GM, FIDX, LIM, FKM>(P, in);
 #pragma unroll
         for (int j = 0; j < D; ++j) vnew[j] = o.vnew[j];
         a2 = o.a2;
@@ -1756,9 +1756,21 @@ static int grid_mode_of(const CostParams &p) {
 
 // ---- persistent planner: kernel selection, geometry, cooperative launch
 template <int D>
-static const void *persistent_kernel_of(int gm, bool lim) {
-#define DOAPP_PP(GMV) \
-  return lim ? (const void *)plan_persistent_kernel<D, GMV, true> : (const void *)plan_persistent_kernel<D, GMV, false>
+static const void *persistent_kernel_of(int gm, bool lim, bool fkm) {
+#define DOAPP_PP(GMV)                                                    \
+  return lim ? (const void *)plan_persistent_kernel<D, GMV, true, false> \
+             : (const void *)plan_persistent_kernel<D, GMV, false, false>
+#define DOAPP_PP_FK(GMV)                                                \
+  return lim ? (const void *)plan_persistent_kernel<D, GMV, true, true> \
+             : (const void *)plan_persistent_kernel<D, GMV, false, true>
+  if (fkm) { // URDF chain + spheres: own instances (register budget of the reference chain kept)
+    switch (gm) {
+    case GM_U8_CDG: DOAPP_PP_FK(GM_U8_CDG);
+    case GM_F32_CDG: DOAPP_PP_FK(GM_F32_CDG);
+    case GM_GENERIC: DOAPP_PP_FK(GM_GENERIC);
+    default: break;
+    }
+  }
   switch (gm) {
   case GM_U8_CDG: DOAPP_PP(GM_U8_CDG);
   case GM_F32_CDG: DOAPP_PP(GM_F32_CDG);
@@ -1766,6 +1778,7 @@ static const void *persistent_kernel_of(int gm, bool lim) {
   default: DOAPP_PP(GM_NONE);
   }
 #undef DOAPP_PP
+#undef DOAPP_PP_FK
 }
 
 static size_t persistent_smem(const CostParams &p, int d, uint32_t T, uint32_t wpp) {
@@ -1779,8 +1792,8 @@ cudaError_t persistent_plan_config(const CostParams &p, int d, int sm_count, Per
                                    bool *ok) {
   *ok = false;
   if (p.k == 0 || p.m == 0 || p.n_noise != 1) return cudaSuccess;
-  const void *kern = d == 5 ? persistent_kernel_of<5>(grid_mode_of(p), p.use_limits != 0)
-                            : persistent_kernel_of<4>(grid_mode_of(p), p.use_limits != 0);
+  const void *kern = d == 5 ? persistent_kernel_of<5>(grid_mode_of(p), p.use_limits != 0, p.fk_on != 0)
+                            : persistent_kernel_of<4>(grid_mode_of(p), p.use_limits != 0, p.fk_on != 0);
   // fewest waypoints per thread (shortest dependent chain) whose grid is co-resident
   for (uint32_t wpp = 1; wpp <= 4; wpp *= 2) {
     const uint32_t need = (p.n + wpp - 1) / wpp;
@@ -1811,8 +1824,8 @@ cudaError_t persistent_plan_config(const CostParams &p, int d, int sm_count, Per
 
 cudaError_t launch_persistent_plan(const PersistParams &q, int d, cudaStream_t st) {
   const CostParams &p = q.cost;
-  const void *kern = d == 5 ? persistent_kernel_of<5>(grid_mode_of(p), p.use_limits != 0)
-                            : persistent_kernel_of<4>(grid_mode_of(p), p.use_limits != 0);
+  const void *kern = d == 5 ? persistent_kernel_of<5>(grid_mode_of(p), p.use_limits != 0, p.fk_on != 0)
+                            : persistent_kernel_of<4>(grid_mode_of(p), p.use_limits != 0, p.fk_on != 0);
   const uint32_t T = 1u << q.t_log2, SB = 256 / T;
   const size_t smem = persistent_smem(p, d, T, p.wpp);
   if (smem > 48 * 1024) {

@@ -220,8 +220,11 @@ def test_model_cost_parity(capi, oracle_mod, k, m, n, d, n_noise, grid, frame, s
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("update_mode", [0, 1])
-def test_model_plan_parity(capi, oracle_mod, update_mode):
+@pytest.mark.parametrize("update_mode,persist", [(0, "1"), (0, "0"), (1, "1")])
+def test_model_plan_parity(capi, oracle_mod, monkeypatch, update_mode, persist):
+    """Planner loop on the FK model: the persistent one-launch planner (keep-best), the
+    launch-per-iteration graph, and the weighted update rule."""
+    monkeypatch.setenv("DOAPP_PERSIST", persist)
     k, m, n, iters = 2, 96, 48, 6
     om = oracle_mod.fk_model_rexarm()
     kw = dict(sigma=0.05, select_mode=1, update_mode=update_mode, update_gain=1e-3)
@@ -234,7 +237,7 @@ def test_model_plan_parity(capi, oracle_mod, update_mode):
     plain = ctx.plan(synth.START, synth.GOALS[1], init, iters)["best_traj"].copy()
     ctx.set_fk_model(capi.fk_model_rexarm())
     a = ctx.plan(synth.START, synth.GOALS[1], init, iters)
-    assert ctx.plan_mode() == 0  # the FK model runs through cost_kernel, one launch per iteration
+    assert (ctx.plan_mode() & 1) == (1 if update_mode == 0 and persist == "1" else 0)
     b = orc.plan(synth.START, init, iters)
     st = ctx.plan_state()
     assert np.array_equal(st["trajectories"].view(np.uint32), b["trajectories"].view(np.uint32))
