@@ -88,8 +88,7 @@ struct doapp_ctx {
   DevBuf<int32_t> coll, final_coll;
   DevBuf<unsigned long long> keys, keys_float;
   DevBuf<uint32_t> cur_hi;
-  DevBuf<unsigned long long> pkeys; // persistent planner: 3 x [k] rotating keys
-  DevBuf<unsigned int> pbar;        // ... and its grid barrier counter
+  DevBuf<unsigned long long> pkeys; // persistent planner: 3 x [k] rotating barrier words {key, arrivals - 1}
   int persist_mode = -1;            // DOAPP_PERSIST=0/1: never / whenever legal
   // peer-memory argmin merge: own mailbox [2 epochs][3][k][8] + result [3][k], the ranks' mailboxes
   DevBuf<unsigned long long> mailbox, presult;
@@ -382,10 +381,8 @@ doapp_status enqueue_plan_persistent(doapp_ctx *ctx, PersistParams q, uint32_t i
   CU(cudaMemsetAsync(ctx->keys.p, 0xFF, sizeof(unsigned long long) * 3 * k, ctx->stream));
   // seed pass: score the k unperturbed trajectories (gt.cu:180-191); its keys seed cur_hi
   ST(launch_pass(ctx, climber_cost_params(ctx), PEND_NONE, 0, NOISE_ZERO, nullptr, true));
-  ST(ensure(ctx, ctx->pkeys, 3 * k));
-  ST(ensure(ctx, ctx->pbar, 1));
-  CU(cudaMemsetAsync(ctx->pkeys.p, 0xFF, sizeof(unsigned long long) * 3 * k, ctx->stream));
-  CU(cudaMemsetAsync(ctx->pbar.p, 0, sizeof(unsigned int), ctx->stream));
+  ST(ensure(ctx, ctx->pkeys, 3 * k * 2));
+  CU(cudaMemsetAsync(ctx->pkeys.p, 0xFF, sizeof(unsigned long long) * 3 * k * 2, ctx->stream));
   CostParams &p = q.cost;
   p.traj = traj_half_ptr(ctx, ctx->traj_s);
   p.traj_next = traj_half_ptr(ctx, 1 - ctx->traj_s);
@@ -397,7 +394,6 @@ doapp_status enqueue_plan_persistent(doapp_ctx *ctx, PersistParams q, uint32_t i
   p.noise_t0 = 0;
   q.iters = iters;
   q.keys3 = ctx->pkeys.p;
-  q.barrier = ctx->pbar.p;
   q.noise_base = noise_mode == NOISE_EXTERNAL ? ctx->noise.p : nullptr;
   q.noise_iter_stride = (uint64_t)c.num_climbers * ctx->m_global * c.waypoint_dim;
   q.nranks = 1;
@@ -787,7 +783,7 @@ void doapp_destroy(doapp_ctx *ctx) {
   release(ctx->pts); release(ctx->coll); release(ctx->final_coll); release(ctx->keys);
   release(ctx->keys_float); release(ctx->cur_hi); release(ctx->found); release(ctx->grid_cells);
   release(ctx->lookup_coll); release(ctx->lookup_idx); release(ctx->dbg_a); release(ctx->dbg_b);
-  release(ctx->dbg_c); release(ctx->vbad); release(ctx->usum); release(ctx->pkeys); release(ctx->pbar);
+  release(ctx->dbg_c); release(ctx->vbad); release(ctx->usum); release(ctx->pkeys);
   for (int r = 0; r < 8; ++r)
     if (ctx->peer_ready && r != ctx->peer_rank && ctx->peer_mbox[r]) cudaIpcCloseMemHandle(ctx->peer_mbox[r]);
   release(ctx->mailbox); release(ctx->presult); release(ctx->depth); release(ctx->fk_dev);

@@ -658,15 +658,24 @@ __global__ void __launch_bounds__(kMaxCostThreads)
 // memory across iterations, and one grid-wide barrier per iteration publishes the argmin key.
 // Arithmetic, noise, keys and tie-breaking are those of cost_kernel, so the result is
 // bit-identical to the launch-per-iteration path.
-__device__ __forceinline__ void grid_arrive(unsigned int *counter) {
+// Per-iteration, per-climber barrier word: 16 bytes {argmin key, arrivals - 1}, all ones when
+// armed.  A CTA publishes with atomicMin on the key, a fence, then atomicAdd on the count; the
+// waiter polls BOTH with one 16-byte load (one transaction on one L2 sector): when the count is
+// complete every atomicMin ordered before an arrival has been performed on that sector, so the
+// key half of the same load is the final minimum -- no second round trip to re-read the key.
+// The key is the only data that crosses CTAs here, so no acquire fence follows the poll.
+__device__ __forceinline__ void grid_publish(unsigned long long *word, unsigned long long key) {
+  atomicMin(word, key);
   __threadfence();
-  atomicAdd(counter, 1u);
+  atomicAdd(word + 1, 1ull);
 }
-__device__ __forceinline__ void grid_wait(const unsigned int *counter, unsigned int target) {
-  unsigned int v;
+__device__ __forceinline__ unsigned long long grid_wait_key(const unsigned long long *word,
+                                                            unsigned long long arrivals) {
+  unsigned long long key, cnt;
   do {
-    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(counter) : "memory");
-  } while (v < target);
+    asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(key), "=l"(cnt) : "l"(word) : "memory");
+  } while (cnt + 1 < arrivals); // armed: cnt + 1 == 0
+  return key;
 }
 
 template <int D, int GM, bool LIM, bool FKM>
@@ -691,7 +700,6 @@ __global__ void __launch_bounds__(256) plan_persistent_kernel(const __grid_const
   const bool active = t < P.m;
   t = active ? t : P.m - 1;
   const uint32_t tg = (uint32_t)(P.sample_offset + t);
-  const unsigned int num_ctas = gridDim.x * gridDim.y;
 
   float start[D];
 #pragma unroll
@@ -816,20 +824,22 @@ __global__ void __launch_bounds__(256) plan_persistent_kernel(const __grid_const
         atomicMin(skey, ((unsigned long long)key_hi(P.select_mode, score) << 32) | tg);
     }
     __syncthreads();
-    unsigned long long *kcur = Q.keys3 + (size_t)(it % 3) * k;
+    unsigned long long *kcur = Q.keys3 + ((size_t)(it % 3) * k + c) * 2;
     if (threadIdx.x == 0) {
-      atomicMin(kcur + c, *skey);
+      const unsigned long long mine = *skey;
       *skey = kKeyNone;
-      // re-arm the buffer of iteration it + 1: its last readers passed barrier it - 1
-      if (blockIdx.x == 0) Q.keys3[(size_t)((it + 1) % 3) * k + c] = kKeyNone;
-      grid_arrive(Q.barrier);
+      // re-arm the word of iteration it + 1: its last readers passed barrier it - 1
+      if (blockIdx.x == 0)
+        *reinterpret_cast<ulonglong2 *>(Q.keys3 + ((size_t)((it + 1) % 3) * k + c) * 2) =
+            make_ulonglong2(kKeyNone, kKeyNone);
+      grid_publish(kcur, mine);
     }
     if (it + 1 < Q.iters) gen_noise(it + 1); // overlaps the barrier
     unsigned long long best;
     if (Q.nranks <= 1) {
-      if (threadIdx.x == 0) grid_wait(Q.barrier, (it + 1) * num_ctas);
+      if (threadIdx.x == 0) *sbest = grid_wait_key(kcur, gridDim.x);
       __syncthreads();
-      best = __ldcg(kcur + c);
+      best = *sbest;
     } else {
       // The climber's first CTA waits for the rank's CTAs, then stores the rank's key into the
       // mailbox of every rank (its own included): one 8-byte store per peer over NVLink,
@@ -840,10 +850,10 @@ __global__ void __launch_bounds__(256) plan_persistent_kernel(const __grid_const
       const size_t cur = ((size_t)(it % 3) * k + c) * 8;
       if (blockIdx.x == 0 && threadIdx.x < 32) {
         const uint32_t ln = threadIdx.x;
-        if (ln == 0) grid_wait(Q.barrier, (it + 1) * num_ctas);
-        __syncwarp();
+        unsigned long long local = 0;
+        if (ln == 0) local = grid_wait_key(kcur, gridDim.x);
+        local = __shfl_sync(kFull, local, 0);
         if (ln < Q.nranks) {
-          const unsigned long long local = __ldcg(kcur + c);
           Q.mailbox[Q.rank][((size_t)((it + 1) % 3) * k + c) * 8 + ln] = kKeyNone;
           asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(Q.mailbox[ln] + cur + Q.rank), "l"(local) : "memory");
         }

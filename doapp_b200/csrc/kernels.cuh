@@ -117,8 +117,7 @@ struct PersistParams {
   CostParams cost;
   uint32_t iters;
   uint32_t t_log2;             // threads per sample = 2^t_log2, each owning cost.wpp waypoints
-  unsigned long long *keys3;   // [3][k] rotating per-iteration argmin keys (all kKeyNone at launch)
-  unsigned int *barrier;       // monotonic arrival counter, 0 at launch
+  unsigned long long *keys3;   // [3][k] rotating per-iteration barrier words {argmin key, arrivals - 1}, 16 B each (all ones at launch)
   const float *noise_base;     // external noise of iteration 0 (or nullptr: Philox)
   uint64_t noise_iter_stride;  // elements between iterations in the external buffer
   // Multi-GPU (nranks > 1): the ranks' argmin keys are merged through peer memory over NVLink
