@@ -679,12 +679,15 @@ __device__ __forceinline__ unsigned long long grid_wait_key(const unsigned long 
 }
 
 template <int D, int GM, bool LIM, bool FKM>
-__global__ void __launch_bounds__(256) plan_persistent_kernel(const __grid_constant__ PersistParams Q) {
+__global__ void __launch_bounds__(kPersistThreads) plan_persistent_kernel(const __grid_constant__ PersistParams Q) {
   const CostParams &P = Q.cost;
   constexpr bool FIDX = GM == GM_U8_CDG || GM == GM_F32_CDG;
   extern __shared__ __align__(16) float smem[];
-  const uint32_t T = 1u << Q.t_log2, SB = blockDim.x >> Q.t_log2;
+  const uint32_t T = 1u << Q.t_log2, SB = kPersistComputeThreads >> Q.t_log2;
   const uint32_t WS = T * P.wpp; // waypoint slots per sample (>= n)
+  // warps 0..7 cost the samples; warp 8 (the helper) does the grid-wide key exchange meanwhile
+  const bool helper = threadIdx.x >= kPersistComputeThreads;
+  const uint32_t hl = threadIdx.x - kPersistComputeThreads; // helper lane
   float *sbase = smem;                                   // [D][npad]  current trajectory
   float *spart = sbase + (size_t)D * P.npad;             // [SB][WS]   per-waypoint sum of acc^2
   float *slim = spart + (size_t)SB * WS;                 // [SB][WS]   (limits)
@@ -715,6 +718,7 @@ __global__ void __launch_bounds__(256) plan_persistent_kernel(const __grid_const
   // one d-vector of noise per sample and iteration (generate_trajectories.cu:37-44): the
   // sample's first three threads draw one Box-Muller pair each
   auto gen_noise = [&](uint32_t it) {
+    if (helper) return;
     if (P.noise_mode == NOISE_PHILOX) {
       if (T >= 4) {
         if (r < 3) {
@@ -748,69 +752,121 @@ __global__ void __launch_bounds__(256) plan_persistent_kernel(const __grid_const
 
   const uint32_t w0 = r * P.wpp;
   const uint32_t w1 = (w0 + P.wpp) < P.n ? (w0 + P.wpp) : P.n;
-  for (uint32_t it = 0; it < Q.iters; ++it) {
-    float eps[D];
-#pragma unroll
-    for (int j = 0; j < D; ++j) eps[j] = seps[s * 8 + j];
-    auto noisy = [&](uint32_t w, int j) -> float { return dm::add_(sbase[j * P.npad + w], eps[j]); };
-    uint32_t w = w0;
-    float xprev[D], vprev[D];
-    bool fine1 = P.fast_ok != 0, fine2 = fine1;
-    if (w == 0) {
-#pragma unroll
-      for (int j = 0; j < D; ++j) {
-        xprev[j] = vprev[j] = start[j];
-        fine1 = fine1 & dm::fine_angle(start[j]);
-      }
-    } else if (w < P.n) {
-#pragma unroll
-      for (int j = 0; j < D; ++j) {
-        const float x1 = noisy(w - 1, j);
-        const float x2 = w >= 2 ? noisy(w - 2, j) : start[j];
-        xprev[j] = x1;
-        vprev[j] = dm::div_fast(dm::sub_(x1, x2), P.dt_div);
-        fine1 = fine1 & dm::fine_angle(x1);
-        fine2 = fine2 & dm::fine_angle(x2);
-      }
+
+  // Helper warp: sends the CTA's key of iteration it (taken from *skey into h_mine earlier)
+  // into the grid-wide argmin, waits for the merged key -- with several ranks through the
+  // NVLink peer mailboxes -- and leaves it in *sbest.
+  unsigned long long h_mine = kKeyNone;
+  auto helper_exchange = [&](uint32_t it) {
+    unsigned long long *kcur = Q.keys3 + ((size_t)(it % 3) * k + c) * 2;
+    if (hl == 0) {
+      // re-arm the word of iteration it + 1: its last readers passed barrier it - 1
+      if (blockIdx.x == 0)
+        *reinterpret_cast<ulonglong2 *>(Q.keys3 + ((size_t)((it + 1) % 3) * k + c) * 2) =
+            make_ulonglong2(kKeyNone, kKeyNone);
+      grid_publish(kcur, h_mine);
     }
-    int coll = 0;
-    for (; w < w1; ++w) {
-      float x[D], vnew[D];
+    if (Q.nranks <= 1) {
+      if (hl == 0) *sbest = grid_wait_key(kcur, gridDim.x);
+    } else {
+      // The climber's first CTA waits for the rank's CTAs, then stores the rank's key into the
+      // mailbox of every rank (its own included): one 8-byte store per peer over NVLink,
+      // payload = flag.  EVERY CTA polls the rank's own mailbox -- local memory -- for the
+      // nranks keys of this iteration and takes the minimum.  Buffers rotate three ways; the
+      // slots of iteration it + 1 are re-armed before this rank's key of iteration it leaves,
+      // so no peer can be writing them yet and no local CTA is still reading them.
+      const size_t cur = ((size_t)(it % 3) * k + c) * 8;
+      if (blockIdx.x == 0) {
+        unsigned long long local = 0;
+        if (hl == 0) local = grid_wait_key(kcur, gridDim.x);
+        local = __shfl_sync(kFull, local, 0);
+        if (hl < Q.nranks) {
+          Q.mailbox[Q.rank][((size_t)((it + 1) % 3) * k + c) * 8 + hl] = kKeyNone;
+          asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(Q.mailbox[hl] + cur + Q.rank), "l"(local) : "memory");
+        }
+      }
+      unsigned long long v = kKeyNone;
+      if (hl < Q.nranks) {
+        const unsigned long long *mine = Q.mailbox[Q.rank] + cur + hl;
+        do {
+          asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(mine) : "memory");
+        } while (v == kKeyNone);
+      }
+      v = warp_min_u64(v);
+      if (hl == 0) *sbest = v;
+    }
+  };
+
+  // One iteration's cost pass over the CTA's samples with the noise in seps and the trajectory
+  // in sbase; leaves the CTA's minimum key in *skey.  While the eight compute warps do that, the
+  // helper warp runs the key exchange of the PREVIOUS iteration (exchange_prev).
+  auto evaluate = [&](bool exchange_prev, uint32_t prev_it) {
+    if (helper) {
+      if (exchange_prev) helper_exchange(prev_it);
+    } else {
+      float eps[D];
 #pragma unroll
-      for (int j = 0; j < D; ++j) x[j] = noisy(w, j);
-      float a2, l2;
-      int cw;
-      const bool fine0 = waypoint_cost<D, GM, FIDX, LIM, true, FKM>(P, x, xprev, vprev, vnew, &a2, &l2, &cw);
-      const bool fast_valid = fine0 & fine1 & fine2;
-      fine2 = fine1;
-      fine1 = fine0 & (P.fast_ok != 0);
-      if (!fast_valid) {
-        WpIn<D> in;
+      for (int j = 0; j < D; ++j) eps[j] = seps[s * 8 + j];
+      auto noisy = [&](uint32_t w, int j) -> float { return dm::add_(sbase[j * P.npad + w], eps[j]); };
+      uint32_t w = w0;
+      float xprev[D], vprev[D];
+      bool fine1 = P.fast_ok != 0, fine2 = fine1;
+      if (w == 0) {
 #pragma unroll
         for (int j = 0; j < D; ++j) {
-          in.x[j] = x[j];
-          in.xprev[j] = xprev[j];
-          in.vprev[j] = vprev[j];
+          xprev[j] = vprev[j] = start[j];
+          fine1 = fine1 & dm::fine_angle(start[j]);
         }
-        const WpOut<D> o = waypoint_cost_general<D, GM, FIDX, LIM, FKM>(P, in);
+      } else if (w < P.n) {
 #pragma unroll
-        for (int j = 0; j < D; ++j) vnew[j] = o.vnew[j];
-        a2 = o.a2;
-        l2 = o.l2;
-        cw = o.coll;
+        for (int j = 0; j < D; ++j) {
+          const float x1 = noisy(w - 1, j);
+          const float x2 = w >= 2 ? noisy(w - 2, j) : start[j];
+          xprev[j] = x1;
+          vprev[j] = dm::div_fast(dm::sub_(x1, x2), P.dt_div);
+          fine1 = fine1 & dm::fine_angle(x1);
+          fine2 = fine2 & dm::fine_angle(x2);
+        }
       }
+      int coll = 0;
+      for (; w < w1; ++w) {
+        float x[D], vnew[D];
 #pragma unroll
-      for (int j = 0; j < D; ++j) {
-        xprev[j] = x[j];
-        vprev[j] = vnew[j];
+        for (int j = 0; j < D; ++j) x[j] = noisy(w, j);
+        float a2, l2;
+        int cw;
+        const bool fine0 = waypoint_cost<D, GM, FIDX, LIM, true, FKM>(P, x, xprev, vprev, vnew, &a2, &l2, &cw);
+        const bool fast_valid = fine0 & fine1 & fine2;
+        fine2 = fine1;
+        fine1 = fine0 & (P.fast_ok != 0);
+        if (!fast_valid) {
+          WpIn<D> in;
+#pragma unroll
+          for (int j = 0; j < D; ++j) {
+            in.x[j] = x[j];
+            in.xprev[j] = xprev[j];
+            in.vprev[j] = vprev[j];
+          }
+          const WpOut<D> o = waypoint_cost_general<D, GM, FIDX, LIM, FKM>(P, in);
+#pragma unroll
+          for (int j = 0; j < D; ++j) vnew[j] = o.vnew[j];
+          a2 = o.a2;
+          l2 = o.l2;
+          cw = o.coll;
+        }
+#pragma unroll
+        for (int j = 0; j < D; ++j) {
+          xprev[j] = x[j];
+          vprev[j] = vnew[j];
+        }
+        coll += cw;
+        spart[s * WS + w] = a2;
+        if (LIM) slim[s * WS + w] = l2;
       }
-      coll += cw;
-      spart[s * WS + w] = a2;
-      if (LIM) slim[s * WS + w] = l2;
+      if (coll) atomicAdd(scoll + s, coll); // integer: order-independent
     }
-    if (coll) atomicAdd(scoll + s, coll); // integer: order-independent
     __syncthreads();
-    if (r == 0) { // fixed order: left fold over the waypoints (oracle ORC_SUM_WAYPOINT)
+    if (!helper && r == 0) { // fixed order: left fold over the waypoints (oracle ORC_SUM_WAYPOINT)
       float total = 0.0f, ltotal = 0.0f;
       for (uint32_t ww = 0; ww < P.n; ++ww) {
         total = dm::add_(total, spart[s * WS + ww]);
@@ -824,79 +880,73 @@ __global__ void __launch_bounds__(256) plan_persistent_kernel(const __grid_const
         atomicMin(skey, ((unsigned long long)key_hi(P.select_mode, score) << 32) | tg);
     }
     __syncthreads();
-    unsigned long long *kcur = Q.keys3 + ((size_t)(it % 3) * k + c) * 2;
-    if (threadIdx.x == 0) {
-      const unsigned long long mine = *skey;
-      *skey = kKeyNone;
-      // re-arm the word of iteration it + 1: its last readers passed barrier it - 1
-      if (blockIdx.x == 0)
-        *reinterpret_cast<ulonglong2 *>(Q.keys3 + ((size_t)((it + 1) % 3) * k + c) * 2) =
-            make_ulonglong2(kKeyNone, kKeyNone);
-      grid_publish(kcur, mine);
-    }
-    if (it + 1 < Q.iters) gen_noise(it + 1); // overlaps the barrier
-    unsigned long long best;
-    if (Q.nranks <= 1) {
-      if (threadIdx.x == 0) *sbest = grid_wait_key(kcur, gridDim.x);
-      __syncthreads();
-      best = *sbest;
-    } else {
-      // The climber's first CTA waits for the rank's CTAs, then stores the rank's key into the
-      // mailbox of every rank (its own included): one 8-byte store per peer over NVLink,
-      // payload = flag.  EVERY CTA polls the rank's own mailbox -- local memory -- for the
-      // nranks keys of this iteration and takes the minimum.  Buffers rotate three ways; the
-      // slots of iteration it + 1 are re-armed before this rank's key of iteration it leaves,
-      // so no peer can be writing them yet and no local CTA is still reading them.
-      const size_t cur = ((size_t)(it % 3) * k + c) * 8;
-      if (blockIdx.x == 0 && threadIdx.x < 32) {
-        const uint32_t ln = threadIdx.x;
-        unsigned long long local = 0;
-        if (ln == 0) local = grid_wait_key(kcur, gridDim.x);
-        local = __shfl_sync(kFull, local, 0);
-        if (ln < Q.nranks) {
-          Q.mailbox[Q.rank][((size_t)((it + 1) % 3) * k + c) * 8 + ln] = kKeyNone;
-          asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(Q.mailbox[ln] + cur + Q.rank), "l"(local) : "memory");
-        }
-      }
-      if (threadIdx.x < 32) {
-        unsigned long long v = kKeyNone;
-        if (threadIdx.x < Q.nranks) {
-          const unsigned long long *mine = Q.mailbox[Q.rank] + cur + threadIdx.x;
-          do {
-            asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(mine) : "memory");
-          } while (v == kKeyNone);
-        }
-        v = warp_min_u64(v);
-        if (threadIdx.x == 0) *sbest = v;
-      }
-      __syncthreads();
-      best = *sbest;
-    }
-    // keep-best (generate_trajectories.cu:225-241, D5/D6 fixed): every CTA applies it to its copy
+  };
+
+  // Applies the keep-best of iteration it (merged key in *sbest) to the CTA's copy of the
+  // trajectory (generate_trajectories.cu:225-241, D5/D6 fixed).  Returns whether the trajectory
+  // changed (block-uniform).
+  auto apply = [&](uint32_t it) -> bool {
+    const unsigned long long best = *sbest;
     const uint32_t hi = (uint32_t)(best >> 32), win = (uint32_t)best;
-    if (hi < cur_hi) { // block-uniform
-      cur_hi = hi;
-      found = true;
-      if (threadIdx.x < 3) {
-        float a = 0.0f, b = 0.0f;
-        const uint32_t q = threadIdx.x;
-        if (P.noise_mode == NOISE_PHILOX) {
-          dm::noise_pair(P.seed_lo, P.seed_hi, P.sigma, it, c, win, 0, q, &a, &b);
-        } else if (P.noise_mode == NOISE_EXTERNAL) {
-          const float *pn = Q.noise_base + (size_t)it * Q.noise_iter_stride +
-                            ((size_t)c * P.noise_m + (size_t)(win - P.noise_t0)) * D;
-          a = 2 * q < D ? __ldg(pn + 2 * q) : 0.0f;
-          b = 2 * q + 1 < D ? __ldg(pn + 2 * q + 1) : 0.0f;
+    if (hi >= cur_hi) return false;
+    cur_hi = hi;
+    found = true;
+    if (threadIdx.x < 3) {
+      float a = 0.0f, b = 0.0f;
+      const uint32_t q = threadIdx.x;
+      if (P.noise_mode == NOISE_PHILOX) {
+        dm::noise_pair(P.seed_lo, P.seed_hi, P.sigma, it, c, win, 0, q, &a, &b);
+      } else if (P.noise_mode == NOISE_EXTERNAL) {
+        const float *pn = Q.noise_base + (size_t)it * Q.noise_iter_stride +
+                          ((size_t)c * P.noise_m + (size_t)(win - P.noise_t0)) * D;
+        a = 2 * q < D ? __ldg(pn + 2 * q) : 0.0f;
+        b = 2 * q + 1 < D ? __ldg(pn + 2 * q + 1) : 0.0f;
+      }
+      if (2 * q < D) swin[2 * q] = a;
+      if (2 * q + 1 < D) swin[2 * q + 1] = b;
+    }
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < (uint32_t)D * P.npad; i += blockDim.x) {
+      const uint32_t j = i / P.npad;
+      if (i - j * P.npad < P.n) sbase[i] = dm::add_(sbase[i], swin[j]);
+    }
+    __syncthreads();
+    return true;
+  };
+
+  // Software-pipelined keep-best loop.  Most iterations do not improve the trajectory, so the
+  // cost pass of iteration ev runs SPECULATIVELY on the current trajectory while the helper
+  // warp exchanges the keys of iteration ev - 1 (two L2 round trips, or NVLink ones, that the
+  // compute warps never wait for).  If that exchange does bring an update, the pass is repeated
+  // on the updated trajectory (same noise) before the key of iteration ev is taken.  The keys
+  // that leave the CTA are therefore exactly those of the sequential loop.
+  if (Q.iters > 0) {
+    uint32_t ev = 0;
+    bool pending = false; // the key of iteration ev - 1 is taken but not yet exchanged
+    for (;;) {
+      evaluate(pending, ev - 1); // iteration ev
+      if (pending) {
+        pending = false;
+        if (apply(ev - 1)) { // mis-speculated: discard, evaluate ev again
+          if (threadIdx.x == 0) *skey = kKeyNone;
+          __syncthreads();
+          continue;
         }
-        if (2 * q < D) swin[2 * q] = a;
-        if (2 * q + 1 < D) swin[2 * q + 1] = b;
       }
-      __syncthreads();
-      for (uint32_t i = threadIdx.x; i < (uint32_t)D * P.npad; i += blockDim.x) {
-        const uint32_t j = i / P.npad;
-        if (i - j * P.npad < P.n) sbase[i] = dm::add_(sbase[i], swin[j]);
+      if (helper && hl == 0) { // the key of iteration ev is final: take it
+        h_mine = *skey;
+        *skey = kKeyNone;
       }
+      pending = true;
+      if (ev + 1 == Q.iters) {
+        if (helper) helper_exchange(ev);
+        __syncthreads();
+        apply(ev);
+        break;
+      }
+      gen_noise(ev + 1);
       __syncthreads();
+      ++ev;
     }
   }
   if (blockIdx.x == 0) { // the climber's final state, for the final scoring pass
@@ -1818,7 +1868,7 @@ cudaError_t persistent_plan_config(const CostParams &p, int d, int sm_count, Per
       if (e != cudaSuccess) return e;
     }
     int per_sm = 0;
-    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 256, smem);
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kPersistThreads, smem);
     if (e != cudaSuccess) return e;
     const uint64_t ctas = (uint64_t)p.k * ((p.m + SB - 1) / SB);
     if (ctas > (uint64_t)per_sm * sm_count) continue;
@@ -1843,7 +1893,7 @@ cudaError_t launch_persistent_plan(const PersistParams &q, int d, cudaStream_t s
     if (e != cudaSuccess) return e;
   }
   void *args[] = {(void *)&q};
-  return cudaLaunchCooperativeKernel(kern, dim3((p.m + SB - 1) / SB, p.k), dim3(256), args, smem, st);
+  return cudaLaunchCooperativeKernel(kern, dim3((p.m + SB - 1) / SB, p.k), dim3(kPersistThreads), args, smem, st);
 }
 
 template <int D>

@@ -113,6 +113,8 @@ struct CostParams {
 // generate_trajectories.cu:197-253 in ONE cooperative launch, one grid-wide barrier per
 // iteration.  `cost` carries the problem (traj = input half, traj_next = output half,
 // pend_keys = the seed pass's keys, cur_hi_out / found_better = final state).
+// plan_persistent_kernel: 8 compute warps + 1 helper warp (the grid-wide key exchange)
+constexpr int kPersistComputeThreads = 256, kPersistThreads = kPersistComputeThreads + 32;
 struct PersistParams {
   CostParams cost;
   uint32_t iters;
