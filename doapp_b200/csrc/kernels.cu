@@ -691,11 +691,11 @@ __global__ void __launch_bounds__(kPersistThreads) plan_persistent_kernel(const 
   float *sbase = smem;                                   // [D][npad]  current trajectory
   float *spart = sbase + (size_t)D * P.npad;             // [SB][WS]   per-waypoint sum of acc^2
   float *slim = spart + (size_t)SB * WS;                 // [SB][WS]   (limits)
-  float *seps = slim + (LIM ? (size_t)SB * WS : 0);      // [SB][8]    this iteration's noise
-  float *swin = seps + (size_t)SB * 8;                   // [8]        winner's noise
+  float *seps = slim + (LIM ? (size_t)SB * WS : 0);      // [2][SB][8] noise of iteration it in half it & 1
+  float *swin = seps + (size_t)SB * 16;                  // [8]        winner's noise
   int *scoll = (int *)(swin + 8);                        // [SB]
-  unsigned long long *skey = (unsigned long long *)(scoll + ((SB + 1) & ~1u)); // [1] CTA minimum
-  unsigned long long *sbest = skey + 1;                                        // [1] merged minimum
+  unsigned long long *skey = (unsigned long long *)(scoll + ((SB + 1) & ~1u)); // [2] CTA minimum of iteration it in slot it & 1
+  unsigned long long *sbest = skey + 2;                                        // [2] merged minimum of iteration it in slot it & 1
 
   const uint32_t c = blockIdx.y, k = gridDim.y;
   const uint32_t s = threadIdx.x >> Q.t_log2, r = threadIdx.x & (T - 1);
@@ -710,33 +710,37 @@ __global__ void __launch_bounds__(kPersistThreads) plan_persistent_kernel(const 
   for (uint32_t i = threadIdx.x; i < (uint32_t)D * P.npad; i += blockDim.x)
     sbase[i] = __ldg(P.traj + (size_t)c * D * P.npad + i);
   if (threadIdx.x < SB) scoll[threadIdx.x] = 0;
-  if (threadIdx.x == 0) *skey = kKeyNone;
+  if (threadIdx.x < 2) skey[threadIdx.x] = kKeyNone;
   // the seed pass scored the unperturbed trajectory (generate_trajectories.cu:180-191)
   uint32_t cur_hi = (uint32_t)(__ldg(P.pend_keys + c) >> 32);
   bool found = false;
 
   // one d-vector of noise per sample and iteration (generate_trajectories.cu:37-44): the
   // sample's first three threads draw one Box-Muller pair each
+  // (threads T/2 .. T/2 + 2 of the sample when T >= 8: with T = 64 a different warp than the one whose
+  // lane 0 folds the sample's sums, so the two overlap)
+  const uint32_t rn = r - (T >= 8 ? (T >> 1) : 0u); // 0, 1, 2 on the noise threads
   auto gen_noise = [&](uint32_t it) {
     if (helper) return;
+    float *se = seps + (size_t)(it & 1) * SB * 8 + s * 8;
     if (P.noise_mode == NOISE_PHILOX) {
       if (T >= 4) {
-        if (r < 3) {
+        if (rn < 3) {
           float a, b;
-          dm::noise_pair(P.seed_lo, P.seed_hi, P.sigma, it, c, tg, 0, r, &a, &b);
-          if (2 * r < D) seps[s * 8 + 2 * r] = a;
-          if (2 * r + 1 < D) seps[s * 8 + 2 * r + 1] = b;
+          dm::noise_pair(P.seed_lo, P.seed_hi, P.sigma, it, c, tg, 0, rn, &a, &b);
+          if (2 * rn < D) se[2 * rn] = a;
+          if (2 * rn + 1 < D) se[2 * rn + 1] = b;
         }
       } else if (r == 0) {
         float e[D];
         dm::noise_vec<D>(P.seed_lo, P.seed_hi, P.sigma, it, c, tg, 0, e);
 #pragma unroll
-        for (int j = 0; j < D; ++j) seps[s * 8 + j] = e[j];
+        for (int j = 0; j < D; ++j) se[j] = e[j];
       }
     } else if (r == 0) {
 #pragma unroll
       for (int j = 0; j < D; ++j)
-        seps[s * 8 + j] =
+        se[j] =
             P.noise_mode == NOISE_EXTERNAL
                 ? __ldg(Q.noise_base + (size_t)it * Q.noise_iter_stride +
                         ((size_t)c * P.noise_m + (size_t)(tg - P.noise_t0)) * D + j)
@@ -755,7 +759,7 @@ __global__ void __launch_bounds__(kPersistThreads) plan_persistent_kernel(const 
 
   // Helper warp: sends the CTA's key of iteration it (taken from *skey into h_mine earlier)
   // into the grid-wide argmin, waits for the merged key -- with several ranks through the
-  // NVLink peer mailboxes -- and leaves it in *sbest.
+  // NVLink peer mailboxes -- and leaves it in sbest[it & 1].
   unsigned long long h_mine = kKeyNone;
   auto helper_exchange = [&](uint32_t it) {
     unsigned long long *kcur = Q.keys3 + ((size_t)(it % 3) * k + c) * 2;
@@ -767,7 +771,7 @@ __global__ void __launch_bounds__(kPersistThreads) plan_persistent_kernel(const 
       grid_publish(kcur, h_mine);
     }
     if (Q.nranks <= 1) {
-      if (hl == 0) *sbest = grid_wait_key(kcur, gridDim.x);
+      if (hl == 0) sbest[it & 1] = grid_wait_key(kcur, gridDim.x);
     } else {
       // The climber's first CTA waits for the rank's CTAs, then stores the rank's key into the
       // mailbox of every rank (its own included): one 8-byte store per peer over NVLink,
@@ -793,20 +797,20 @@ __global__ void __launch_bounds__(kPersistThreads) plan_persistent_kernel(const 
         } while (v == kKeyNone);
       }
       v = warp_min_u64(v);
-      if (hl == 0) *sbest = v;
+      if (hl == 0) sbest[it & 1] = v;
     }
   };
 
   // One iteration's cost pass over the CTA's samples with the noise in seps and the trajectory
   // in sbase; leaves the CTA's minimum key in *skey.  While the eight compute warps do that, the
   // helper warp runs the key exchange of the PREVIOUS iteration (exchange_prev).
-  auto evaluate = [&](bool exchange_prev, uint32_t prev_it) {
+  auto evaluate = [&](uint32_t ev, bool exchange_prev) {
     if (helper) {
-      if (exchange_prev) helper_exchange(prev_it);
+      if (exchange_prev) helper_exchange(ev - 1);
     } else {
       float eps[D];
 #pragma unroll
-      for (int j = 0; j < D; ++j) eps[j] = seps[s * 8 + j];
+      for (int j = 0; j < D; ++j) eps[j] = seps[(size_t)(ev & 1) * SB * 8 + s * 8 + j];
       auto noisy = [&](uint32_t w, int j) -> float { return dm::add_(sbase[j * P.npad + w], eps[j]); };
       uint32_t w = w0;
       float xprev[D], vprev[D];
@@ -864,8 +868,11 @@ __global__ void __launch_bounds__(kPersistThreads) plan_persistent_kernel(const 
         if (LIM) slim[s * WS + w] = l2;
       }
       if (coll) atomicAdd(scoll + s, coll); // integer: order-independent
+      // the compute warps only: the helper joins at the end of the pass, so its exchange also
+      // overlaps the fold
+      asm volatile("bar.sync 1, %0;" ::"n"(kPersistComputeThreads) : "memory");
+      if (ev + 1 < Q.iters) gen_noise(ev + 1); // into the other half of seps
     }
-    __syncthreads();
     if (!helper && r == 0) { // fixed order: left fold over the waypoints (oracle ORC_SUM_WAYPOINT)
       float total = 0.0f, ltotal = 0.0f;
       for (uint32_t ww = 0; ww < P.n; ++ww) {
@@ -877,16 +884,16 @@ __global__ void __launch_bounds__(kPersistThreads) plan_persistent_kernel(const 
       float score = dm::add_((float)ctot, dm::mul_(P.smooth_scale, total));
       if (LIM && P.limit_weight != 0.0f) score = dm::add_(score, dm::mul_(P.limit_weight, ltotal));
       if (active)
-        atomicMin(skey, ((unsigned long long)key_hi(P.select_mode, score) << 32) | tg);
+        atomicMin(skey + (ev & 1), ((unsigned long long)key_hi(P.select_mode, score) << 32) | tg);
     }
     __syncthreads();
   };
 
   // Applies the keep-best of iteration it (merged key in *sbest) to the CTA's copy of the
-  // trajectory (generate_trajectories.cu:225-241, D5/D6 fixed).  Returns whether the trajectory
+  // trajectory (generate_trajectories.cu:225-241, D5/D6 fixed; merged key in sbest[it & 1]).  Returns whether the trajectory
   // changed (block-uniform).
   auto apply = [&](uint32_t it) -> bool {
-    const unsigned long long best = *sbest;
+    const unsigned long long best = sbest[it & 1];
     const uint32_t hi = (uint32_t)(best >> 32), win = (uint32_t)best;
     if (hi >= cur_hi) return false;
     cur_hi = hi;
@@ -920,22 +927,25 @@ __global__ void __launch_bounds__(kPersistThreads) plan_persistent_kernel(const 
   // compute warps never wait for).  If that exchange does bring an update, the pass is repeated
   // on the updated trajectory (same noise) before the key of iteration ev is taken.  The keys
   // that leave the CTA are therefore exactly those of the sequential loop.
+  // No CTA-wide barrier separates two passes: noise and CTA key are double-buffered by the
+  // iteration's parity, and the helper re-arms a key slot before the barrier that ends the
+  // next pass, i.e. before the slot's next fold.
   if (Q.iters > 0) {
     uint32_t ev = 0;
     bool pending = false; // the key of iteration ev - 1 is taken but not yet exchanged
     for (;;) {
-      evaluate(pending, ev - 1); // iteration ev
+      evaluate(ev, pending);
       if (pending) {
         pending = false;
         if (apply(ev - 1)) { // mis-speculated: discard, evaluate ev again
-          if (threadIdx.x == 0) *skey = kKeyNone;
+          if (threadIdx.x == 0) skey[ev & 1] = kKeyNone;
           __syncthreads();
           continue;
         }
       }
       if (helper && hl == 0) { // the key of iteration ev is final: take it
-        h_mine = *skey;
-        *skey = kKeyNone;
+        h_mine = skey[ev & 1];
+        skey[ev & 1] = kKeyNone;
       }
       pending = true;
       if (ev + 1 == Q.iters) {
@@ -944,8 +954,6 @@ __global__ void __launch_bounds__(kPersistThreads) plan_persistent_kernel(const 
         apply(ev);
         break;
       }
-      gen_noise(ev + 1);
-      __syncthreads();
       ++ev;
     }
   }
@@ -1844,7 +1852,7 @@ static const void *persistent_kernel_of(int gm, bool lim, bool fkm) {
 static size_t persistent_smem(const CostParams &p, int d, uint32_t T, uint32_t wpp) {
   const uint32_t SB = 256 / T, WS = T * wpp;
   size_t f = (size_t)d * p.npad + (size_t)SB * WS * (p.use_limits ? 2 : 1) + (size_t)SB * 8 + 8 +
-             ((SB + 1) & ~1u) + 4;
+             ((SB + 1) & ~1u) + 8 + (size_t)SB * 8;
   return f * sizeof(float);
 }
 
