@@ -56,20 +56,51 @@ def _stamp(target: str, sources: list[str], flags: list[str] | None = None) -> N
         f.write(_digest([s for s in sources if not s.endswith(".so")], flags or []))
 
 
+OBJ_DIR = os.path.join(LIB_DIR, "obj")
+# translation units: (source, object suffix, extra defines).  The cost / planner kernels are
+# compiled once per joint count so that the eight jobs run in parallel.
+UNITS = [
+    ("kernels_cost.cu", "_d4", ["-DDOAPP_D=4"]), ("kernels_cost.cu", "_d5", ["-DDOAPP_D=5"]),
+    ("kernels_pk.cu", "_d4", ["-DDOAPP_D=4"]), ("kernels_pk.cu", "_d5", ["-DDOAPP_D=5"]),
+    ("kernels_persist.cu", "_d4", ["-DDOAPP_D=4"]), ("kernels_persist.cu", "_d5", ["-DDOAPP_D=5"]),
+    ("kernels_aux.cu", "", []), ("doapp_capi.cu", "", []),
+]
+HEADERS = ["kernels.cuh", "device_math.cuh", "cost_device.cuh"]
+
+
 def build(force: bool = False, verbose: bool = False) -> str:
-    os.makedirs(LIB_DIR, exist_ok=True)
-    cu = [os.path.join(CSRC, f) for f in ("kernels.cu", "doapp_capi.cu")]
-    deps = cu + [os.path.join(CSRC, f) for f in ("kernels.cuh", "device_math.cuh")] + \
-        [os.path.join(ROOT, "include", "doapp", "doapp.h")]
-    if force or _stale(LIB, deps, NVCC_FLAGS):
-        cmd = [_nvcc(), *NVCC_FLAGS, "-shared", "-I", os.path.join(ROOT, "include"), "-I", CSRC,
-               *cu, "-o", LIB, "-ldl"]
+    from concurrent.futures import ThreadPoolExecutor
+    os.makedirs(OBJ_DIR, exist_ok=True)
+    hdrs = [os.path.join(CSRC, f) for f in HEADERS] + [os.path.join(ROOT, "include", "doapp", "doapp.h")]
+    nvcc = _nvcc()
+
+    def compile_unit(unit):
+        src, suffix, defs = unit
+        path = os.path.join(CSRC, src)
+        obj = os.path.join(OBJ_DIR, os.path.splitext(src)[0] + suffix + ".o")
+        flags = NVCC_FLAGS + defs
+        deps = [path] + hdrs
+        if not (force or _stale(obj, deps, flags)):
+            return obj, False
+        cmd = [nvcc, *flags, "-c", "-I", os.path.join(ROOT, "include"), "-I", CSRC, path, "-o", obj]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
-        r = subprocess.run(cmd, capture_output=not verbose, text=True)
+        r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
-            raise RuntimeError(f"nvcc failed ({r.returncode}):\n{r.stdout}\n{r.stderr}")
-        _stamp(LIB, deps, NVCC_FLAGS)
+            raise RuntimeError(f"nvcc failed ({r.returncode}) on {src}{suffix}:\n{r.stdout}\n{r.stderr}")
+        if verbose:
+            sys.stderr.write(r.stderr)
+        _stamp(obj, deps, flags)
+        return obj, True
+
+    with ThreadPoolExecutor(max_workers=min(len(UNITS), os.cpu_count() or 1)) as ex:
+        results = list(ex.map(compile_unit, UNITS))
+    objs = [o for o, _ in results]
+    if force or any(changed for _, changed in results) or not os.path.exists(LIB):
+        r = subprocess.run([nvcc, *NVCC_FLAGS, "-shared", *objs, "-o", LIB, "-ldl"],
+                           capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError(f"link failed ({r.returncode}):\n{r.stdout}\n{r.stderr}")
     host_dir = os.path.join(PKG, "host")
     host_src = os.path.join(host_dir, "planning_state.cpp")
     if os.path.exists(host_src):

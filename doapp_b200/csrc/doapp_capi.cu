@@ -2,7 +2,7 @@
 //
 // Host side of the hot path: owns every device buffer (plain cudaMalloc; the
 // reference uses cudaMallocManaged for everything, vector.cuh:142-167), stages
-// inputs, enqueues the kernels of kernels.cu on one stream per ctx — the whole
+// inputs, enqueues the kernels of kernels_*.cu on one stream per ctx — the whole
 // planner loop as a single CUDA graph — and reads results back.  There is no
 // CPU fallback: without a device doapp_create fails.
 #include "doapp/doapp.h"

@@ -11,6 +11,8 @@ namespace doapp {
 
 constexpr int kMaxJoints = 5;
 constexpr uint64_t kKeyNone = 0xFFFFFFFFFFFFFFFFull;
+// cost_kernel_pk with 2 or 4 parts per sample: 32 KB of per-waypoint sums per CTA at most
+constexpr uint32_t kPkMaxPartN = 256;
 
 enum NoiseMode : int { NOISE_ZERO = 0, NOISE_EXTERNAL = 1, NOISE_PHILOX = 2 };
 // PEND_SEED: the previous launch scored the unperturbed trajectories, its key seeds cur_hi
@@ -183,6 +185,20 @@ struct ScatterParams {
 };
 
 cudaError_t launch_cost(const CostParams &p, int d, int sm_count, cudaStream_t st);
+// The cost / planner kernels are compiled once per joint count (kernels_cost.cu, kernels_pk.cu,
+// kernels_persist.cu with -DDOAPP_D=4 and -DDOAPP_D=5); launch_cost and the persistent planner
+// (kernels_aux.cu) dispatch to these.
+#define DOAPP_DIM_CAT2(a, b) a##b
+#define DOAPP_DIM_CAT(a, b) DOAPP_DIM_CAT2(a, b)
+#define DOAPP_DIM_FN(name) DOAPP_DIM_CAT(name, DOAPP_D)
+cudaError_t launch_cost_dim4(const CostParams &p, dim3 grid, unsigned threads, size_t smem,
+                             unsigned cluster, cudaStream_t st);
+cudaError_t launch_cost_dim5(const CostParams &p, dim3 grid, unsigned threads, size_t smem,
+                             unsigned cluster, cudaStream_t st);
+cudaError_t launch_cost_pk_dim4(const CostParams &p, int gm, cudaStream_t st);
+cudaError_t launch_cost_pk_dim5(const CostParams &p, int gm, cudaStream_t st);
+const void *persistent_kernel_dim4(int gm, bool lim, bool fkm);
+const void *persistent_kernel_dim5(int gm, bool lim, bool fkm);
 cudaError_t launch_verify_div(dm::FastDiv d, uint32_t lo_bits, uint32_t hi_bits, int mode,
                               unsigned long long *bad, int sm_count, cudaStream_t st);
 // geometry + co-residency check; *ok = false when the problem does not fit one cooperative wave
