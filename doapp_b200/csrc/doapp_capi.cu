@@ -13,8 +13,11 @@
 #include <cstdlib>
 #include <cstring>
 #include <dlfcn.h>
+#include <map>
+#include <mutex>
 #include <new>
 #include <string>
+#include <tuple>
 #include <utility>
 #include <vector>
 
@@ -144,6 +147,7 @@ struct doapp_ctx {
   size_t replan_points = 0;
   const float *replan_cloud = nullptr;
   const uint8_t *replan_cells = nullptr;
+  uint64_t replan_grid_generation = ~0ull;
   uint64_t replan_kernels = 0;
   int replan_end[3] = {0, 0, -1};
 
@@ -227,11 +231,25 @@ uint32_t f2u(float f) {
 
 // Runs the exhaustive device check of dm::div_fast_unguarded against __fdiv_rn for divisor b
 // over the floats with bit patterns [lo_bits, hi_bits]; *ok = no mismatch.
+// The verdict depends only on (divisor, range, mode) -- the arithmetic is the same on every
+// sm_100a device -- so it is cached per process: a caller that re-allocates its grid every
+// frame pays the ~1 ms check once per resolution.
 doapp_status verify_fast_div(doapp_ctx *ctx, float b, uint32_t lo_bits, uint32_t hi_bits, int mode,
                              bool *ok) {
   *ok = false;
   volatile float rcp = 1.0f / b;
   if (!ctx->fast_math_ok || !(b > 0x1p-60f && b < 0x1p+60f)) return DOAPP_OK;
+  static std::mutex mu;
+  static std::map<std::tuple<uint32_t, uint32_t, uint32_t, int>, bool> verdicts;
+  const auto key = std::make_tuple(f2u(b), lo_bits, hi_bits, mode);
+  {
+    std::lock_guard<std::mutex> lk(mu);
+    auto it = verdicts.find(key);
+    if (it != verdicts.end()) {
+      *ok = it->second;
+      return DOAPP_OK;
+    }
+  }
   ST(ensure(ctx, ctx->vbad, 1));
   CU(cudaMemsetAsync(ctx->vbad.p, 0, sizeof(unsigned long long), ctx->stream));
   dm::FastDiv d{b, rcp, 0.0f, 0.0f};
@@ -241,6 +259,10 @@ doapp_status verify_fast_div(doapp_ctx *ctx, float b, uint32_t lo_bits, uint32_t
   CU(cudaMemcpyAsync(&bad, ctx->vbad.p, sizeof(bad), cudaMemcpyDeviceToHost, ctx->stream));
   CU(cudaStreamSynchronize(ctx->stream));
   *ok = bad == 0;
+  {
+    std::lock_guard<std::mutex> lk(mu);
+    verdicts[key] = *ok;
+  }
   return DOAPP_OK;
 }
 
@@ -369,6 +391,16 @@ doapp_status persistent_eligible(doapp_ctx *ctx, PersistParams *q, bool *ok) {
   // several ranks: only with the peer mailboxes mapped (doapp_peer_import), else NCCL per iteration
   if (ctx->comm && !(ctx->peer_ready && ctx->peer_nranks == ctx->nranks)) return DOAPP_OK;
   CostParams p = base_cost_params(ctx);
+  // With several ranks the verdict must be the same everywhere (a rank in the persistent kernel
+  // would wait for keys a rank on the NCCL path never sends): decide it from the largest shard,
+  // which every rank can compute, then fill the geometry for this rank's own shard.
+  if (ctx->comm && ctx->nranks > 1) {
+    CostParams pm = p;
+    pm.m = (uint32_t)((ctx->m_global + ctx->nranks - 1) / ctx->nranks);
+    PersistParams qm{};
+    CU(persistent_plan_config(pm, c.waypoint_dim, ctx->sm_count, &qm, ok));
+    if (!*ok) return DOAPP_OK;
+  }
   CU(persistent_plan_config(p, c.waypoint_dim, ctx->sm_count, q, ok));
   return DOAPP_OK;
 }
@@ -874,6 +906,7 @@ doapp_status doapp_grid_alloc(doapp_ctx *ctx, int32_t kind, int32_t frame, uint3
   ctx->grid = g;
   ctx->grid_bytes = bytes;
   ctx->grid_generation++;
+  invalidate_graph(ctx); // captured graphs carry the old GridDev and clear size by value
   return DOAPP_OK;
 }
 
@@ -1472,6 +1505,14 @@ doapp_status doapp_replan_dynamic(doapp_ctx *ctx, const float *start, const floa
       p.iteration = it;
       ST(launch_pass(ctx, p, PEND_SEED, 0, NOISE_PHILOX, nullptr, true));
       nk += 2;
+      if (ctx->comm) { // sharded samples: every rank needs the global winner
+        NcclApi *nccl = nccl_api(nullptr);
+        unsigned long long *kb = ctx->keys.p + (size_t)ctx->key_w * k;
+        ncclResult_t r = nccl->AllReduce(kb, kb, k, ncclUint64, ncclMin, ctx->comm, ctx->stream);
+        if (r != ncclSuccess)
+          return fail(ctx, DOAPP_NCCL_ERROR, "ncclAllReduce: %s",
+                      nccl->GetErrorString ? nccl->GetErrorString(r) : "error");
+      }
     }
     CostParams p = climber_cost_params(ctx);
     p.scores = ctx->final_scores.p;
@@ -1503,7 +1544,8 @@ doapp_status doapp_replan_dynamic(doapp_ctx *ctx, const float *start, const floa
   } else {
     const bool hit = ctx->replan_exec && ctx->replan_iters == iters &&
                      ctx->replan_points == num_points && ctx->replan_cloud == ctx->cloud.p &&
-                     ctx->replan_cells == ctx->grid_cells.p;
+                     ctx->replan_cells == ctx->grid_cells.p &&
+                     ctx->replan_grid_generation == ctx->grid_generation;
     if (!hit) {
       if (ctx->replan_exec) cudaGraphExecDestroy(ctx->replan_exec);
       ctx->replan_exec = nullptr;
@@ -1526,6 +1568,7 @@ doapp_status doapp_replan_dynamic(doapp_ctx *ctx, const float *start, const floa
       ctx->replan_points = num_points;
       ctx->replan_cloud = ctx->cloud.p;
       ctx->replan_cells = ctx->grid_cells.p;
+      ctx->replan_grid_generation = ctx->grid_generation;
       ctx->replan_kernels = nk;
       ctx->replan_end[0] = ctx->traj_s;
       ctx->replan_end[1] = ctx->cur_s;

@@ -471,7 +471,8 @@ float orc_cost_sample(const orc_params *p, const orc_grid *g, const float *base,
                       int32_t *violated_out) {
   const uint32_t n = p->n, d = p->d;
   float xprev[8], vprev[8], x[8], v[8];
-  float *acc2 = (float *)malloc(sizeof(float) * n * 2);
+  float stack_sums[2 * 256]; /* per-waypoint sums: no heap traffic for the BASELINE shapes */
+  float *acc2 = n <= 256 ? stack_sums : (float *)malloc(sizeof(float) * n * 2);
   float *lim2 = acc2 + n;
   int32_t coll = 0, violated = 0;
   float seq_sum = 0.0f, seq_lim = 0.0f; /* element-by-element order of gt.test.cu:187-195 */
@@ -533,7 +534,7 @@ float orc_cost_sample(const orc_params *p, const orc_grid *g, const float *base,
     float lc = p->limit_weight * lsum;
     score = score + lc;
   }
-  free(acc2);
+  if (acc2 != stack_sums) free(acc2);
   if (collisions) *collisions = coll;
   if (smooth_out) *smooth_out = smooth;
   if (violated_out) *violated_out = violated;
@@ -561,7 +562,8 @@ static void *orc_eval_range(void *arg) {
   orc_job *jb = (orc_job *)arg;
   const orc_params *p = jb->p;
   size_t nd = (size_t)p->n_noise * p->d;
-  float *tmp = (float *)malloc(sizeof(float) * nd);
+  float tmp_small[8];
+  float *tmp = nd <= 8 ? tmp_small : (float *)malloc(sizeof(float) * nd);
   for (size_t s = jb->s0; s < jb->s1; ++s) {
     uint32_t c = (uint32_t)(s / p->m);
     uint32_t t = (uint32_t)(s % p->m);
@@ -581,7 +583,37 @@ static void *orc_eval_range(void *arg) {
     jb->scores[s] = sc;
     if (jb->collisions) jb->collisions[s] = coll;
   }
-  free(tmp);
+  if (tmp != tmp_small) free(tmp);
+  return NULL;
+}
+
+/* Persistent worker pool: the threads are created once and reused by every evaluation (the
+ * reference spawns its fill threads per call, cdg.cu:88-110, but it fills once per grid; the
+ * planner loop evaluates once per ITERATION, so per-call pthread_create would dominate small
+ * problems).  One evaluation at a time (mu_call); workers sleep on a condition variable. */
+#define ORC_POOL_MAX 256
+static struct {
+  pthread_mutex_t mu, mu_call;
+  pthread_cond_t cv_work, cv_done;
+  pthread_t th[ORC_POOL_MAX];
+  int nthreads;        /* workers alive */
+  uint64_t generation; /* bumped per evaluation */
+  orc_job *jobs;
+  int njobs, next_job, pending;
+} orc_pool = {PTHREAD_MUTEX_INITIALIZER, PTHREAD_MUTEX_INITIALIZER, PTHREAD_COND_INITIALIZER,
+              PTHREAD_COND_INITIALIZER, {0}, 0, 0, NULL, 0, 0, 0};
+
+static void *orc_pool_worker(void *arg) {
+  (void)arg;
+  pthread_mutex_lock(&orc_pool.mu);
+  for (;;) {
+    while (orc_pool.next_job >= orc_pool.njobs) pthread_cond_wait(&orc_pool.cv_work, &orc_pool.mu);
+    orc_job *jb = &orc_pool.jobs[orc_pool.next_job++];
+    pthread_mutex_unlock(&orc_pool.mu);
+    orc_eval_range(jb);
+    pthread_mutex_lock(&orc_pool.mu);
+    if (--orc_pool.pending == 0) pthread_cond_signal(&orc_pool.cv_done);
+  }
   return NULL;
 }
 
@@ -591,9 +623,9 @@ static void orc_eval_all(const orc_params *p, const orc_grid *g, const float *ba
                          int32_t *collisions, int num_threads) {
   size_t S = (size_t)p->k * p->m;
   if (num_threads < 1) num_threads = 1;
+  if (num_threads > ORC_POOL_MAX) num_threads = ORC_POOL_MAX;
   if ((size_t)num_threads > S) num_threads = (int)(S ? S : 1);
-  orc_job *jobs = (orc_job *)calloc((size_t)num_threads, sizeof(orc_job));
-  pthread_t *th = (pthread_t *)calloc((size_t)num_threads, sizeof(pthread_t));
+  orc_job jobs[ORC_POOL_MAX];
   size_t per = (S + (size_t)num_threads - 1) / (size_t)num_threads;
   for (int i = 0; i < num_threads; ++i) {
     orc_job jb = {p, g, base_traj, start, noise, iteration, scores, collisions,
@@ -601,15 +633,41 @@ static void orc_eval_all(const orc_params *p, const orc_grid *g, const float *ba
     jb.s0 = per * (size_t)i < S ? per * (size_t)i : S;
     jb.s1 = per * (size_t)(i + 1) < S ? per * (size_t)(i + 1) : S;
     jobs[i] = jb;
-    if (num_threads == 1)
-      orc_eval_range(&jobs[i]);
-    else
-      pthread_create(&th[i], NULL, orc_eval_range, &jobs[i]);
   }
-  if (num_threads > 1)
-    for (int i = 0; i < num_threads; ++i) pthread_join(th[i], NULL);
-  free(jobs);
-  free(th);
+  if (num_threads == 1) {
+    orc_eval_range(&jobs[0]);
+    return;
+  }
+  /* the calling thread takes job 0, the pool the rest */
+  pthread_mutex_lock(&orc_pool.mu_call);
+  pthread_mutex_lock(&orc_pool.mu);
+  while (orc_pool.nthreads < num_threads - 1) {
+    if (pthread_create(&orc_pool.th[orc_pool.nthreads], NULL, orc_pool_worker, NULL) != 0) break;
+    pthread_detach(orc_pool.th[orc_pool.nthreads]);
+    orc_pool.nthreads++;
+  }
+  const int have_pool = orc_pool.nthreads > 0;
+  if (have_pool) {
+    orc_pool.jobs = jobs;
+    orc_pool.next_job = 1;
+    orc_pool.pending = num_threads - 1;
+    orc_pool.njobs = num_threads;
+    orc_pool.generation++;
+    pthread_cond_broadcast(&orc_pool.cv_work);
+  }
+  pthread_mutex_unlock(&orc_pool.mu);
+  orc_eval_range(&jobs[0]);
+  if (have_pool) {
+    pthread_mutex_lock(&orc_pool.mu);
+    while (orc_pool.pending > 0) pthread_cond_wait(&orc_pool.cv_done, &orc_pool.mu);
+    orc_pool.njobs = 0;
+    orc_pool.next_job = 0;
+    orc_pool.jobs = NULL;
+    pthread_mutex_unlock(&orc_pool.mu);
+  } else {
+    for (int i = 1; i < num_threads; ++i) orc_eval_range(&jobs[i]);
+  }
+  pthread_mutex_unlock(&orc_pool.mu_call);
 }
 
 int64_t orc_cost_eval(const orc_params *p, const orc_grid *g, const float *base_traj,
