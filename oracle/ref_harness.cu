@@ -20,6 +20,7 @@
 
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <random>
@@ -184,7 +185,62 @@ static bool part_kernel() {
   return true;
 }
 
+// --time N: the reference kernel at the shape the shipped node launches (main.cu:20-21,
+// planning_state.cu:61-62,79-84: k = 1000 blocks x n*m*d = 1000 threads), one optimiser iteration
+// per launch (stop flag preset), N launches timed with CUDA events after 3 warm-ups.  The
+// kernel's own device printf (gt.cu:194,237,255) is part of what is timed: it is the reference
+// as shipped.  One JSON line on stdout (after the kernel's prints).
+static int part_time(int reps) {
+  const unsigned k = 1000, n = 50, d = doapp::num_joints, m = 1024 / n / d; // main.cu:20-21
+  const float dt = 0.1f;
+  const unsigned per_traj = d * (n > m ? n : m), num_rngs = k * per_traj;
+  doapp::CPUDistanceGrid *g = make_grid(100, 100, 100, 0.01);
+  if (!g) return 3;
+  float *traj = managed<float>(k * n * d), *noise = managed<float>(k * m * d);
+  float *noisy = managed<float>(k * m * n * d), *vel = managed<float>(k * m * n * d);
+  float *acc = managed<float>(k * m * n * d), *smooth = managed<float>(k * m);
+  float *scores = managed<float>(k * (m + 1)), *upd = managed<float>(k * d);
+  bool *found = managed<bool>(k), *flag = managed<bool>(1);
+  curandState *rngs = managed<curandState>(num_rngs);
+  if (!traj || !rngs || !flag) return 3;
+  init_cudarand<<<(num_rngs + 511) / 512, 512>>>(rngs, num_rngs);
+  if (cudaDeviceSynchronize() != cudaSuccess) return 3;
+  const float start[4] = {0.0f, 0.0f, 0.0f, 0.0f}, goal[4] = {0.0f, -1.0f, 1.5f, -1.5f};
+  std::vector<float> lerp(n * d);
+  for (unsigned w = 0; w < n; ++w)
+    for (unsigned j = 0; j < d; ++j)
+      lerp[w * d + j] = start[j] + float(w + 1) * ((goal[j] - start[j]) / float(n));
+  cudaMemcpyToSymbol(initial_waypoint, start, sizeof start);
+  cudaMemcpyToSymbol(final_waypoint, goal, sizeof goal);
+  cudaMemcpyToSymbol(initial_trajectory, lerp.data(), lerp.size() * sizeof(float));
+  flag[0] = true;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0);
+  cudaEventCreate(&e1);
+  float ms = 0.0f;
+  for (int r = -3; r < reps; ++r) {
+    if (r == 0) cudaEventRecord(e0);
+    optimize_trajectories<<<k, n * m * d>>>(traj, noise, noisy, rngs, vel, acc, smooth, scores, upd,
+                                            found, flag, per_traj, n, d, m, dt, *g);
+  }
+  cudaEventRecord(e1);
+  if (cudaDeviceSynchronize() != cudaSuccess) {
+    fprintf(stderr, "optimize_trajectories: %s\n", cudaGetErrorString(cudaGetLastError()));
+    return 3;
+  }
+  cudaEventElapsedTime(&ms, e0, e1);
+  const double wps = double(k) * m * n, us = 1e3 * ms / reps;
+  fflush(stdout);
+  printf("{\"kernel\": \"optimize_trajectories (reference, as shipped: collision term stubbed)\", "
+         "\"shape_kmnd\": [%u, %u, %u, %u], \"launches\": %d, \"us_per_iteration\": %.3f, "
+         "\"waypoint_samples_per_iteration\": %.0f, \"value\": %.6g, "
+         "\"unit\": \"waypoint-samples/s\"}\n",
+         k, m, n, d, reps, us, wps, wps / (us * 1e-6));
+  return 0;
+}
+
 int main(int argc, char **argv) {
+  if (argc > 2 && !strcmp(argv[1], "--time")) return part_time(atoi(argv[2]) > 0 ? atoi(argv[2]) : 20);
   out = argc > 1 ? fopen(argv[1], "w") : stdout;
   if (!out) return 2;
   fputc('{', out);
