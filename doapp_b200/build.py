@@ -63,6 +63,7 @@ UNITS = [
     ("kernels_cost.cu", "_d4", ["-DDOAPP_D=4"]), ("kernels_cost.cu", "_d5", ["-DDOAPP_D=5"]),
     ("kernels_pk.cu", "_d4", ["-DDOAPP_D=4"]), ("kernels_pk.cu", "_d5", ["-DDOAPP_D=5"]),
     ("kernels_persist.cu", "_d4", ["-DDOAPP_D=4"]), ("kernels_persist.cu", "_d5", ["-DDOAPP_D=5"]),
+    ("kernels_persist2.cu", "_d4", ["-DDOAPP_D=4"]), ("kernels_persist2.cu", "_d5", ["-DDOAPP_D=5"]),
     ("kernels_aux.cu", "", []), ("doapp_capi.cu", "", []),
 ]
 HEADERS = ["kernels.cuh", "device_math.cuh", "cost_device.cuh"]

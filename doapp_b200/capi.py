@@ -33,7 +33,7 @@ ABI_SYMBOLS = [
     "doapp_cost_eval_dev", "doapp_read_results", "doapp_plan_lerp", "doapp_plan",
     "doapp_plan_async", "doapp_plan_wait", "doapp_plan_state", "doapp_replan_dynamic",
     "doapp_plan_bench", "doapp_plan_profile", "doapp_probe_gather", "doapp_peer_export", "doapp_peer_import", "doapp_comm_unique_id", "doapp_comm_init", "doapp_grid_broadcast",
-    "doapp_plan_mode", "doapp_launch_count", "doapp_debug_sincos", "doapp_debug_fk",
+    "doapp_plan_mode", "doapp_plan_stats", "doapp_launch_count", "doapp_debug_sincos", "doapp_debug_fk",
     "doapp_debug_fk_model",
 ]
 
@@ -134,6 +134,7 @@ def load_library(path: str | None = None) -> C.CDLL:
     L.doapp_grid_broadcast.argtypes = [vp, C.c_int32]
     L.doapp_plan_mode.argtypes = [vp]
     L.doapp_plan_mode.restype = C.c_uint32
+    L.doapp_plan_stats.argtypes = [vp, vp, vp]
     L.doapp_launch_count.argtypes = [vp]
     L.doapp_launch_count.restype = C.c_uint64
     L.doapp_debug_sincos.argtypes = [vp, f32p, C.c_size_t, f32p, f32p]
@@ -407,6 +408,11 @@ class Context:
     def plan_mode(self) -> int:
         """bit 0: persistent one-launch planner; bit 1: in-kernel peer-mailbox argmin merge."""
         return int(self.L.doapp_plan_mode(self.h))
+
+    def plan_stats(self) -> dict:
+        acc, passes = C.c_uint64(), C.c_uint64()
+        self._ck(self.L.doapp_plan_stats(self.h, C.addressof(acc), C.addressof(passes)))
+        return dict(accepted_updates=acc.value, cost_passes=passes.value)
 
     def launch_count(self) -> int:
         return int(self.L.doapp_launch_count(self.h))

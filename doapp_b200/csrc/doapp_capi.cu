@@ -93,6 +93,11 @@ struct doapp_ctx {
   DevBuf<uint32_t> cur_hi;
   DevBuf<unsigned long long> pkeys; // persistent planner: 3 x [k] rotating barrier words {key, arrivals - 1}
   int persist_mode = -1;            // DOAPP_PERSIST=0/1: never / whenever legal
+  int persist_version = 2;          // DOAPP_PERSIST_V=1: first-generation kernel (plan_persistent_kernel)
+  int persist_depth = 0;            // DOAPP_PERSIST_DEPTH=1..7 (0: 3 on one rank, 5 on several)
+  DevBuf<unsigned long long> p2_entries, p2_stats; // plan_pipeline_kernel: tagged CTA keys, counters
+  DevBuf<unsigned int> p2_error;    // set by the kernel when the key exchange timed out
+  bool p2_ran = false;              // the last plan ran plan_pipeline_kernel
   // peer-memory argmin merge: own mailbox [2 epochs][3][k][8] + result [3][k], the ranks' mailboxes
   DevBuf<unsigned long long> mailbox, presult;
   unsigned long long *peer_mbox[8] = {};
@@ -405,6 +410,103 @@ doapp_status persistent_eligible(doapp_ctx *ctx, PersistParams *q, bool *ok) {
   return DOAPP_OK;
 }
 
+// Second-generation persistent planner (plan_pipeline_kernel); same rules, same rank-uniform
+// verdict.  Preferred over the first generation whenever it is eligible.
+doapp_status pipeline_eligible(doapp_ctx *ctx, Persist2Params *q, bool *ok) {
+  *ok = false;
+  const doapp_config &c = ctx->cfg;
+  if (ctx->persist_mode == 0 || ctx->persist_version != 2 ||
+      c.update_mode != DOAPP_UPDATE_KEEP_BEST || c.noise_waypoints != 1)
+    return DOAPP_OK;
+  if (ctx->comm && !(ctx->peer_ready && ctx->peer_nranks == ctx->nranks)) return DOAPP_OK;
+  CostParams p = base_cost_params(ctx);
+  if (ctx->comm && ctx->nranks > 1) {
+    CostParams pm = p;
+    pm.m = (uint32_t)((ctx->m_global + ctx->nranks - 1) / ctx->nranks);
+    pm.sample_offset = ctx->m_global - pm.m; // the last shard: largest offset
+    Persist2Params qm{};
+    CU(pipeline_plan_config(pm, c.waypoint_dim, ctx->sm_count, &qm, ok));
+    if (!*ok) return DOAPP_OK;
+  }
+  CU(pipeline_plan_config(p, c.waypoint_dim, ctx->sm_count, q, ok));
+  return DOAPP_OK;
+}
+
+doapp_status enqueue_final(doapp_ctx *ctx) {
+  const doapp_config &c = ctx->cfg;
+  CostParams f0 = climber_cost_params(ctx);
+  f0.scores = ctx->final_scores.p;
+  f0.collisions = ctx->final_coll.p;
+  ST(launch_pass(ctx, f0, PEND_NONE, 0, NOISE_ZERO, nullptr, false));
+  FinalParams f{};
+  f.traj = traj_half_ptr(ctx, ctx->traj_s);
+  f.start = ctx->start.p;
+  f.scores = ctx->final_scores.p;
+  f.found_better = ctx->found.p;
+  f.k = c.num_climbers;
+  f.n = c.num_waypoints;
+  f.npad = ctx->npad;
+  f.d = c.waypoint_dim;
+  f.dt = c.delta_t;
+  f.out = ctx->out.p;
+  CU(launch_final(f, ctx->stream));
+  return DOAPP_OK;
+}
+
+doapp_status enqueue_plan_pipeline(doapp_ctx *ctx, Persist2Params q, uint32_t iters, int noise_mode,
+                                   uint64_t *kernels) {
+  const doapp_config &c = ctx->cfg;
+  const size_t k = c.num_climbers;
+  reset_plan_state(ctx);
+  CU(cudaMemsetAsync(ctx->keys.p, 0xFF, sizeof(unsigned long long) * 3 * k, ctx->stream));
+  // seed pass: score the k unperturbed trajectories (gt.cu:180-191); its keys seed cur_hi
+  ST(launch_pass(ctx, climber_cost_params(ctx), PEND_NONE, 0, NOISE_ZERO, nullptr, true));
+  const size_t nent = (size_t)kP2Ring * k * pipeline_grid_x(q);
+  ST(ensure(ctx, ctx->p2_entries, nent));
+  CU(cudaMemsetAsync(ctx->p2_entries.p, 0xFF, sizeof(unsigned long long) * nent, ctx->stream));
+  CostParams &p = q.cost;
+  p.traj = traj_half_ptr(ctx, ctx->traj_s);
+  p.traj_next = traj_half_ptr(ctx, 1 - ctx->traj_s);
+  p.pend_keys = ctx->keys.p + (size_t)ctx->key_w * k;
+  p.cur_hi_out = ctx->cur_hi.p + (size_t)(1 - ctx->cur_s) * k;
+  p.found_better = ctx->found.p;
+  p.noise_mode = noise_mode;
+  p.noise_m = ctx->m_global;
+  p.noise_t0 = 0;
+  q.iters = iters;
+  q.entries = ctx->p2_entries.p;
+  q.noise_base = noise_mode == NOISE_EXTERNAL ? ctx->noise.p : nullptr;
+  q.noise_iter_stride = (uint64_t)c.num_climbers * ctx->m_global * c.waypoint_dim;
+  q.nranks = 1;
+  q.rank = 0;
+  q.error = ctx->p2_error.p;
+  q.stats = ctx->p2_stats.p;
+  q.timeout_ns = 20ull * 1000000000ull; // a peer that never arrives: leave after 20 s
+  ctx->last_plan_mode = 1;
+  const bool multi = ctx->comm && ctx->peer_ready;
+  if (multi) {
+    ctx->last_plan_mode = 3;
+    const size_t set = (size_t)kP2Ring * k * 8;
+    q.nranks = (uint32_t)ctx->peer_nranks;
+    q.rank = (uint32_t)ctx->peer_rank;
+    for (int r = 0; r < ctx->peer_nranks; ++r) q.mailbox[r] = ctx->peer_mbox[r] + (ctx->peer_epoch & 1) * set;
+    q.mailbox_next = ctx->mailbox.p + ((ctx->peer_epoch + 1) & 1) * set;
+    ctx->peer_epoch++;
+  }
+  q.depth = ctx->persist_depth ? (uint32_t)ctx->persist_depth : (multi ? 5u : 3u);
+  if (q.depth > (uint32_t)kP2MaxDepth) q.depth = kP2MaxDepth;
+  if (ctx->profiling) CU(cudaEventRecord(ctx->prof_events[0], ctx->stream));
+  CU(launch_pipeline_plan(q, c.waypoint_dim, ctx->sm_count, ctx->stream));
+  if (ctx->profiling) CU(cudaEventRecord(ctx->prof_events[1], ctx->stream));
+  ctx->prof_launches = 1;
+  ctx->p2_ran = true;
+  ctx->traj_s ^= 1;
+  ctx->cur_s ^= 1;
+  ST(enqueue_final(ctx));
+  if (kernels) *kernels = 4;
+  return DOAPP_OK;
+}
+
 doapp_status enqueue_plan_persistent(doapp_ctx *ctx, PersistParams q, uint32_t iters, int noise_mode,
                                      uint64_t *kernels) {
   const doapp_config &c = ctx->cfg;
@@ -483,7 +585,12 @@ doapp_status enqueue_plan(doapp_ctx *ctx, uint32_t iters, int noise_mode, uint64
   const size_t k = c.num_climbers;
   uint64_t nk = 0;
   NcclApi *nccl = ctx->comm ? nccl_api(nullptr) : nullptr;
+  ctx->p2_ran = false;
   {
+    Persist2Params q2{};
+    bool pipeline = false;
+    ST(pipeline_eligible(ctx, &q2, &pipeline));
+    if (pipeline) return enqueue_plan_pipeline(ctx, q2, iters, noise_mode, kernels);
     PersistParams q{};
     bool persistent = false;
     ST(persistent_eligible(ctx, &q, &persistent));
@@ -605,6 +712,10 @@ doapp_status run_plan(doapp_ctx *ctx, uint32_t iters, int noise_mode) {
   PersistParams pq{};
   bool persistent = false;
   ST(persistent_eligible(ctx, &pq, &persistent));
+  if (!persistent) {
+    Persist2Params pq2{};
+    ST(pipeline_eligible(ctx, &pq2, &persistent));
+  }
   // the persistent path is four launches in all: nothing for a graph to amortise
   if (!ctx->use_graph || ctx->profiling || persistent) {
     uint64_t nk = 0;
@@ -749,6 +860,10 @@ doapp_status doapp_create(const doapp_config *cfg, doapp_ctx **out) {
   ctx->use_graph = !(ng && ng[0] == '1');
   const char *psv = getenv("DOAPP_PERSIST");
   ctx->persist_mode = (psv && (psv[0] == '0' || psv[0] == '1')) ? psv[0] - '0' : -1;
+  const char *pvv = getenv("DOAPP_PERSIST_V");
+  ctx->persist_version = (pvv && pvv[0] == '1') ? 1 : 2;
+  const char *pdv = getenv("DOAPP_PERSIST_DEPTH");
+  ctx->persist_depth = (pdv && pdv[0] >= '1' && pdv[0] <= '7') ? pdv[0] - '0' : 0;
   const char *pkv = getenv("DOAPP_PK");
   ctx->pk_mode = (pkv && (pkv[0] == '0' || pkv[0] == '1')) ? pkv[0] - '0' : -1;
   const char *xd = getenv("DOAPP_EXACT_DIV");
@@ -776,6 +891,10 @@ doapp_status doapp_create(const doapp_config *cfg, doapp_ctx **out) {
     ST(ensure(ctx, ctx->usum, 2 * k * 8));
     ST(ensure(ctx, ctx->found, k));
     ST(ensure(ctx, ctx->out, 4 + 2 * n * d));
+    ST(ensure(ctx, ctx->p2_error, 1));
+    ST(ensure(ctx, ctx->p2_stats, 2));
+    CU(cudaMemsetAsync(ctx->p2_error.p, 0, sizeof(unsigned int), ctx->stream));
+    CU(cudaMemsetAsync(ctx->p2_stats.p, 0, 2 * sizeof(unsigned long long), ctx->stream));
     CU(cudaMemsetAsync(ctx->traj.p, 0, sizeof(float) * 2 * ctx->traj_half, ctx->stream));
     CU(cudaMemsetAsync(ctx->start.p, 0, sizeof(float) * 8, ctx->stream));
     CU(cudaMemsetAsync(ctx->found.p, 0, k, ctx->stream));
@@ -816,6 +935,7 @@ void doapp_destroy(doapp_ctx *ctx) {
   release(ctx->keys_float); release(ctx->cur_hi); release(ctx->found); release(ctx->grid_cells);
   release(ctx->lookup_coll); release(ctx->lookup_idx); release(ctx->dbg_a); release(ctx->dbg_b);
   release(ctx->dbg_c); release(ctx->vbad); release(ctx->usum); release(ctx->pkeys);
+  release(ctx->p2_entries); release(ctx->p2_stats); release(ctx->p2_error);
   for (int r = 0; r < 8; ++r)
     if (ctx->peer_ready && r != ctx->peer_rank && ctx->peer_mbox[r]) cudaIpcCloseMemHandle(ctx->peer_mbox[r]);
   release(ctx->mailbox); release(ctx->presult); release(ctx->depth); release(ctx->fk_dev);
@@ -1376,8 +1496,16 @@ doapp_status doapp_plan_wait(doapp_ctx *ctx, float *best_traj, float *best_vel, 
   const size_t nd = (size_t)ctx->cfg.num_waypoints * ctx->cfg.waypoint_dim;
   CU(cudaMemcpyAsync(ctx->h_out.data(), ctx->out.p, (4 + 2 * nd) * sizeof(float),
                      cudaMemcpyDeviceToHost, ctx->stream));
+  unsigned int p2_err = 0;
+  if (ctx->p2_ran)
+    CU(cudaMemcpyAsync(&p2_err, ctx->p2_error.p, sizeof(p2_err), cudaMemcpyDeviceToHost, ctx->stream));
   CU(cudaStreamSynchronize(ctx->stream));
   ctx->plan_pending = false;
+  if (p2_err) {
+    CU(cudaMemsetAsync(ctx->p2_error.p, 0, sizeof(unsigned int), ctx->stream));
+    return fail(ctx, DOAPP_CUDA_ERROR,
+                "persistent planner: the argmin key exchange timed out (a rank did not arrive)");
+  }
   if (best_score) *best_score = ctx->h_out[0];
   if (best_climber) memcpy(best_climber, &ctx->h_out[2], 8);
   if (best_traj) memcpy(best_traj, &ctx->h_out[4], nd * sizeof(float));
@@ -1663,7 +1791,9 @@ doapp_status doapp_peer_export(doapp_ctx *ctx, uint8_t handle[DOAPP_PEER_HANDLE_
   if (!handle) return fail(ctx, DOAPP_INVALID_ARG, "doapp_peer_export: null handle");
   static_assert(sizeof(cudaIpcMemHandle_t) <= DOAPP_PEER_HANDLE_BYTES, "IPC handle size");
   CU(cudaSetDevice(ctx->cfg.device));
-  const size_t k = ctx->cfg.num_climbers, elems = 2 * 3 * k * 8;
+  // two alternating sets of [ring][k][8 ranks] words (kP2Ring covers the first-generation
+  // kernel's three-way rotation as well)
+  const size_t k = ctx->cfg.num_climbers, elems = 2 * (size_t)kP2Ring * k * 8;
   ST(ensure(ctx, ctx->mailbox, elems));
   ST(ensure(ctx, ctx->presult, 3 * k));
   CU(cudaMemsetAsync(ctx->mailbox.p, 0xFF, elems * sizeof(unsigned long long), ctx->stream));
@@ -1760,6 +1890,17 @@ doapp_status doapp_grid_broadcast(doapp_ctx *ctx, int32_t root) {
 // --------------------------------------------------------------- introspection
 
 uint64_t doapp_launch_count(const doapp_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+doapp_status doapp_plan_stats(doapp_ctx *ctx, uint64_t *accepted_updates, uint64_t *cost_passes) {
+  if (!ctx) return DOAPP_INVALID_ARG;
+  CU(cudaSetDevice(ctx->cfg.device));
+  unsigned long long h[2] = {0, 0};
+  CU(cudaStreamSynchronize(ctx->stream));
+  if (ctx->p2_ran) CU(cudaMemcpy(h, ctx->p2_stats.p, sizeof(h), cudaMemcpyDeviceToHost));
+  if (accepted_updates) *accepted_updates = h[0];
+  if (cost_passes) *cost_passes = h[1];
+  return DOAPP_OK;
+}
 uint32_t doapp_plan_mode(const doapp_ctx *ctx) { return ctx ? ctx->last_plan_mode : 0; }
 
 doapp_status doapp_debug_sincos(doapp_ctx *ctx, const float *angles, size_t count, float *sin_out,

@@ -135,6 +135,39 @@ struct PersistParams {
   unsigned long long *result;
 };
 
+// Second-generation persistent planner (plan_pipeline_kernel, kernels_persist2.cu): one CTA per
+// SM, warp-specialised (compute / fold / collect / noise), speculation `depth` iterations deep,
+// tagged 8-byte key words instead of barriers.
+constexpr int kP2Ring = 16;        // iterations in the global entry / mailbox rings (>= 2 * depth + 1)
+constexpr int kP2Q = 8;            // iterations in the shared-memory rings (>= depth + 1)
+constexpr int kP2MaxDepth = 7;
+constexpr int kP2HelperWarps = 3;  // fold, collect, noise
+constexpr int kP2MaxComputeWarps = 16;
+constexpr int kP2MaxThreads = 32 * (kP2MaxComputeWarps + kP2HelperWarps);
+struct Persist2Params {
+  CostParams cost;             // traj = input, traj_next = output, pend_keys = the seed pass's keys
+  uint32_t iters;
+  uint32_t t_log2;             // lanes per sample = 2^t_log2 (<= 32)
+  uint32_t ppt;                // waypoint pairs per lane
+  uint32_t sb;                 // samples per CTA
+  uint32_t depth;              // iterations costed ahead of the last decided one
+  unsigned long long *entries; // [kP2Ring][k][gridDim.x] tagged CTA keys (any content at launch
+                               // except a valid tag of the first ring turn: memset 0xFF)
+  const float *noise_base;     // external noise of iteration 0 (or nullptr: Philox)
+  uint64_t noise_iter_stride;
+  uint32_t nranks, rank;
+  unsigned long long *mailbox[8];   // rank r's mailbox [kP2Ring][k][8] (own one included)
+  unsigned long long *mailbox_next; // own mailbox set of the NEXT launch, re-armed at kernel start
+  unsigned int *error;              // device word: set when the key exchange timed out
+  unsigned long long *stats;        // [2] accepted updates, cost passes of CTA 0 (or nullptr)
+  unsigned long long timeout_ns;
+};
+cudaError_t pipeline_plan_config(const CostParams &p, int d, int sm_count, Persist2Params *q, bool *ok);
+cudaError_t launch_pipeline_plan(const Persist2Params &q, int d, int sm_count, cudaStream_t st);
+uint32_t pipeline_grid_x(const Persist2Params &q);
+const void *pipeline_kernel_dim4(int gm, bool lim, bool fkm);
+const void *pipeline_kernel_dim5(int gm, bool lim, bool fkm);
+
 struct FinalParams {
   const float *traj; // [k][d][npad]
   const float *start;

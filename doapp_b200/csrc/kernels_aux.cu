@@ -530,6 +530,72 @@ cudaError_t launch_cost(const CostParams &p_in, int d, int sm_count, cudaStream_
                 : launch_cost_dim4(p, grid, threads, smem, cs, st);
 }
 
+// ---- second-generation persistent planner: geometry, co-residency check, cooperative launch
+static size_t pipeline_smem(const CostParams &p, int d, uint32_t sb, uint32_t cw) {
+  const uint32_t NP = p.npad + 2, NPS = p.n | 1u;
+  size_t words = (size_t)2 * d * NP + (size_t)kP2Q * sb * NPS * (p.use_limits ? 2 : 1) +
+                 (size_t)kP2Q * sb * 8 + 8 + (size_t)kP2Q * sb + (size_t)kP2Q * cw + 8;
+  return words * sizeof(float);
+}
+
+uint32_t pipeline_grid_x(const Persist2Params &q) { return (q.cost.m + q.sb - 1) / q.sb; }
+
+cudaError_t pipeline_plan_config(const CostParams &p, int d, int sm_count, Persist2Params *q, bool *ok) {
+  *ok = false;
+  const int gm = grid_mode_of(p);
+  // packed arithmetic only (as cost_kernel_pk): verified reciprocal divides, no generic grid;
+  // the sample index shares its word with the 8-bit tag
+  if (p.k == 0 || p.m == 0 || p.n_noise != 1 || p.n < 2 || gm == GM_GENERIC || !p.fast_ok) return cudaSuccess;
+  if (p.m_global >= (1ull << 24) || p.sample_offset + p.m > (1ull << 24)) return cudaSuccess;
+  if ((uint32_t)sm_count < p.k) return cudaSuccess;
+  const uint32_t pairs = (p.n + 1) / 2;
+  uint32_t tl = 0;
+  while ((1u << tl) < pairs && tl < 5) ++tl;
+  const uint32_t T = 1u << tl, spw = 32 / T, ppt = (pairs + T - 1) / T;
+  // one CTA per SM: the fewest samples per CTA whose grid still fits the chip
+  const uint32_t ctas_per_climber = (uint32_t)sm_count / p.k;
+  const uint32_t sb = (p.m + ctas_per_climber - 1) / ctas_per_climber;
+  const uint32_t cw = (sb + spw - 1) / spw;
+  if (cw > (uint32_t)kP2MaxComputeWarps) return cudaSuccess;
+  const size_t smem = pipeline_smem(p, d, sb, cw);
+  if (smem > 200 * 1024) return cudaSuccess;
+  const void *kern = d == 5 ? pipeline_kernel_dim5(gm, p.use_limits != 0, p.fk_on != 0)
+                            : pipeline_kernel_dim4(gm, p.use_limits != 0, p.fk_on != 0);
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+  }
+  const int threads = 32 * (int)(cw + kP2HelperWarps);
+  int per_sm = 0;
+  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, smem);
+  if (e != cudaSuccess) return e;
+  const uint64_t ctas = (uint64_t)p.k * ((p.m + sb - 1) / sb);
+  if (per_sm < 1 || ctas > (uint64_t)per_sm * sm_count) return cudaSuccess;
+  q->cost = p;
+  q->cost.res_div = dm::FastDiv{p.grid.res, p.grid.res_rcp, 0.0f, 0.0f};
+  q->t_log2 = tl;
+  q->ppt = ppt;
+  q->sb = sb;
+  *ok = true;
+  return cudaSuccess;
+}
+
+cudaError_t launch_pipeline_plan(const Persist2Params &q, int d, int sm_count, cudaStream_t st) {
+  (void)sm_count;
+  const CostParams &p = q.cost;
+  const void *kern = d == 5 ? pipeline_kernel_dim5(grid_mode_of(p), p.use_limits != 0, p.fk_on != 0)
+                            : pipeline_kernel_dim4(grid_mode_of(p), p.use_limits != 0, p.fk_on != 0);
+  const uint32_t spw = 32u >> q.t_log2, cw = (q.sb + spw - 1) / spw;
+  const size_t smem = pipeline_smem(p, d, q.sb, cw);
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+  }
+  void *args[] = {(void *)&q};
+  return cudaLaunchCooperativeKernel(kern, dim3(pipeline_grid_x(q), p.k), dim3(32 * (cw + kP2HelperWarps)),
+                                     args, smem, st);
+}
+
 cudaError_t launch_verify_div(dm::FastDiv d, uint32_t lo_bits, uint32_t hi_bits, int mode,
                               unsigned long long *bad, int sm_count, cudaStream_t st) {
   verify_div_kernel<<<sm_count * 8, 256, 0, st>>>(d, lo_bits, hi_bits, mode, bad);

@@ -1,0 +1,485 @@
+// kernels_persist2.cu — plan_pipeline_kernel: the whole keep-best loop of
+// generate_trajectories.cu:197-253 in ONE cooperative launch, second generation.
+// Compiled once per joint count (-DDOAPP_D=4 / 5).
+//
+// Small problems (BASELINE config 2: 1024 samples x 64 waypoints x 100 iterations) are bound by
+// latency, not throughput: one iteration is 65 536 waypoint-samples, under half a wave.  The
+// kernel therefore runs ONE CTA PER SM with specialised warps and no CTA-wide barrier, atomic or
+// fence anywhere in the loop:
+//
+//   compute warps   one sample per group of T <= 32 lanes, every lane TWO consecutive waypoints
+//                   per step in packed fp32x2 arithmetic (waypoint_cost2, as cost_kernel_pk);
+//                   they cost iteration e on the CURRENT trajectory speculatively, up to `depth`
+//                   iterations ahead of the last decided one, and leave per-waypoint sums in a
+//                   shared-memory ring;
+//   fold warp       lane s folds sample s's per-waypoint sums in the canonical order (left fold,
+//                   waypoint 0 first: oracle ORC_SUM_WAYPOINT), takes the CTA's minimum key and
+//                   publishes it with ONE 8-byte store into the CTA's own slot of the
+//                   iteration's entry ring in global memory;
+//   collect warp    reads every CTA's slot of the oldest undecided iteration (coalesced 8-byte
+//                   loads, no atomics), merges across GPUs through NVLink peer mailboxes (one
+//                   8-byte store per peer), applies the keep-best (generate_trajectories.cu:225-241,
+//                   D5/D6 fixed) to the other trajectory buffer and bumps the version;
+//   noise warp      draws the Philox / Box-Muller noise vectors of later iterations into a ring.
+//
+// Every published word carries its own validity: key = {score bits : 8-bit tag : 24-bit sample},
+// tag = (iteration / ring) mod 16 and (trajectory version) mod 16.  A reader polls until all
+// slots show the tag of the (iteration, version) it is deciding, so no slot is ever re-armed, no
+// release/acquire pair is needed (the 8-byte word is the only data), and a CTA may abandon a
+// speculative iteration the moment it learns that an earlier one was accepted: all CTAs (and
+// ranks) see the same merged keys in the same order, so they agree on every (iteration, version)
+// that matters; words published for abandoned versions are never waited for.
+// An accepted update is rare (a few per plan), so the cost passes never wait for the exchange:
+// with depth d the exchange may take d - 1 evaluation times.
+// Arithmetic, noise, keys and tie-breaking are those of cost_kernel / cost_kernel_pk: results are
+// bit-identical to the launch-per-iteration path (tests/test_plan_gpu.py).
+#include "cost_device.cuh"
+
+#ifndef DOAPP_D
+#error "compile with -DDOAPP_D=4 or -DDOAPP_D=5"
+#endif
+
+namespace doapp {
+
+namespace {
+
+constexpr unsigned long long kTagMask = 0xFFull << 24;
+
+__device__ __forceinline__ uint32_t p2_tag(uint32_t it, uint32_t ver) {
+  return ((it / kP2Ring) & 15u) | ((ver & 15u) << 4);
+}
+__device__ __forceinline__ unsigned long long p2_pack(unsigned long long key, uint32_t tag) {
+  return (key & ~kTagMask) | ((unsigned long long)tag << 24);
+}
+__device__ __forceinline__ unsigned long long p2_strip(unsigned long long e) { return e & ~kTagMask; }
+__device__ __forceinline__ uint32_t p2_tag_of(unsigned long long e) { return (uint32_t)(e >> 24) & 0xFFu; }
+
+__device__ __forceinline__ uint32_t ldv(const volatile uint32_t *p) { return *p; }
+__device__ __forceinline__ void stv(volatile uint32_t *p, uint32_t v) { *p = v; }
+__device__ __forceinline__ unsigned long long ld_gpu(const unsigned long long *p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_gpu(unsigned long long *p, unsigned long long v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_sys(const unsigned long long *p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_sys(unsigned long long *p, unsigned long long v) {
+  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
+// control words of a CTA (shared memory, volatile)
+struct P2State {
+  uint32_t ver;     // trajectory version = accepted updates so far; buffer = ver & 1
+  uint32_t base;    // first iteration to cost with this version (the one after the last accept)
+  uint32_t decided; // iterations decided so far (every iteration below is final)
+  uint32_t noise;   // iterations whose noise is in the ring
+  uint32_t abort;   // exchange timed out: everybody leaves
+  uint32_t pad[3];
+};
+
+// The cost pass of iteration e for this lane's run of waypoint pairs: cost_kernel_pk's loop body.
+template <int D, int GM, bool LIM, bool FKM>
+__device__ __forceinline__ void p2_evaluate(const CostParams &P, const float *sb, uint32_t NP,
+                                            const float (&eps)[D], const float (&start)[D],
+                                            uint32_t w0, uint32_t w_end, float *sp, float *sl,
+                                            int *coll_out) {
+  using namespace dm;
+  float xprev[D], vprev[D];
+  bool fine1 = P.fast_ok != 0, fine2 = fine1;
+  if (w0 == 0) { // the initial waypoint is the prior of BOTH derivative passes (gt.cu:285, D7)
+#pragma unroll
+    for (int j = 0; j < D; ++j) {
+      xprev[j] = vprev[j] = start[j];
+      fine1 = fine1 & fine_angle(start[j]);
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < D; ++j) {
+      const float x1 = add_(sb[j * NP + w0 - 1], eps[j]);
+      const float x2 = add_(sb[j * NP + w0 - 2], eps[j]); // w0 is even and >= 2
+      xprev[j] = x1;
+      vprev[j] = div_fast(sub_(x1, x2), P.dt_div);
+      fine1 = fine1 & fine_angle(x1);
+      fine2 = fine2 & fine_angle(x2);
+    }
+  }
+  int coll = 0;
+  for (uint32_t w = w0; w < w_end; w += 2) {
+    const bool has_hi = w + 1 < w_end;
+    f2 x[D], vnew[D];
+#pragma unroll
+    for (int j = 0; j < D; ++j) { // generate_trajectories.cu:53-57
+      const float2 b = *reinterpret_cast<const float2 *>(sb + j * NP + w);
+      x[j] = f2_pack(add_(b.x, eps[j]), add_(b.y, eps[j]));
+    }
+    f2 a2, l2;
+    int cw0, cw1;
+    bool f0, f1;
+    waypoint_cost2<D, GM, LIM, FKM>(P, x, xprev, vprev, vnew, &a2, &l2, &cw0, &cw1, &f0, &f1);
+    const bool valid0 = f0 & fine1 & fine2, valid1 = f1 & f0 & fine1;
+    fine2 = f0 & (P.fast_ok != 0);
+    fine1 = f1 & (P.fast_ok != 0);
+    if (!(valid0 & valid1)) { // rare: redo the offending waypoint(s) with IEEE divides, full sin/cos
+#pragma unroll 1
+      for (int h = 0; h < 2; ++h) {
+        if (h == 0 ? valid0 : valid1) continue;
+        WpIn<D> in;
+#pragma unroll
+        for (int j = 0; j < D; ++j) {
+          in.x[j] = h ? f2_hi(x[j]) : f2_lo(x[j]);
+          in.xprev[j] = h ? f2_lo(x[j]) : xprev[j];
+          in.vprev[j] = h ? f2_lo(vnew[j]) : vprev[j];
+        }
+        const WpOut<D> o = waypoint_cost_general<D, GM, true, LIM, FKM>(P, in);
+#pragma unroll
+        for (int j = 0; j < D; ++j)
+          vnew[j] = h ? f2_pack(f2_lo(vnew[j]), o.vnew[j]) : f2_pack(o.vnew[j], f2_hi(vnew[j]));
+        a2 = h ? f2_pack(f2_lo(a2), o.a2) : f2_pack(o.a2, f2_hi(a2));
+        l2 = h ? f2_pack(f2_lo(l2), o.l2) : f2_pack(o.l2, f2_hi(l2));
+        if (h) cw1 = o.coll; else cw0 = o.coll;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < D; ++j) {
+      xprev[j] = f2_hi(x[j]);
+      vprev[j] = f2_hi(vnew[j]);
+    }
+    coll += cw0;
+    if (sp) sp[w] = f2_lo(a2);
+    if (LIM && sl) sl[w] = f2_lo(l2);
+    if (has_hi) {
+      coll += cw1;
+      if (sp) sp[w + 1] = f2_hi(a2);
+      if (LIM && sl) sl[w + 1] = f2_hi(l2);
+    }
+  }
+  *coll_out = coll;
+}
+
+template <int D, int GM, bool LIM, bool FKM>
+__global__ void __launch_bounds__(kP2MaxThreads) plan_pipeline_kernel(const __grid_constant__ Persist2Params Q) {
+  const CostParams &P = Q.cost;
+  extern __shared__ __align__(16) float smem[];
+  const uint32_t T = 1u << Q.t_log2, spw = 32u >> Q.t_log2; // lanes per sample, samples per warp
+  const uint32_t SB = Q.sb, CW = (SB + spw - 1) / spw;      // samples / compute warps per CTA
+  const uint32_t NP = P.npad + 2;                            // trajectory row: slot n duplicates n - 1
+  const uint32_t NPS = P.n | 1u;                             // row of per-waypoint sums (odd: the
+                                                             // fold's lanes hit distinct banks)
+  float *sbase = smem;                                       // [2][D][NP]   trajectory, by version & 1
+  float *spart = sbase + 2 * D * NP;                         // [Q][SB][NPS] per-waypoint sum of acc^2
+  float *slim = spart + (size_t)kP2Q * SB * NPS;             // [Q][SB][NPS] (limits)
+  float *seps = slim + (LIM ? (size_t)kP2Q * SB * NPS : 0);  // [Q][SB][8]   noise of iteration it in it % Q
+  float *swin = seps + (size_t)kP2Q * SB * 8;                // [8]          winner's noise
+  int *scoll = (int *)(swin + 8);                            // [Q][SB]
+  volatile uint32_t *stag = (volatile uint32_t *)(scoll + kP2Q * SB); // [Q][CW] (iteration << 8 | version) done
+  volatile P2State *S = (volatile P2State *)(stag + kP2Q * CW);
+
+  const uint32_t c = blockIdx.y, k = gridDim.y, nctas = gridDim.x;
+  const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t iters = Q.iters, depth = Q.depth;
+
+  // ---- prologue: the climber's trajectory -> buffer 0, control words
+  for (uint32_t i = threadIdx.x; i < (uint32_t)D * NP; i += blockDim.x) {
+    const uint32_t j = i / NP, w = i - j * NP;
+    const uint32_t ws = w < P.n ? w : P.n - 1;
+    sbase[i] = __ldg(P.traj + ((size_t)c * D + j) * P.npad + ws);
+  }
+  for (uint32_t i = threadIdx.x; i < kP2Q * CW; i += blockDim.x) stag[i] = 0xFFFFFFFFu;
+  if (threadIdx.x == 0) {
+    S->ver = 0;
+    S->base = 0;
+    S->decided = 0;
+    S->noise = 0;
+    S->abort = 0;
+  }
+  // the mailbox set of the NEXT launch: no peer writes it before this rank's last key of this
+  // launch has left (it needs that key to finish its own launch)
+  if (Q.nranks > 1 && blockIdx.x == 0)
+    for (uint32_t i = threadIdx.x; i < kP2Ring * 8; i += blockDim.x)
+      Q.mailbox_next[((size_t)(i >> 3) * k + c) * 8 + (i & 7)] = kKeyNone;
+  __syncthreads(); // the only CTA-wide barrier of the kernel
+
+  if (warp < CW) {
+    // ================================================================ compute warps
+    const uint32_t s_local = warp * spw + (lane >> Q.t_log2), r = lane & (T - 1);
+    const bool owns = s_local < SB;
+    uint32_t t = blockIdx.x * SB + (owns ? s_local : SB - 1);
+    t = t < P.m ? t : P.m - 1; // idle slots shadow the last sample
+    const uint32_t w0 = r * 2 * Q.ppt;
+    uint32_t w_end = w0 + 2 * Q.ppt;
+    w_end = w_end < P.n ? w_end : P.n;
+    float start[D];
+#pragma unroll
+    for (int j = 0; j < D; ++j) start[j] = __ldg(P.start + j);
+    uint32_t my_ver = 0, e = 0, evals = 0;
+    for (;;) {
+      bool leave = false;
+      for (;;) { // wait for work: warp-uniform (every read is a broadcast of one shared word)
+        const uint32_t v = ldv(&S->ver);
+        if (v != my_ver) { // an earlier iteration was accepted: restart behind it
+          __threadfence_block();
+          e = ldv(&S->base);
+          my_ver = v;
+        }
+        const uint32_t dec = ldv(&S->decided);
+        if (dec >= iters || ldv(&S->abort)) {
+          leave = true;
+          break;
+        }
+        if (e < iters && e < dec + depth && ldv(&S->noise) > e) break;
+        __nanosleep(32); // a spinning warp would take issue slots from the working ones
+      }
+      if (leave) break;
+      __threadfence_block(); // the noise / trajectory words behind the control words
+      const uint32_t q = e % kP2Q;
+      float eps[D];
+#pragma unroll
+      for (int j = 0; j < D; ++j) eps[j] = seps[((size_t)q * SB + (owns ? s_local : 0)) * 8 + j];
+      int coll = 0;
+      if (w0 < P.n)
+        p2_evaluate<D, GM, LIM, FKM>(P, sbase + (my_ver & 1u) * D * NP, NP, eps, start, w0, w_end,
+                                     owns ? spart + ((size_t)q * SB + s_local) * NPS : nullptr,
+                                     owns ? slim + ((size_t)q * SB + s_local) * NPS : nullptr, &coll);
+      for (uint32_t off = T >> 1; off >= 1; off >>= 1) coll += __shfl_xor_sync(kFull, coll, off);
+      if (r == 0 && owns) scoll[q * SB + s_local] = coll;
+      __syncwarp();
+      __threadfence_block();
+      if (lane == 0) stag[q * CW + warp] = (e << 8) | (my_ver & 0xFFu);
+      ++e;
+      ++evals;
+    }
+    if (Q.stats && blockIdx.x == 0 && c == 0 && threadIdx.x == 0) Q.stats[1] = evals;
+  } else if (warp == CW) {
+    // ================================================================ fold warp
+    uint32_t my_ver = 0, e = 0;
+    for (;;) {
+      bool leave = false;
+      for (;;) {
+        const uint32_t v = ldv(&S->ver);
+        if (v != my_ver) {
+          __threadfence_block();
+          e = ldv(&S->base);
+          my_ver = v;
+        }
+        if (ldv(&S->decided) >= iters || ldv(&S->abort)) {
+          leave = true;
+          break;
+        }
+        if (e < iters) {
+          const uint32_t want = (e << 8) | (my_ver & 0xFFu);
+          bool ok = true;
+          for (uint32_t wi = lane; wi < CW; wi += 32) ok = ok && stag[(e % kP2Q) * CW + wi] == want;
+          if (__all_sync(kFull, ok)) break;
+        }
+        __nanosleep(32);
+      }
+      if (leave) break;
+      __threadfence_block();
+      const uint32_t q = e % kP2Q;
+      unsigned long long key = kKeyNone;
+      for (uint32_t s = lane; s < SB; s += 32) {
+        const uint32_t t = blockIdx.x * SB + s;
+        const float *row = spart + ((size_t)q * SB + s) * NPS, *lrow = slim + ((size_t)q * SB + s) * NPS;
+        float total = 0.0f, ltotal = 0.0f; // fixed order: left fold over the waypoints
+        for (uint32_t w = 0; w < P.n; ++w) {
+          total = dm::add_(total, row[w]);
+          if (LIM) ltotal = dm::add_(ltotal, lrow[w]);
+        }
+        float score = dm::add_((float)scoll[q * SB + s], dm::mul_(P.smooth_scale, total)); // :81,100,107-108
+        if (LIM && P.limit_weight != 0.0f) score = dm::add_(score, dm::mul_(P.limit_weight, ltotal));
+        if (t < P.m) {
+          const unsigned long long kk =
+              ((unsigned long long)key_hi(P.select_mode, score) << 32) | (uint32_t)(P.sample_offset + t);
+          key = kk < key ? kk : key;
+        }
+      }
+      key = warp_min_u64(key);
+      if (lane == 0)
+        st_gpu(Q.entries + ((size_t)(e % kP2Ring) * k + c) * nctas + blockIdx.x, p2_pack(key, p2_tag(e, my_ver)));
+      ++e;
+    }
+  } else if (warp == CW + 1) {
+    // ================================================================ collect warp
+    uint32_t cur_hi = (uint32_t)(__ldg(P.pend_keys + c) >> 32); // the seed pass (gt.cu:180-191)
+    uint32_t ver = 0, accepts = 0;
+    bool dead = false;
+    const unsigned long long t_start = globaltimer_ns();
+    for (uint32_t i = 0; i < iters && !dead; ++i) {
+      const uint32_t want = p2_tag(i, ver);
+      const unsigned long long *row = Q.entries + ((size_t)(i % kP2Ring) * k + c) * nctas;
+      unsigned long long mn;
+      for (uint32_t spins = 1;; ++spins) { // every CTA's key of (i, ver): coalesced polls, no atomics
+        bool ok = true;
+        mn = kKeyNone;
+        for (uint32_t u = lane; u < nctas; u += 32) {
+          const unsigned long long v = ld_gpu(row + u);
+          ok = ok && p2_tag_of(v) == want;
+          const unsigned long long sv = p2_strip(v);
+          mn = sv < mn ? sv : mn;
+        }
+        if (__all_sync(kFull, ok)) break;
+        if ((spins & 0xFFFu) == 0 &&
+            (*(volatile unsigned int *)Q.error != 0 || globaltimer_ns() - t_start > Q.timeout_ns)) {
+          dead = true;
+          break;
+        }
+      }
+      if (dead) break;
+      mn = warp_min_u64(mn);
+      if (Q.nranks > 1) {
+        // rank keys through the peers' mailboxes: the climber's first CTA stores this rank's key
+        // into every rank's mailbox (one 8-byte store per peer over NVLink, the word carries its
+        // own tag), every CTA polls its own rank's mailbox -- local memory
+        const size_t slot = ((size_t)(i % kP2Ring) * k + c) * 8;
+        if (blockIdx.x == 0 && lane < Q.nranks) st_sys(Q.mailbox[lane] + slot + Q.rank, p2_pack(mn, want));
+        for (uint32_t spins = 1;; ++spins) {
+          unsigned long long v = 0;
+          bool ok = true;
+          if (lane < Q.nranks) {
+            v = ld_sys(Q.mailbox[Q.rank] + slot + lane);
+            ok = p2_tag_of(v) == want;
+          }
+          mn = lane < Q.nranks ? p2_strip(v) : kKeyNone;
+          if (__all_sync(kFull, ok)) break;
+          if ((spins & 0xFFFu) == 0 &&
+              (*(volatile unsigned int *)Q.error != 0 || globaltimer_ns() - t_start > Q.timeout_ns)) {
+            dead = true;
+            break;
+          }
+        }
+        if (dead) break;
+        mn = warp_min_u64(mn);
+      }
+      const uint32_t hi = (uint32_t)(mn >> 32);
+      if (hi < cur_hi) { // keep-best (generate_trajectories.cu:225-241, D5/D6 fixed)
+        cur_hi = hi;
+        ++accepts;
+        const uint32_t win = (uint32_t)mn & 0xFFFFFFu;
+        if (lane < 3) {
+          float a = 0.0f, b = 0.0f;
+          if (P.noise_mode == NOISE_PHILOX) {
+            dm::noise_pair(P.seed_lo, P.seed_hi, P.sigma, i, c, win, 0, lane, &a, &b);
+          } else if (P.noise_mode == NOISE_EXTERNAL) {
+            const float *pn = Q.noise_base + (size_t)i * Q.noise_iter_stride +
+                              ((size_t)c * P.noise_m + (size_t)(win - P.noise_t0)) * D;
+            a = 2 * lane < D ? __ldg(pn + 2 * lane) : 0.0f;
+            b = 2 * lane + 1 < D ? __ldg(pn + 2 * lane + 1) : 0.0f;
+          }
+          if (2 * lane < D) swin[2 * lane] = a;
+          if (2 * lane + 1 < D) swin[2 * lane + 1] = b;
+        }
+        __syncwarp();
+        const float *src = sbase + (ver & 1u) * D * NP;
+        float *dst = sbase + ((ver + 1) & 1u) * D * NP;
+        for (uint32_t idx = lane; idx < (uint32_t)D * NP; idx += 32) dst[idx] = dm::add_(src[idx], swin[idx / NP]);
+        ++ver;
+        __syncwarp();
+        __threadfence_block();
+        if (lane == 0) {
+          S->base = i + 1;
+          __threadfence_block();
+          S->ver = ver;
+          S->decided = i + 1;
+        }
+      } else if (lane == 0) {
+        S->decided = i + 1;
+      }
+    }
+    if (dead) {
+      if (lane == 0) {
+        atomicExch(Q.error, 1u);
+        S->abort = 1;
+      }
+    } else if (blockIdx.x == 0) { // the climber's final state, for the final scoring pass
+      const float *fin = sbase + (ver & 1u) * D * NP;
+      for (uint32_t idx = lane; idx < (uint32_t)D * P.npad; idx += 32) {
+        const uint32_t j = idx / P.npad, w = idx - j * P.npad;
+        P.traj_next[(size_t)c * D * P.npad + idx] = w < P.n ? fin[j * NP + w] : 0.0f;
+      }
+      if (lane == 0) {
+        P.cur_hi_out[c] = cur_hi;
+        P.found_better[c] = accepts ? 1 : 0;
+        if (Q.stats && c == 0) Q.stats[0] = accepts;
+      }
+    }
+  } else {
+    // ================================================================ noise warp
+    // one d-vector of noise per sample and iteration (generate_trajectories.cu:37-44), drawn up
+    // to Q - 1 iterations ahead of the last decided one: one Box-Muller pair per lane
+    for (uint32_t g = 0; g < iters; ++g) {
+      bool leave = false;
+      while (g >= ldv(&S->decided) + kP2Q) {
+        if (ldv(&S->abort)) {
+          leave = true;
+          break;
+        }
+        __nanosleep(64);
+      }
+      if (leave) break;
+      float *se = seps + (size_t)(g % kP2Q) * SB * 8;
+      if (P.noise_mode == NOISE_PHILOX) {
+        for (uint32_t l = lane; l < SB * 3; l += 32) {
+          const uint32_t s = l / 3, pr = l - 3 * s;
+          uint32_t t = blockIdx.x * SB + s;
+          t = t < P.m ? t : P.m - 1;
+          float a, b;
+          dm::noise_pair(P.seed_lo, P.seed_hi, P.sigma, g, c, (uint32_t)(P.sample_offset + t), 0, pr, &a, &b);
+          if (2 * pr < D) se[s * 8 + 2 * pr] = a;
+          if (2 * pr + 1 < D) se[s * 8 + 2 * pr + 1] = b;
+        }
+      } else {
+        for (uint32_t l = lane; l < SB * D; l += 32) {
+          const uint32_t s = l / D, j = l - D * s;
+          uint32_t t = blockIdx.x * SB + s;
+          t = t < P.m ? t : P.m - 1;
+          se[s * 8 + j] = P.noise_mode == NOISE_EXTERNAL
+                              ? __ldg(Q.noise_base + (size_t)g * Q.noise_iter_stride +
+                                      ((size_t)c * P.noise_m + (size_t)(P.sample_offset + t - P.noise_t0)) * D + j)
+                              : 0.0f;
+        }
+      }
+      __syncwarp();
+      __threadfence_block();
+      if (lane == 0) S->noise = g + 1;
+    }
+  }
+}
+
+} // namespace
+
+template <int D> static const void *pipeline_kernel_of(int gm, bool lim, bool fkm) {
+#define DOAPP_P2(GMV)                                                  \
+  return lim ? (const void *)plan_pipeline_kernel<D, GMV, true, false> \
+             : (const void *)plan_pipeline_kernel<D, GMV, false, false>
+#define DOAPP_P2_FK(GMV)                                              \
+  return lim ? (const void *)plan_pipeline_kernel<D, GMV, true, true> \
+             : (const void *)plan_pipeline_kernel<D, GMV, false, true>
+  if (fkm) {
+    if (gm == GM_U8_CDG) DOAPP_P2_FK(GM_U8_CDG);
+    if (gm == GM_F32_CDG) DOAPP_P2_FK(GM_F32_CDG);
+  }
+  switch (gm) {
+  case GM_U8_CDG: DOAPP_P2(GM_U8_CDG);
+  case GM_F32_CDG: DOAPP_P2(GM_F32_CDG);
+  default: DOAPP_P2(GM_NONE);
+  }
+#undef DOAPP_P2
+#undef DOAPP_P2_FK
+}
+
+const void *DOAPP_DIM_FN(pipeline_kernel_dim)(int gm, bool lim, bool fkm) {
+  return pipeline_kernel_of<DOAPP_D>(gm, lim, fkm);
+}
+
+} // namespace doapp

@@ -340,7 +340,10 @@ DOAPP_API doapp_status doapp_grid_broadcast(doapp_ctx *ctx, int32_t root);
  * the handles of all ranks (any transport; same role as the NCCL unique id above) and every
  * rank imports the full table, then all ranks synchronise once on the host before the first
  * doapp_plan.  At most 8 ranks (one NVSwitch domain).  Optional: without it multi-rank plans
- * use the NCCL path; doapp_peer_import(ctx, NULL, 0, 0) switches back to it. */
+ * use the NCCL path; doapp_peer_import(ctx, NULL, 0, 0) switches back to it.
+ * The ranks' kernels wait for each other: drive the ranks from separate threads / processes, or
+ * call doapp_plan_async on every rank's ctx before the first doapp_plan_wait.  A rank that never
+ * arrives makes the others give up after 20 s (doapp_plan_wait returns DOAPP_CUDA_ERROR). */
 #define DOAPP_PEER_HANDLE_BYTES 64
 DOAPP_API doapp_status doapp_peer_export(doapp_ctx *ctx, uint8_t handle[DOAPP_PEER_HANDLE_BYTES]);
 DOAPP_API doapp_status doapp_peer_import(doapp_ctx *ctx, const uint8_t *handles /*[nranks][64]*/,
@@ -352,6 +355,11 @@ DOAPP_API doapp_status doapp_peer_import(doapp_ctx *ctx, const uint8_t *handles 
  * launch per iteration), bit 1 = argmin keys merged in-kernel through the peer mailboxes
  * (else, with several ranks, one NCCL all-reduce per iteration). */
 DOAPP_API uint32_t doapp_plan_mode(const doapp_ctx *ctx);
+/* Counters of the last plan when it ran as one persistent launch (else zeros): accepted
+ * keep-best updates (generate_trajectories.cu:225-241) and cost passes the first CTA made --
+ * passes beyond `iters` were speculative ones discarded after an accepted update. */
+DOAPP_API doapp_status doapp_plan_stats(doapp_ctx *ctx, uint64_t *accepted_updates,
+                                        uint64_t *cost_passes);
 /* Number of kernels this ctx has launched since creation (bench `gpu_launches`). */
 DOAPP_API uint64_t doapp_launch_count(const doapp_ctx *ctx);
 /* The deterministic sin/cos used by the FK kernels, evaluated ON THE DEVICE for

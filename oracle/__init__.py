@@ -106,6 +106,8 @@ def lib() -> C.CDLL:
         L.orc_philox4x32_10.argtypes = [C.c_void_p] * 3
         L.orc_noise_fill.argtypes = [C.POINTER(Params), C.c_uint32, C.c_void_p]
         L.orc_fk_points.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p]
+        L.orc_rotation.argtypes = [C.c_int, C.c_float, C.c_void_p]
+        L.orc_rotation_rpy.argtypes = [C.c_float, C.c_float, C.c_float, C.c_void_p]
         L.orc_fk_model_rexarm.argtypes = [C.c_void_p]
         L.orc_fk_model_points.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
         L.orc_fk_points_as_shipped_matvec.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p]
@@ -158,6 +160,8 @@ class Oracle:
         for key, val in kw.items():
             if key in ("limit_min", "limit_max", "fk_model"):
                 continue
+            if key == "global_samples_per_climber":  # the name doapp_config uses
+                key = "m_global"
             if not hasattr(self.p, key):
                 raise AttributeError(key)
             setattr(self.p, key, val)
@@ -310,6 +314,19 @@ def philox(ctr, key):
     key = np.ascontiguousarray(key, np.uint32)
     out = np.empty(4, np.uint32)
     lib().orc_philox4x32_10(_p(ctr), _p(key), _p(out))
+    return out
+
+
+def rotation(axis: int, theta: float) -> np.ndarray:
+    """3x3 rotation builder of gt.cu:303-352 (axis 0/1/2 = x/y/z) with the deterministic sin/cos."""
+    out = np.empty((3, 3), np.float32)
+    lib().orc_rotation(int(axis), float(theta), _p(out))
+    return out
+
+
+def rotation_rpy(roll: float, pitch: float, yaw: float) -> np.ndarray:
+    out = np.empty((3, 3), np.float32)
+    lib().orc_rotation_rpy(float(roll), float(pitch), float(yaw), _p(out))
     return out
 
 

@@ -290,6 +290,17 @@ static void orc_fk_impl(const float *waypoint, uint32_t d, float out[5][3], int 
   }
 }
 
+/* test access to the rotation builders (pinned against the reference's own device code,
+ * tests/golden/ref_fk_outputs.npz): axis 0/1/2 = gt.cu:303-318 / 320-335 / 337-352 */
+void orc_rotation(int axis, float theta, float out[9]) {
+  orc_m3 R = axis == 0 ? orc_rotx(theta) : axis == 1 ? orc_roty(theta) : orc_rotz(theta);
+  memcpy(out, R.a, sizeof(R.a));
+}
+void orc_rotation_rpy(float roll, float pitch, float yaw, float out[9]) { /* gt.cu:354-367 */
+  orc_m3 R = orc_rot_rpy(roll, pitch, yaw);
+  memcpy(out, R.a, sizeof(R.a));
+}
+
 void orc_fk_points(const float *waypoint, uint32_t d, float out[5][3]) {
   orc_fk_impl(waypoint, d, out, 0);
 }

@@ -107,6 +107,8 @@ float orc_noise_at(const orc_params *p, uint32_t iteration, uint32_t c, uint64_t
                    uint32_t wn, uint32_t j);
 
 /* gt.cu:397-463 with a true mat-vec product: 5 link points of one waypoint */
+void orc_rotation(int axis, float theta, float out[9]);
+void orc_rotation_rpy(float roll, float pitch, float yaw, float out[9]);
 void orc_fk_points(const float *waypoint, uint32_t d, float out[5][3]);
 /* same, but with operator*(Matrix,Vector) as shipped (matrix.cuh:315-336: row sums) */
 void orc_fk_points_as_shipped_matvec(const float *waypoint, uint32_t d, float out[5][3]);
