@@ -892,9 +892,9 @@ doapp_status doapp_create(const doapp_config *cfg, doapp_ctx **out) {
     ST(ensure(ctx, ctx->found, k));
     ST(ensure(ctx, ctx->out, 4 + 2 * n * d));
     ST(ensure(ctx, ctx->p2_error, 1));
-    ST(ensure(ctx, ctx->p2_stats, 2));
+    ST(ensure(ctx, ctx->p2_stats, 8));
     CU(cudaMemsetAsync(ctx->p2_error.p, 0, sizeof(unsigned int), ctx->stream));
-    CU(cudaMemsetAsync(ctx->p2_stats.p, 0, 2 * sizeof(unsigned long long), ctx->stream));
+    CU(cudaMemsetAsync(ctx->p2_stats.p, 0, 8 * sizeof(unsigned long long), ctx->stream));
     CU(cudaMemsetAsync(ctx->traj.p, 0, sizeof(float) * 2 * ctx->traj_half, ctx->stream));
     CU(cudaMemsetAsync(ctx->start.p, 0, sizeof(float) * 8, ctx->stream));
     CU(cudaMemsetAsync(ctx->found.p, 0, k, ctx->stream));
@@ -1894,11 +1894,14 @@ uint64_t doapp_launch_count(const doapp_ctx *ctx) { return ctx ? ctx->launches :
 doapp_status doapp_plan_stats(doapp_ctx *ctx, uint64_t *accepted_updates, uint64_t *cost_passes) {
   if (!ctx) return DOAPP_INVALID_ARG;
   CU(cudaSetDevice(ctx->cfg.device));
-  unsigned long long h[2] = {0, 0};
+  unsigned long long h[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   CU(cudaStreamSynchronize(ctx->stream));
   if (ctx->p2_ran) CU(cudaMemcpy(h, ctx->p2_stats.p, sizeof(h), cudaMemcpyDeviceToHost));
   if (accepted_updates) *accepted_updates = h[0];
   if (cost_passes) *cost_passes = h[1];
+  if (getenv("DOAPP_P2_TRACE")) // SM clocks of the first CTA's warps, by phase
+    fprintf(stderr, "p2 trace: passes %llu eval %llu wait %llu | fold %llu wait %llu | poll %llu decide %llu\n",
+            h[1], h[2], h[3], h[4], h[5], h[6], h[7]);
   return DOAPP_OK;
 }
 uint32_t doapp_plan_mode(const doapp_ctx *ctx) { return ctx ? ctx->last_plan_mode : 0; }

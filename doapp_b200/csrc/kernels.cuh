@@ -159,7 +159,7 @@ struct Persist2Params {
   unsigned long long *mailbox[8];   // rank r's mailbox [kP2Ring][k][8] (own one included)
   unsigned long long *mailbox_next; // own mailbox set of the NEXT launch, re-armed at kernel start
   unsigned int *error;              // device word: set when the key exchange timed out
-  unsigned long long *stats;        // [2] accepted updates, cost passes of CTA 0 (or nullptr)
+  unsigned long long *stats;        // [8] accepted updates, cost passes of CTA 0, SM clocks by phase (or nullptr)
   unsigned long long timeout_ns;
 };
 cudaError_t pipeline_plan_config(const CostParams &p, int d, int sm_count, Persist2Params *q, bool *ok);

@@ -223,6 +223,7 @@ __global__ void __launch_bounds__(kP2MaxThreads) plan_pipeline_kernel(const __gr
 #pragma unroll
     for (int j = 0; j < D; ++j) start[j] = __ldg(P.start + j);
     uint32_t my_ver = 0, e = 0, evals = 0;
+    long long t_eval = 0, t_wait = 0, tc0 = clock64();
     for (;;) {
       bool leave = false;
       for (;;) { // wait for work: warp-uniform (every read is a broadcast of one shared word)
@@ -242,6 +243,8 @@ __global__ void __launch_bounds__(kP2MaxThreads) plan_pipeline_kernel(const __gr
       }
       if (leave) break;
       __threadfence_block(); // the noise / trajectory words behind the control words
+      const long long tc1 = clock64();
+      t_wait += tc1 - tc0;
       const uint32_t q = e % kP2Q;
       float eps[D];
 #pragma unroll
@@ -258,11 +261,18 @@ __global__ void __launch_bounds__(kP2MaxThreads) plan_pipeline_kernel(const __gr
       if (lane == 0) stag[q * CW + warp] = (e << 8) | (my_ver & 0xFFu);
       ++e;
       ++evals;
+      tc0 = clock64();
+      t_eval += tc0 - tc1;
     }
-    if (Q.stats && blockIdx.x == 0 && c == 0 && threadIdx.x == 0) Q.stats[1] = evals;
+    if (Q.stats && blockIdx.x == 0 && c == 0 && threadIdx.x == 0) {
+      Q.stats[1] = evals;
+      Q.stats[2] = (unsigned long long)t_eval; // SM clocks inside cost passes / waiting (warp 0)
+      Q.stats[3] = (unsigned long long)t_wait;
+    }
   } else if (warp == CW) {
     // ================================================================ fold warp
     uint32_t my_ver = 0, e = 0;
+    long long t_fold = 0, t_fwait = 0, tf0 = clock64();
     for (;;) {
       bool leave = false;
       for (;;) {
@@ -286,13 +296,29 @@ __global__ void __launch_bounds__(kP2MaxThreads) plan_pipeline_kernel(const __gr
       }
       if (leave) break;
       __threadfence_block();
+      const long long tf1 = clock64();
+      t_fwait += tf1 - tf0;
       const uint32_t q = e % kP2Q;
       unsigned long long key = kKeyNone;
       for (uint32_t s = lane; s < SB; s += 32) {
         const uint32_t t = blockIdx.x * SB + s;
         const float *row = spart + ((size_t)q * SB + s) * NPS, *lrow = slim + ((size_t)q * SB + s) * NPS;
         float total = 0.0f, ltotal = 0.0f; // fixed order: left fold over the waypoints
-        for (uint32_t w = 0; w < P.n; ++w) {
+        uint32_t w = 0;
+        for (; w + 8 <= P.n; w += 8) { // loads first: the dependent chain is the 8 adds only
+          float v[8], lv[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            v[u] = row[w + u];
+            if (LIM) lv[u] = lrow[w + u];
+          }
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            total = dm::add_(total, v[u]);
+            if (LIM) ltotal = dm::add_(ltotal, lv[u]);
+          }
+        }
+        for (; w < P.n; ++w) {
           total = dm::add_(total, row[w]);
           if (LIM) ltotal = dm::add_(ltotal, lrow[w]);
         }
@@ -308,6 +334,12 @@ __global__ void __launch_bounds__(kP2MaxThreads) plan_pipeline_kernel(const __gr
       if (lane == 0)
         st_gpu(Q.entries + ((size_t)(e % kP2Ring) * k + c) * nctas + blockIdx.x, p2_pack(key, p2_tag(e, my_ver)));
       ++e;
+      tf0 = clock64();
+      t_fold += tf0 - tf1;
+    }
+    if (Q.stats && blockIdx.x == 0 && c == 0 && lane == 0) {
+      Q.stats[4] = (unsigned long long)t_fold;
+      Q.stats[5] = (unsigned long long)t_fwait;
     }
   } else if (warp == CW + 1) {
     // ================================================================ collect warp
@@ -315,6 +347,7 @@ __global__ void __launch_bounds__(kP2MaxThreads) plan_pipeline_kernel(const __gr
     uint32_t ver = 0, accepts = 0;
     bool dead = false;
     const unsigned long long t_start = globaltimer_ns();
+    long long t_poll = 0, t_decide = 0, tk0 = clock64();
     for (uint32_t i = 0; i < iters && !dead; ++i) {
       const uint32_t want = p2_tag(i, ver);
       const unsigned long long *row = Q.entries + ((size_t)(i % kP2Ring) * k + c) * nctas;
@@ -361,6 +394,8 @@ __global__ void __launch_bounds__(kP2MaxThreads) plan_pipeline_kernel(const __gr
         if (dead) break;
         mn = warp_min_u64(mn);
       }
+      const long long tk1 = clock64();
+      t_poll += tk1 - tk0;
       const uint32_t hi = (uint32_t)(mn >> 32);
       if (hi < cur_hi) { // keep-best (generate_trajectories.cu:225-241, D5/D6 fixed)
         cur_hi = hi;
@@ -395,6 +430,12 @@ __global__ void __launch_bounds__(kP2MaxThreads) plan_pipeline_kernel(const __gr
       } else if (lane == 0) {
         S->decided = i + 1;
       }
+      tk0 = clock64();
+      t_decide += tk0 - tk1;
+    }
+    if (Q.stats && blockIdx.x == 0 && c == 0 && lane == 0) {
+      Q.stats[6] = (unsigned long long)t_poll;
+      Q.stats[7] = (unsigned long long)t_decide;
     }
     if (dead) {
       if (lane == 0) {
