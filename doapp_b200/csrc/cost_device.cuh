@@ -563,6 +563,29 @@ __device__ __forceinline__ void model_collisions2(const CostParams &P, const dm:
   *c_hi = hi;
 }
 
+// collision counts of two waypoints (lo, hi): the reference chain's 5 link points or the FK
+// model's spheres
+template <int D, int GM, bool FKM>
+__device__ __forceinline__ void waypoint_collisions2(const CostParams &P, const dm::f2 (&x)[D],
+                                                     int *coll_lo, int *coll_hi) {
+  int c_lo = 0, c_hi = 0;
+  if (GM != GM_NONE && FKM) {
+    model_collisions2<D, GM>(P, x, &c_lo, &c_hi);
+  } else if (GM != GM_NONE) {
+    P3v pts[5];
+    fk_points2<D>(x, P.rpy_s, P.rpy_c, pts);
+#pragma unroll
+    for (int l = 0; l < 5; ++l) {
+      int h0, h1;
+      collides2<GM>(P, pts[l], P.coll_dist, &h0, &h1);
+      c_lo += h0;
+      c_hi += h1;
+    }
+  }
+  *coll_lo = c_lo;
+  *coll_hi = c_hi;
+}
+
 // waypoint_cost<..., FAST = true> on two CONSECUTIVE WAYPOINTS (lo = w, hi = w + 1) of one
 // sample.  xprev / vprev are waypoint w - 1's angles and velocities; the hi half's priors are
 // the lo half's own results.  fine_lo / fine_hi as waypoint_cost's return value.
@@ -592,24 +615,9 @@ __device__ __forceinline__ void waypoint_cost2(const CostParams &P, const dm::f2
       l2 = f2_add(l2, f2_pack(__fmul_rn(h0, h0), __fmul_rn(h1, h1)));
     }
   }
-  int c_lo = 0, c_hi = 0;
-  if (GM != GM_NONE && FKM) {
-    model_collisions2<D, GM>(P, x, &c_lo, &c_hi);
-  } else if (GM != GM_NONE) {
-    P3v pts[5];
-    fk_points2<D>(x, P.rpy_s, P.rpy_c, pts);
-#pragma unroll
-    for (int l = 0; l < 5; ++l) {
-      int h0, h1;
-      collides2<GM>(P, pts[l], P.coll_dist, &h0, &h1);
-      c_lo += h0;
-      c_hi += h1;
-    }
-  }
+  waypoint_collisions2<D, GM, FKM>(P, x, coll_lo, coll_hi);
   *a2_out = a2;
   *l2_out = l2;
-  *coll_lo = c_lo;
-  *coll_hi = c_hi;
   *fine_lo = f_lo;
   *fine_hi = f_hi;
 }

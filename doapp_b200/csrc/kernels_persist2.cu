@@ -88,49 +88,88 @@ struct P2State {
   uint32_t pad[3];
 };
 
-// The cost pass of iteration e for this lane's run of waypoint pairs: cost_kernel_pk's loop body.
+// The cost pass of one iteration for this lane's waypoint pairs: pair p = r + i * T (i = 0 ..
+// ppt - 1) of the sample its T-lane group owns, i.e. waypoints 2p (lo half) and 2p + 1 (hi half)
+// in packed arithmetic (waypoint_cost2's derivative part + waypoint_collisions2).  The priors of
+// the lo waypoint -- angles and velocities of waypoint 2p - 1 -- are the hi half of the LEFT
+// lane's pair of the same step (lane 0: lane T - 1's pair of the previous step), so they come by
+// two warp shuffles per joint instead of being recomputed; pair 0 takes the initial waypoint for
+// both derivative passes (generate_trajectories.cu:285).
+// Exactness: the straight-line results are used only where dm::fine_angle holds for the waypoint
+// and its two predecessors (device_math.cuh); if ANY lane of the warp sees a waypoint that is
+// not (never in practice), the warp redoes those waypoints out of line with priors recomputed
+// from shared memory by IEEE divides -- the values the sequential kernels carry along.
 template <int D, int GM, bool LIM, bool FKM>
 __device__ __forceinline__ void p2_evaluate(const CostParams &P, const float *sb, uint32_t NP,
                                             const float (&eps)[D], const float (&start)[D],
-                                            uint32_t w0, uint32_t w_end, float *sp, float *sl,
-                                            int *coll_out) {
+                                            uint32_t r, uint32_t T, uint32_t ppt, uint32_t lane,
+                                            float *sp, float *sl, int *coll_out) {
   using namespace dm;
-  float xprev[D], vprev[D];
-  bool fine1 = P.fast_ok != 0, fine2 = fine1;
-  if (w0 == 0) { // the initial waypoint is the prior of BOTH derivative passes (gt.cu:285, D7)
+  const uint32_t src = (lane & ~(T - 1)) | ((r + T - 1) & (T - 1)); // left neighbour, rotating
+  const bool last = r == T - 1;
+  const uint32_t w_clamp = (P.n - 1) & ~1u; // idle lanes redo the last pair (shuffles stay convergent)
+  float xh_prev[D], vh_prev[D];
+  uint32_t code_prev = 3;
 #pragma unroll
-    for (int j = 0; j < D; ++j) {
-      xprev[j] = vprev[j] = start[j];
-      fine1 = fine1 & fine_angle(start[j]);
-    }
-  } else {
-#pragma unroll
-    for (int j = 0; j < D; ++j) {
-      const float x1 = add_(sb[j * NP + w0 - 1], eps[j]);
-      const float x2 = add_(sb[j * NP + w0 - 2], eps[j]); // w0 is even and >= 2
-      xprev[j] = x1;
-      vprev[j] = div_fast(sub_(x1, x2), P.dt_div);
-      fine1 = fine1 & fine_angle(x1);
-      fine2 = fine2 & fine_angle(x2);
-    }
-  }
+  for (int j = 0; j < D; ++j) xh_prev[j] = vh_prev[j] = 0.0f;
   int coll = 0;
-  for (uint32_t w = w0; w < w_end; w += 2) {
-    const bool has_hi = w + 1 < w_end;
+  for (uint32_t i = 0; i < ppt; ++i) {
+    const uint32_t p = r + i * T;
+    const bool live = 2 * p < P.n, first = p == 0;
+    const uint32_t w = live ? 2 * p : w_clamp;
+    const bool has_hi = w + 1 < P.n;
     f2 x[D], vnew[D];
+    float xprev[D], vprev[D];
+    bool f0 = true, f1 = true;
 #pragma unroll
     for (int j = 0; j < D; ++j) { // generate_trajectories.cu:53-57
       const float2 b = *reinterpret_cast<const float2 *>(sb + j * NP + w);
       x[j] = f2_pack(add_(b.x, eps[j]), add_(b.y, eps[j]));
+      f0 = f0 & fine_angle(f2_lo(x[j]));
+      f1 = f1 & fine_angle(f2_hi(x[j]));
     }
-    f2 a2, l2;
+    const uint32_t code = (f0 ? 1u : 0u) | (f1 ? 2u : 0u);
+    const uint32_t left = __shfl_sync(kFull, last ? code_prev : code, src);
+    bool fine1 = (left & 2u) != 0, fine2 = (left & 1u) != 0; // waypoints w - 1, w - 2
+    if (first) {
+      fine2 = true;
+      fine1 = true;
+#pragma unroll
+      for (int j = 0; j < D; ++j) fine1 = fine1 & fine_angle(start[j]);
+    }
+    f2 a2 = f2_splat(0.0f), l2 = f2_splat(0.0f);
+#pragma unroll
+    for (int j = 0; j < D; ++j) {
+      const float xl = __shfl_sync(kFull, last ? xh_prev[j] : f2_hi(x[j]), src);
+      xprev[j] = first ? start[j] : xl;
+      const f2 xp = f2_pack(xprev[j], f2_lo(x[j]));
+      const f2 v = f2_div_fast_unguarded(f2_sub(x[j], xp), P.dt_div); // :288
+      const float vl = __shfl_sync(kFull, last ? vh_prev[j] : f2_hi(v), src);
+      vprev[j] = first ? start[j] : vl;
+      const f2 vp = f2_pack(vprev[j], f2_lo(v));
+      const f2 a = f2_div_fast_unguarded(f2_sub(v, vp), P.dt_div);
+      a2 = f2_add(a2, f2_mul_rounded(a, a)); // :76 (product rounded, then added)
+      vnew[j] = v;
+      if (LIM) {
+        const f2 over = f2_sub(x[j], f2_splat(P.lim_max[j])), under = f2_sub(f2_splat(P.lim_min[j]), x[j]);
+        const float h0 = fmaxf(0.0f, fmaxf(f2_lo(over), f2_lo(under)));
+        const float h1 = fmaxf(0.0f, fmaxf(f2_hi(over), f2_hi(under)));
+        l2 = f2_add(l2, f2_pack(__fmul_rn(h0, h0), __fmul_rn(h1, h1)));
+      }
+    }
     int cw0, cw1;
-    bool f0, f1;
-    waypoint_cost2<D, GM, LIM, FKM>(P, x, xprev, vprev, vnew, &a2, &l2, &cw0, &cw1, &f0, &f1);
+    waypoint_collisions2<D, GM, FKM>(P, x, &cw0, &cw1);
     const bool valid0 = f0 & fine1 & fine2, valid1 = f1 & f0 & fine1;
-    fine2 = f0 & (P.fast_ok != 0);
-    fine1 = f1 & (P.fast_ok != 0);
-    if (!(valid0 & valid1)) { // rare: redo the offending waypoint(s) with IEEE divides, full sin/cos
+    if (__any_sync(kFull, !(valid0 & valid1))) { // rare: exact priors, then the general path
+      if (!first && w >= 2) {
+#pragma unroll
+        for (int j = 0; j < D; ++j) {
+          const float x1 = add_(sb[j * NP + w - 1], eps[j]);
+          const float x2 = w >= 2 ? add_(sb[j * NP + w - 2], eps[j]) : start[j];
+          xprev[j] = x1;
+          vprev[j] = div_(sub_(x1, x2), P.dt_div.b);
+        }
+      }
 #pragma unroll 1
       for (int h = 0; h < 2; ++h) {
         if (h == 0 ? valid0 : valid1) continue;
@@ -152,16 +191,19 @@ __device__ __forceinline__ void p2_evaluate(const CostParams &P, const float *sb
     }
 #pragma unroll
     for (int j = 0; j < D; ++j) {
-      xprev[j] = f2_hi(x[j]);
-      vprev[j] = f2_hi(vnew[j]);
+      xh_prev[j] = f2_hi(x[j]);
+      vh_prev[j] = f2_hi(vnew[j]);
     }
-    coll += cw0;
-    if (sp) sp[w] = f2_lo(a2);
-    if (LIM && sl) sl[w] = f2_lo(l2);
-    if (has_hi) {
-      coll += cw1;
-      if (sp) sp[w + 1] = f2_hi(a2);
-      if (LIM && sl) sl[w + 1] = f2_hi(l2);
+    code_prev = code;
+    if (live) {
+      coll += cw0;
+      if (sp) sp[w] = f2_lo(a2);
+      if (LIM && sl) sl[w] = f2_lo(l2);
+      if (has_hi) {
+        coll += cw1;
+        if (sp) sp[w + 1] = f2_hi(a2);
+        if (LIM && sl) sl[w + 1] = f2_hi(l2);
+      }
     }
   }
   *coll_out = coll;
@@ -216,9 +258,6 @@ __global__ void __launch_bounds__(kP2MaxThreads) plan_pipeline_kernel(const __gr
     const bool owns = s_local < SB;
     uint32_t t = blockIdx.x * SB + (owns ? s_local : SB - 1);
     t = t < P.m ? t : P.m - 1; // idle slots shadow the last sample
-    const uint32_t w0 = r * 2 * Q.ppt;
-    uint32_t w_end = w0 + 2 * Q.ppt;
-    w_end = w_end < P.n ? w_end : P.n;
     float start[D];
 #pragma unroll
     for (int j = 0; j < D; ++j) start[j] = __ldg(P.start + j);
@@ -250,11 +289,13 @@ __global__ void __launch_bounds__(kP2MaxThreads) plan_pipeline_kernel(const __gr
 #pragma unroll
       for (int j = 0; j < D; ++j) eps[j] = seps[((size_t)q * SB + (owns ? s_local : 0)) * 8 + j];
       int coll = 0;
-      if (w0 < P.n)
-        p2_evaluate<D, GM, LIM, FKM>(P, sbase + (my_ver & 1u) * D * NP, NP, eps, start, w0, w_end,
-                                     owns ? spart + ((size_t)q * SB + s_local) * NPS : nullptr,
-                                     owns ? slim + ((size_t)q * SB + s_local) * NPS : nullptr, &coll);
-      for (uint32_t off = T >> 1; off >= 1; off >>= 1) coll += __shfl_xor_sync(kFull, coll, off);
+      p2_evaluate<D, GM, LIM, FKM>(P, sbase + (my_ver & 1u) * D * NP, NP, eps, start, r, T, Q.ppt, lane,
+                                   owns ? spart + ((size_t)q * SB + s_local) * NPS : nullptr,
+                                   owns ? slim + ((size_t)q * SB + s_local) * NPS : nullptr, &coll);
+      if (T == 32)
+        coll = __reduce_add_sync(kFull, coll);
+      else
+        for (uint32_t off = T >> 1; off >= 1; off >>= 1) coll += __shfl_xor_sync(kFull, coll, off);
       if (r == 0 && owns) scoll[q * SB + s_local] = coll;
       __syncwarp();
       __threadfence_block();
@@ -292,7 +333,7 @@ __global__ void __launch_bounds__(kP2MaxThreads) plan_pipeline_kernel(const __gr
           for (uint32_t wi = lane; wi < CW; wi += 32) ok = ok && stag[(e % kP2Q) * CW + wi] == want;
           if (__all_sync(kFull, ok)) break;
         }
-        __nanosleep(32);
+        __nanosleep(100);
       }
       if (leave) break;
       __threadfence_block();
@@ -465,7 +506,7 @@ __global__ void __launch_bounds__(kP2MaxThreads) plan_pipeline_kernel(const __gr
           leave = true;
           break;
         }
-        __nanosleep(64);
+        __nanosleep(200);
       }
       if (leave) break;
       float *se = seps + (size_t)(g % kP2Q) * SB * 8;
