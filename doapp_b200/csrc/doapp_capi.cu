@@ -94,10 +94,11 @@ struct doapp_ctx {
   DevBuf<unsigned long long> pkeys; // persistent planner: 3 x [k] rotating barrier words {key, arrivals - 1}
   int persist_mode = -1;            // DOAPP_PERSIST=0/1: never / whenever legal
   int persist_version = 2;          // DOAPP_PERSIST_V=1: first-generation kernel (plan_persistent_kernel)
-  int persist_depth = 0;            // DOAPP_PERSIST_DEPTH=1..7 (0: 3 on one rank, 5 on several)
+  int persist_depth = 0;            // DOAPP_PERSIST_DEPTH=1..15 (0: 8 on one rank, 10 on several)
   DevBuf<unsigned long long> p2_entries, p2_stats; // plan_pipeline_kernel: tagged CTA keys, counters
   DevBuf<unsigned int> p2_error;    // set by the kernel when the key exchange timed out
   bool p2_ran = false;              // the last plan ran plan_pipeline_kernel
+  bool persist_graph_ok = true;     // the planner's launch sequence can be replayed as a CUDA graph
   // peer-memory argmin merge: own mailbox [2 epochs][3][k][8] + result [3][k], the ranks' mailboxes
   DevBuf<unsigned long long> mailbox, presult;
   unsigned long long *peer_mbox[8] = {};
@@ -493,7 +494,7 @@ doapp_status enqueue_plan_pipeline(doapp_ctx *ctx, Persist2Params q, uint32_t it
     q.mailbox_next = ctx->mailbox.p + ((ctx->peer_epoch + 1) & 1) * set;
     ctx->peer_epoch++;
   }
-  q.depth = ctx->persist_depth ? (uint32_t)ctx->persist_depth : (multi ? 5u : 3u);
+  q.depth = ctx->persist_depth ? (uint32_t)ctx->persist_depth : (multi ? 10u : 8u);
   if (q.depth > (uint32_t)kP2MaxDepth) q.depth = kP2MaxDepth;
   if (ctx->profiling) CU(cudaEventRecord(ctx->prof_events[0], ctx->stream));
   CU(launch_pipeline_plan(q, c.waypoint_dim, ctx->sm_count, ctx->stream));
@@ -712,12 +713,20 @@ doapp_status run_plan(doapp_ctx *ctx, uint32_t iters, int noise_mode) {
   PersistParams pq{};
   bool persistent = false;
   ST(persistent_eligible(ctx, &pq, &persistent));
-  if (!persistent) {
+  bool pipeline = false;
+  {
     Persist2Params pq2{};
-    ST(pipeline_eligible(ctx, &pq2, &persistent));
+    ST(pipeline_eligible(ctx, &pq2, &pipeline));
+    if (pipeline) // allocate outside any capture
+      ST(ensure(ctx, ctx->p2_entries, (size_t)kP2Ring * ctx->cfg.num_climbers * pipeline_grid_x(pq2)));
   }
-  // the persistent path is four launches in all: nothing for a graph to amortise
-  if (!ctx->use_graph || ctx->profiling || persistent) {
+  // The persistent planners are a handful of launches, but their launch gaps (memsets, seed
+  // pass, planner, final pass, selection) still cost ~0.2 us per iteration of a 100-iteration
+  // plan: the single-rank pipeline planner is replayed as a graph too.  Several ranks: the
+  // mailbox set alternates per launch, so the sequence is enqueued directly.
+  const bool graph_ok = ctx->use_graph && !ctx->profiling &&
+                        (pipeline ? (!ctx->comm && ctx->persist_graph_ok) : !persistent);
+  if (!graph_ok) {
     uint64_t nk = 0;
     ST(enqueue_plan(ctx, iters, noise_mode, &nk));
     ctx->launches += nk;
@@ -733,16 +742,23 @@ doapp_status run_plan(doapp_ctx *ctx, uint32_t iters, int noise_mode) {
     uint64_t nk = 0;
     doapp_status st = enqueue_plan(ctx, iters, noise_mode, &nk);
     cudaError_t ce = cudaStreamEndCapture(ctx->stream, &graph);
-    if (st != DOAPP_OK) {
-      if (graph) cudaGraphDestroy(graph);
-      return st;
+    if (ce == cudaSuccess && st == DOAPP_OK) {
+      ce = cudaGraphInstantiate(&ctx->graph_exec, graph, 0);
+      if (ce != cudaSuccess) ctx->graph_exec = nullptr;
     }
+    if (graph) cudaGraphDestroy(graph);
+    if (pipeline && (st != DOAPP_OK || ce != cudaSuccess)) {
+      // a cooperative launch that cannot be captured / instantiated here: enqueue directly
+      cudaGetLastError();
+      ctx->persist_graph_ok = false;
+      uint64_t nk2 = 0;
+      ST(enqueue_plan(ctx, iters, noise_mode, &nk2));
+      ctx->launches += nk2;
+      return DOAPP_OK;
+    }
+    if (st != DOAPP_OK) return st;
     if (ce != cudaSuccess)
-      return fail(ctx, DOAPP_CUDA_ERROR, "cudaStreamEndCapture: %s", cudaGetErrorString(ce));
-    ce = cudaGraphInstantiate(&ctx->graph_exec, graph, 0);
-    cudaGraphDestroy(graph);
-    if (ce != cudaSuccess)
-      return fail(ctx, DOAPP_CUDA_ERROR, "cudaGraphInstantiate: %s", cudaGetErrorString(ce));
+      return fail(ctx, DOAPP_CUDA_ERROR, "graph capture / instantiate: %s", cudaGetErrorString(ce));
     ctx->graph_iters = iters;
     ctx->graph_noise_mode = noise_mode;
     ctx->graph_noise_ptr = nptr;
@@ -863,7 +879,8 @@ doapp_status doapp_create(const doapp_config *cfg, doapp_ctx **out) {
   const char *pvv = getenv("DOAPP_PERSIST_V");
   ctx->persist_version = (pvv && pvv[0] == '1') ? 1 : 2;
   const char *pdv = getenv("DOAPP_PERSIST_DEPTH");
-  ctx->persist_depth = (pdv && pdv[0] >= '1' && pdv[0] <= '7') ? pdv[0] - '0' : 0;
+  ctx->persist_depth = pdv ? atoi(pdv) : 0;
+  if (ctx->persist_depth < 0 || ctx->persist_depth > kP2MaxDepth) ctx->persist_depth = 0;
   const char *pkv = getenv("DOAPP_PK");
   ctx->pk_mode = (pkv && (pkv[0] == '0' || pkv[0] == '1')) ? pkv[0] - '0' : -1;
   const char *xd = getenv("DOAPP_EXACT_DIV");
@@ -892,9 +909,9 @@ doapp_status doapp_create(const doapp_config *cfg, doapp_ctx **out) {
     ST(ensure(ctx, ctx->found, k));
     ST(ensure(ctx, ctx->out, 4 + 2 * n * d));
     ST(ensure(ctx, ctx->p2_error, 1));
-    ST(ensure(ctx, ctx->p2_stats, 8));
+    ST(ensure(ctx, ctx->p2_stats, 8 + 256 * 8));
     CU(cudaMemsetAsync(ctx->p2_error.p, 0, sizeof(unsigned int), ctx->stream));
-    CU(cudaMemsetAsync(ctx->p2_stats.p, 0, 8 * sizeof(unsigned long long), ctx->stream));
+    CU(cudaMemsetAsync(ctx->p2_stats.p, 0, (8 + 256 * 8) * sizeof(unsigned long long), ctx->stream));
     CU(cudaMemsetAsync(ctx->traj.p, 0, sizeof(float) * 2 * ctx->traj_half, ctx->stream));
     CU(cudaMemsetAsync(ctx->start.p, 0, sizeof(float) * 8, ctx->stream));
     CU(cudaMemsetAsync(ctx->found.p, 0, k, ctx->stream));
@@ -1899,6 +1916,25 @@ doapp_status doapp_plan_stats(doapp_ctx *ctx, uint64_t *accepted_updates, uint64
   if (ctx->p2_ran) CU(cudaMemcpy(h, ctx->p2_stats.p, sizeof(h), cudaMemcpyDeviceToHost));
   if (accepted_updates) *accepted_updates = h[0];
   if (cost_passes) *cost_passes = h[1];
+  if (getenv("DOAPP_P2_TRACE") && ctx->p2_ran) { // per-iteration stamps of the first CTA (SM clocks)
+    std::vector<unsigned long long> st(256 * 8);
+    CU(cudaMemcpy(st.data(), ctx->p2_stats.p + 8, st.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    double d[5] = {0, 0, 0, 0, 0};
+    int cnt = 0;
+    for (int it = 20; it < 90 && it < (int)ctx->plan_iters; ++it) {
+      const unsigned long long *r = &st[(size_t)it * 8];
+      if (!r[1] || !r[2] || !r[3] || !r[4] || !r[5]) continue;
+      d[0] += (double)(r[1] - r[0]); // pass
+      d[1] += (double)((long long)(r[2] - r[1])); // pass end -> fold sees tags
+      d[2] += (double)(r[3] - r[2]); // fold
+      d[3] += (double)((long long)(r[4] - r[3])); // publish -> all keys seen
+      d[4] += (double)(r[5] - r[4]); // decide
+      ++cnt;
+    }
+    if (cnt)
+      fprintf(stderr, "p2 stamps (%d iterations): pass %.0f | end->tags seen %.0f | fold %.0f | publish->all keys %.0f | decide %.0f\n",
+              cnt, d[0] / cnt, d[1] / cnt, d[2] / cnt, d[3] / cnt, d[4] / cnt);
+  }
   if (getenv("DOAPP_P2_TRACE")) // SM clocks of the first CTA's warps, by phase
     fprintf(stderr, "p2 trace: passes %llu eval %llu wait %llu | fold %llu wait %llu | poll %llu decide %llu\n",
             h[1], h[2], h[3], h[4], h[5], h[6], h[7]);

@@ -138,17 +138,19 @@ struct PersistParams {
 // Second-generation persistent planner (plan_pipeline_kernel, kernels_persist2.cu): one CTA per
 // SM, warp-specialised (compute / fold / collect / noise), speculation `depth` iterations deep,
 // tagged 8-byte key words instead of barriers.
-constexpr int kP2Ring = 16;        // iterations in the global entry / mailbox rings (>= 2 * depth + 1)
-constexpr int kP2Q = 8;            // iterations in the shared-memory rings (>= depth + 1)
-constexpr int kP2MaxDepth = 7;
-constexpr int kP2HelperWarps = 3;  // fold, collect, noise
-constexpr int kP2MaxComputeWarps = 16;
+constexpr int kP2Ring = 32;        // iterations in the global entry / mailbox rings (>= 2 * depth + 1)
+constexpr int kP2Q = 16;           // iterations in the shared-memory rings (>= depth + 1)
+constexpr int kP2MaxDepth = 15;
+constexpr int kP2FoldWarps = 2;    // iterations alternate between them
+constexpr int kP2NoiseWarps = 3;
+constexpr int kP2HelperWarps = kP2FoldWarps + 1 + kP2NoiseWarps; // fold, collect, noise
+constexpr int kP2MaxComputeWarps = 14;
 constexpr int kP2MaxThreads = 32 * (kP2MaxComputeWarps + kP2HelperWarps);
 struct Persist2Params {
   CostParams cost;             // traj = input, traj_next = output, pend_keys = the seed pass's keys
   uint32_t iters;
-  uint32_t t_log2;             // lanes per sample = 2^t_log2 (<= 32)
-  uint32_t ppt;                // waypoint pairs per lane
+  uint32_t t_log2;             // lanes per sample = 2^t_log2 (<= 64)
+  uint32_t wpt;                // waypoints per lane (lane r: waypoints r, r + T, ...)
   uint32_t sb;                 // samples per CTA
   uint32_t depth;              // iterations costed ahead of the last decided one
   unsigned long long *entries; // [kP2Ring][k][gridDim.x] tagged CTA keys (any content at launch

@@ -531,10 +531,16 @@ cudaError_t launch_cost(const CostParams &p_in, int d, int sm_count, cudaStream_
 }
 
 // ---- second-generation persistent planner: geometry, co-residency check, cooperative launch
-static size_t pipeline_smem(const CostParams &p, int d, uint32_t sb, uint32_t cw) {
-  const uint32_t NP = p.npad + 2, NPS = p.n | 1u;
+static uint32_t pipeline_compute_warps(uint32_t sb, uint32_t tl) {
+  const uint32_t T = 1u << tl;
+  return T > 32 ? sb * (T >> 5) : (sb + (32u >> tl) - 1) / (32u >> tl);
+}
+
+static size_t pipeline_smem(const CostParams &p, int d, uint32_t sb, uint32_t tl) {
+  const uint32_t NP = p.npad + 2, NPS = ((p.n + 3u) & ~3u) + 4u, T = 1u << tl, wps = T > 32 ? T >> 5 : 1u;
+  const uint32_t cw = pipeline_compute_warps(sb, tl);
   size_t words = (size_t)2 * d * NP + (size_t)kP2Q * sb * NPS * (p.use_limits ? 2 : 1) +
-                 (size_t)kP2Q * sb * 8 + 8 + (size_t)kP2Q * sb + (size_t)kP2Q * cw + 8;
+                 (size_t)kP2Q * sb * 8 + 8 + (size_t)kP2Q * sb * wps + (size_t)kP2Q * cw + kP2Q + 8;
   return words * sizeof(float);
 }
 
@@ -545,19 +551,21 @@ cudaError_t pipeline_plan_config(const CostParams &p, int d, int sm_count, Persi
   const int gm = grid_mode_of(p);
   // packed arithmetic only (as cost_kernel_pk): verified reciprocal divides, no generic grid;
   // the sample index shares its word with the 8-bit tag
-  if (p.k == 0 || p.m == 0 || p.n_noise != 1 || p.n < 2 || gm == GM_GENERIC || !p.fast_ok) return cudaSuccess;
+  if (p.k == 0 || p.m == 0 || p.n_noise != 1 || gm == GM_GENERIC || !p.fast_ok) return cudaSuccess;
   if (p.m_global >= (1ull << 24) || p.sample_offset + p.m > (1ull << 24)) return cudaSuccess;
   if ((uint32_t)sm_count < p.k) return cudaSuccess;
-  const uint32_t pairs = (p.n + 1) / 2;
-  uint32_t tl = 0;
-  while ((1u << tl) < pairs && tl < 5) ++tl;
-  const uint32_t T = 1u << tl, spw = 32 / T, ppt = (pairs + T - 1) / T;
   // one CTA per SM: the fewest samples per CTA whose grid still fits the chip
   const uint32_t ctas_per_climber = (uint32_t)sm_count / p.k;
   const uint32_t sb = (p.m + ctas_per_climber - 1) / ctas_per_climber;
-  const uint32_t cw = (sb + spw - 1) / spw;
+  // one waypoint per lane, up to 64 lanes (two warps) per sample; fewer lanes (more waypoints
+  // per lane) when the CTA's samples would need more than kP2MaxComputeWarps warps
+  uint32_t tl = 0;
+  while ((1u << tl) < p.n && tl < 6) ++tl;
+  while (tl > 0 && pipeline_compute_warps(sb, tl) > (uint32_t)kP2MaxComputeWarps) --tl;
+  const uint32_t cw = pipeline_compute_warps(sb, tl);
   if (cw > (uint32_t)kP2MaxComputeWarps) return cudaSuccess;
-  const size_t smem = pipeline_smem(p, d, sb, cw);
+  const uint32_t T = 1u << tl, wpt = (p.n + T - 1) / T;
+  const size_t smem = pipeline_smem(p, d, sb, tl);
   if (smem > 200 * 1024) return cudaSuccess;
   const void *kern = d == 5 ? pipeline_kernel_dim5(gm, p.use_limits != 0, p.fk_on != 0)
                             : pipeline_kernel_dim4(gm, p.use_limits != 0, p.fk_on != 0);
@@ -574,7 +582,7 @@ cudaError_t pipeline_plan_config(const CostParams &p, int d, int sm_count, Persi
   q->cost = p;
   q->cost.res_div = dm::FastDiv{p.grid.res, p.grid.res_rcp, 0.0f, 0.0f};
   q->t_log2 = tl;
-  q->ppt = ppt;
+  q->wpt = wpt;
   q->sb = sb;
   *ok = true;
   return cudaSuccess;
@@ -585,8 +593,8 @@ cudaError_t launch_pipeline_plan(const Persist2Params &q, int d, int sm_count, c
   const CostParams &p = q.cost;
   const void *kern = d == 5 ? pipeline_kernel_dim5(grid_mode_of(p), p.use_limits != 0, p.fk_on != 0)
                             : pipeline_kernel_dim4(grid_mode_of(p), p.use_limits != 0, p.fk_on != 0);
-  const uint32_t spw = 32u >> q.t_log2, cw = (q.sb + spw - 1) / spw;
-  const size_t smem = pipeline_smem(p, d, q.sb, cw);
+  const uint32_t cw = pipeline_compute_warps(q.sb, q.t_log2);
+  const size_t smem = pipeline_smem(p, d, q.sb, q.t_log2);
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;

@@ -61,8 +61,11 @@ __device__ __forceinline__ unsigned long long ld_gpu(const unsigned long long *p
   asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
   return v;
 }
+// publishing store: an atomic exchange is performed at the L2 at once, a plain store may sit in
+// the SM's write path for microseconds (measured: 4 us from store to visibility)
 __device__ __forceinline__ void st_gpu(unsigned long long *p, unsigned long long v) {
-  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+  unsigned long long old;
+  asm volatile("atom.relaxed.gpu.global.exch.b64 %0, [%1], %2;" : "=l"(old) : "l"(p), "l"(v) : "memory");
 }
 __device__ __forceinline__ unsigned long long ld_sys(const unsigned long long *p) {
   unsigned long long v;
@@ -71,6 +74,7 @@ __device__ __forceinline__ unsigned long long ld_sys(const unsigned long long *p
 }
 __device__ __forceinline__ void st_sys(unsigned long long *p, unsigned long long v) {
   asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+  asm volatile("fence.acq_rel.sys;" ::: "memory"); // push it out now
 }
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
   unsigned long long t;
@@ -88,68 +92,45 @@ struct P2State {
   uint32_t pad[3];
 };
 
-// The cost pass of one iteration for this lane's waypoint pairs: pair p = r + i * T (i = 0 ..
-// ppt - 1) of the sample its T-lane group owns, i.e. waypoints 2p (lo half) and 2p + 1 (hi half)
-// in packed arithmetic (waypoint_cost2's derivative part + waypoint_collisions2).  The priors of
-// the lo waypoint -- angles and velocities of waypoint 2p - 1 -- are the hi half of the LEFT
-// lane's pair of the same step (lane 0: lane T - 1's pair of the previous step), so they come by
-// two warp shuffles per joint instead of being recomputed; pair 0 takes the initial waypoint for
-// both derivative passes (generate_trajectories.cu:285).
-// Exactness: the straight-line results are used only where dm::fine_angle holds for the waypoint
-// and its two predecessors (device_math.cuh); if ANY lane of the warp sees a waypoint that is
-// not (never in practice), the warp redoes those waypoints out of line with priors recomputed
-// from shared memory by IEEE divides -- the values the sequential kernels carry along.
+// One cost pass of a compute lane: its waypoints w = r, r + T, ... of its sample for TWO
+// iterations at once -- the two halves of every packed register are the same waypoint under the
+// noise of iteration e (lo) and of iteration e + 1 (hi), both on the current trajectory (the
+// second is one more step of speculation).  All arithmetic is "vertical" fma.rn.f32x2: no
+// half-to-half moves.  The waypoint's priors (angles of w - 1, w - 2 and the velocity of w - 1;
+// the initial waypoint for both derivative passes at w = 0, generate_trajectories.cu:285, D7)
+// are recomputed from the shared trajectory, so lanes and warps are independent.
+// Exactness: the straight-line divides / sin / cos are bit-identical to the IEEE formulation
+// when every angle of the sample is "fine" (dm::fine_angle, device_math.cuh); the lane reports
+// whether its own angles are, per half, and the fold warp redoes a sample that is not (never in
+// practice) with the general path.
 template <int D, int GM, bool LIM, bool FKM>
 __device__ __forceinline__ void p2_evaluate(const CostParams &P, const float *sb, uint32_t NP,
-                                            const float (&eps)[D], const float (&start)[D],
-                                            uint32_t r, uint32_t T, uint32_t ppt, uint32_t lane,
-                                            float *sp, float *sl, int *coll_out) {
+                                            const dm::f2 (&eps)[D], const float (&start)[D],
+                                            uint32_t r, uint32_t T, uint32_t wpt, float *sp_lo,
+                                            float *sp_hi, float *sl_lo, float *sl_hi, int *coll_lo,
+                                            int *coll_hi, bool *fine_lo, bool *fine_hi) {
   using namespace dm;
-  const uint32_t src = (lane & ~(T - 1)) | ((r + T - 1) & (T - 1)); // left neighbour, rotating
-  const bool last = r == T - 1;
-  const uint32_t w_clamp = (P.n - 1) & ~1u; // idle lanes redo the last pair (shuffles stay convergent)
-  float xh_prev[D], vh_prev[D];
-  uint32_t code_prev = 3;
-#pragma unroll
-  for (int j = 0; j < D; ++j) xh_prev[j] = vh_prev[j] = 0.0f;
-  int coll = 0;
-  for (uint32_t i = 0; i < ppt; ++i) {
-    const uint32_t p = r + i * T;
-    const bool live = 2 * p < P.n, first = p == 0;
-    const uint32_t w = live ? 2 * p : w_clamp;
-    const bool has_hi = w + 1 < P.n;
-    f2 x[D], vnew[D];
-    float xprev[D], vprev[D];
-    bool f0 = true, f1 = true;
-#pragma unroll
-    for (int j = 0; j < D; ++j) { // generate_trajectories.cu:53-57
-      const float2 b = *reinterpret_cast<const float2 *>(sb + j * NP + w);
-      x[j] = f2_pack(add_(b.x, eps[j]), add_(b.y, eps[j]));
-      f0 = f0 & fine_angle(f2_lo(x[j]));
-      f1 = f1 & fine_angle(f2_hi(x[j]));
-    }
-    const uint32_t code = (f0 ? 1u : 0u) | (f1 ? 2u : 0u);
-    const uint32_t left = __shfl_sync(kFull, last ? code_prev : code, src);
-    bool fine1 = (left & 2u) != 0, fine2 = (left & 1u) != 0; // waypoints w - 1, w - 2
-    if (first) {
-      fine2 = true;
-      fine1 = true;
-#pragma unroll
-      for (int j = 0; j < D; ++j) fine1 = fine1 & fine_angle(start[j]);
-    }
-    f2 a2 = f2_splat(0.0f), l2 = f2_splat(0.0f);
+  int c_lo = 0, c_hi = 0;
+  bool f_lo = true, f_hi = true;
+  const uint32_t w_last = P.n - 1;
+  for (uint32_t i = 0; i < wpt; ++i) {
+    const uint32_t wq = r + i * T;
+    const bool live = wq < P.n;
+    const uint32_t w = live ? wq : w_last; // idle lanes shadow the last waypoint
+    f2 x[D], a2 = f2_splat(0.0f), l2 = f2_splat(0.0f);
 #pragma unroll
     for (int j = 0; j < D; ++j) {
-      const float xl = __shfl_sync(kFull, last ? xh_prev[j] : f2_hi(x[j]), src);
-      xprev[j] = first ? start[j] : xl;
-      const f2 xp = f2_pack(xprev[j], f2_lo(x[j]));
-      const f2 v = f2_div_fast_unguarded(f2_sub(x[j], xp), P.dt_div); // :288
-      const float vl = __shfl_sync(kFull, last ? vh_prev[j] : f2_hi(v), src);
-      vprev[j] = first ? start[j] : vl;
-      const f2 vp = f2_pack(vprev[j], f2_lo(v));
-      const f2 a = f2_div_fast_unguarded(f2_sub(v, vp), P.dt_div);
+      const float *row = sb + j * NP;
+      const f2 st = f2_splat(start[j]);
+      x[j] = f2_add(f2_splat(row[w]), eps[j]); // generate_trajectories.cu:53-57
+      const f2 x1 = w >= 1 ? f2_add(f2_splat(row[w - (w >= 1 ? 1 : 0)]), eps[j]) : st;
+      const f2 x2 = w >= 2 ? f2_add(f2_splat(row[w - (w >= 2 ? 2 : 0)]), eps[j]) : st;
+      const f2 v1 = w >= 1 ? f2_div_fast_unguarded(f2_sub(x1, x2), P.dt_div) : st;
+      const f2 v = f2_div_fast_unguarded(f2_sub(x[j], x1), P.dt_div); // :288
+      const f2 a = f2_div_fast_unguarded(f2_sub(v, v1), P.dt_div);
       a2 = f2_add(a2, f2_mul_rounded(a, a)); // :76 (product rounded, then added)
-      vnew[j] = v;
+      f_lo = f_lo & fine_angle(f2_lo(x[j]));
+      f_hi = f_hi & fine_angle(f2_hi(x[j]));
       if (LIM) {
         const f2 over = f2_sub(x[j], f2_splat(P.lim_max[j])), under = f2_sub(f2_splat(P.lim_min[j]), x[j]);
         const float h0 = fmaxf(0.0f, fmaxf(f2_lo(over), f2_lo(under)));
@@ -159,73 +140,42 @@ __device__ __forceinline__ void p2_evaluate(const CostParams &P, const float *sb
     }
     int cw0, cw1;
     waypoint_collisions2<D, GM, FKM>(P, x, &cw0, &cw1);
-    const bool valid0 = f0 & fine1 & fine2, valid1 = f1 & f0 & fine1;
-    if (__any_sync(kFull, !(valid0 & valid1))) { // rare: exact priors, then the general path
-      if (!first && w >= 2) {
-#pragma unroll
-        for (int j = 0; j < D; ++j) {
-          const float x1 = add_(sb[j * NP + w - 1], eps[j]);
-          const float x2 = w >= 2 ? add_(sb[j * NP + w - 2], eps[j]) : start[j];
-          xprev[j] = x1;
-          vprev[j] = div_(sub_(x1, x2), P.dt_div.b);
-        }
-      }
-#pragma unroll 1
-      for (int h = 0; h < 2; ++h) {
-        if (h == 0 ? valid0 : valid1) continue;
-        WpIn<D> in;
-#pragma unroll
-        for (int j = 0; j < D; ++j) {
-          in.x[j] = h ? f2_hi(x[j]) : f2_lo(x[j]);
-          in.xprev[j] = h ? f2_lo(x[j]) : xprev[j];
-          in.vprev[j] = h ? f2_lo(vnew[j]) : vprev[j];
-        }
-        const WpOut<D> o = waypoint_cost_general<D, GM, true, LIM, FKM>(P, in);
-#pragma unroll
-        for (int j = 0; j < D; ++j)
-          vnew[j] = h ? f2_pack(f2_lo(vnew[j]), o.vnew[j]) : f2_pack(o.vnew[j], f2_hi(vnew[j]));
-        a2 = h ? f2_pack(f2_lo(a2), o.a2) : f2_pack(o.a2, f2_hi(a2));
-        l2 = h ? f2_pack(f2_lo(l2), o.l2) : f2_pack(o.l2, f2_hi(l2));
-        if (h) cw1 = o.coll; else cw0 = o.coll;
-      }
-    }
-#pragma unroll
-    for (int j = 0; j < D; ++j) {
-      xh_prev[j] = f2_hi(x[j]);
-      vh_prev[j] = f2_hi(vnew[j]);
-    }
-    code_prev = code;
     if (live) {
-      coll += cw0;
-      if (sp) sp[w] = f2_lo(a2);
-      if (LIM && sl) sl[w] = f2_lo(l2);
-      if (has_hi) {
-        coll += cw1;
-        if (sp) sp[w + 1] = f2_hi(a2);
-        if (LIM && sl) sl[w + 1] = f2_hi(l2);
-      }
+      c_lo += cw0;
+      c_hi += cw1;
+      if (sp_lo) sp_lo[w] = f2_lo(a2);
+      if (sp_hi) sp_hi[w] = f2_hi(a2);
+      if (LIM && sl_lo) sl_lo[w] = f2_lo(l2);
+      if (LIM && sl_hi) sl_hi[w] = f2_hi(l2);
     }
   }
-  *coll_out = coll;
+  *coll_lo = c_lo;
+  *coll_hi = c_hi;
+  *fine_lo = f_lo;
+  *fine_hi = f_hi;
 }
 
 template <int D, int GM, bool LIM, bool FKM>
 __global__ void __launch_bounds__(kP2MaxThreads) plan_pipeline_kernel(const __grid_constant__ Persist2Params Q) {
   const CostParams &P = Q.cost;
   extern __shared__ __align__(16) float smem[];
-  const uint32_t T = 1u << Q.t_log2, spw = 32u >> Q.t_log2; // lanes per sample, samples per warp
-  const uint32_t SB = Q.sb, CW = (SB + spw - 1) / spw;      // samples / compute warps per CTA
-  const uint32_t NP = P.npad + 2;                            // trajectory row: slot n duplicates n - 1
-  const uint32_t NPS = P.n | 1u;                             // row of per-waypoint sums (odd: the
-                                                             // fold's lanes hit distinct banks)
+  // T lanes per sample (1 .. 64), each lane the waypoints r, r + T, ...; WPS warps per sample
+  // (T = 64) or spw samples per warp (T <= 32)
+  const uint32_t T = 1u << Q.t_log2, WPS = T > 32 ? T >> 5 : 1u, spw = T > 32 ? 1u : 32u >> Q.t_log2;
+  const uint32_t SB = Q.sb, CW = T > 32 ? SB * WPS : (SB + spw - 1) / spw; // samples / compute warps per CTA
+  const uint32_t NP = P.npad + 2;                            // trajectory row
+  const uint32_t NPS = ((P.n + 3u) & ~3u) + 4u;              // row of per-waypoint sums: 16-byte aligned
+                                                             // for the fold's vector loads, the rows
+                                                             // of 8 samples on distinct banks
   float *sbase = smem;                                       // [2][D][NP]   trajectory, by version & 1
   float *spart = sbase + 2 * D * NP;                         // [Q][SB][NPS] per-waypoint sum of acc^2
   float *slim = spart + (size_t)kP2Q * SB * NPS;             // [Q][SB][NPS] (limits)
   float *seps = slim + (LIM ? (size_t)kP2Q * SB * NPS : 0);  // [Q][SB][8]   noise of iteration it in it % Q
   float *swin = seps + (size_t)kP2Q * SB * 8;                // [8]          winner's noise
-  int *scoll = (int *)(swin + 8);                            // [Q][SB]
-  volatile uint32_t *stag = (volatile uint32_t *)(scoll + kP2Q * SB); // [Q][CW] (iteration << 8 | version) done
-  volatile P2State *S = (volatile P2State *)(stag + kP2Q * CW);
+  int *scoll = (int *)(swin + 8);                            // [Q][SB][WPS] collision counts per compute warp
+  volatile uint32_t *stag = (volatile uint32_t *)(scoll + kP2Q * SB * WPS); // [Q][CW] iteration << 8 | not-fine << 7 | version
+  volatile uint32_t *snz = stag + kP2Q * CW;                 // [Q] iteration + 1 whose noise is in the slot
+  volatile P2State *S = (volatile P2State *)(snz + kP2Q);
 
   const uint32_t c = blockIdx.y, k = gridDim.y, nctas = gridDim.x;
   const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -238,6 +188,7 @@ __global__ void __launch_bounds__(kP2MaxThreads) plan_pipeline_kernel(const __gr
     sbase[i] = __ldg(P.traj + ((size_t)c * D + j) * P.npad + ws);
   }
   for (uint32_t i = threadIdx.x; i < kP2Q * CW; i += blockDim.x) stag[i] = 0xFFFFFFFFu;
+  for (uint32_t i = threadIdx.x; i < kP2Q; i += blockDim.x) snz[i] = 0u;
   if (threadIdx.x == 0) {
     S->ver = 0;
     S->base = 0;
@@ -254,17 +205,22 @@ __global__ void __launch_bounds__(kP2MaxThreads) plan_pipeline_kernel(const __gr
 
   if (warp < CW) {
     // ================================================================ compute warps
-    const uint32_t s_local = warp * spw + (lane >> Q.t_log2), r = lane & (T - 1);
+    const uint32_t s_local = T > 32 ? warp / WPS : warp * spw + (lane >> Q.t_log2);
+    const uint32_t wis = T > 32 ? warp % WPS : 0u;                    // warp index inside the sample
+    const uint32_t r = T > 32 ? wis * 32 + lane : lane & (T - 1);     // lane index inside the sample
     const bool owns = s_local < SB;
-    uint32_t t = blockIdx.x * SB + (owns ? s_local : SB - 1);
-    t = t < P.m ? t : P.m - 1; // idle slots shadow the last sample
+    const uint32_t so = owns ? s_local : 0u;
     float start[D];
+    bool start_fine = true;
 #pragma unroll
-    for (int j = 0; j < D; ++j) start[j] = __ldg(P.start + j);
+    for (int j = 0; j < D; ++j) {
+      start[j] = __ldg(P.start + j);
+      start_fine = start_fine & dm::fine_angle(start[j]);
+    }
     uint32_t my_ver = 0, e = 0, evals = 0;
     long long t_eval = 0, t_wait = 0, tc0 = clock64();
     for (;;) {
-      bool leave = false;
+      bool leave = false, two = false;
       for (;;) { // wait for work: warp-uniform (every read is a broadcast of one shared word)
         const uint32_t v = ldv(&S->ver);
         if (v != my_ver) { // an earlier iteration was accepted: restart behind it
@@ -277,32 +233,66 @@ __global__ void __launch_bounds__(kP2MaxThreads) plan_pipeline_kernel(const __gr
           leave = true;
           break;
         }
-        if (e < iters && e < dec + depth && ldv(&S->noise) > e) break;
+        if (e < iters && e < dec + depth && snz[e % kP2Q] == e + 1) {
+          // a pass costs the same for one iteration as for two: when the next iteration may run
+          // too, wait for its noise rather than waste the hi halves
+          if (e + 1 < iters && e + 1 < dec + depth) {
+            if (snz[(e + 1) % kP2Q] == e + 2) {
+              two = true;
+              break;
+            }
+          } else {
+            break;
+          }
+        }
         __nanosleep(32); // a spinning warp would take issue slots from the working ones
       }
       if (leave) break;
       __threadfence_block(); // the noise / trajectory words behind the control words
       const long long tc1 = clock64();
       t_wait += tc1 - tc0;
-      const uint32_t q = e % kP2Q;
-      float eps[D];
+      const bool stamp = Q.stats && blockIdx.x == 0 && c == 0 && threadIdx.x == 0 && e < 256;
+      if (stamp) Q.stats[8 + e * 8 + 0] = (unsigned long long)tc1; // pass of iteration e starts
+      // iteration e in the lo halves, e + 1 in the hi halves (a copy of e when it may not run yet)
+      const uint32_t q0 = e % kP2Q, q1 = (two ? e + 1 : e) % kP2Q;
+      dm::f2 eps[D];
 #pragma unroll
-      for (int j = 0; j < D; ++j) eps[j] = seps[((size_t)q * SB + (owns ? s_local : 0)) * 8 + j];
-      int coll = 0;
-      p2_evaluate<D, GM, LIM, FKM>(P, sbase + (my_ver & 1u) * D * NP, NP, eps, start, r, T, Q.ppt, lane,
-                                   owns ? spart + ((size_t)q * SB + s_local) * NPS : nullptr,
-                                   owns ? slim + ((size_t)q * SB + s_local) * NPS : nullptr, &coll);
-      if (T == 32)
-        coll = __reduce_add_sync(kFull, coll);
-      else
-        for (uint32_t off = T >> 1; off >= 1; off >>= 1) coll += __shfl_xor_sync(kFull, coll, off);
-      if (r == 0 && owns) scoll[q * SB + s_local] = coll;
+      for (int j = 0; j < D; ++j)
+        eps[j] = dm::f2_pack(seps[((size_t)q0 * SB + so) * 8 + j], seps[((size_t)q1 * SB + so) * 8 + j]);
+      int coll_lo, coll_hi;
+      bool f_lo, f_hi;
+      p2_evaluate<D, GM, LIM, FKM>(P, sbase + (my_ver & 1u) * D * NP, NP, eps, start, r, T, Q.wpt,
+                                   owns ? spart + ((size_t)q0 * SB + s_local) * NPS : nullptr,
+                                   owns && two ? spart + ((size_t)q1 * SB + s_local) * NPS : nullptr,
+                                   owns ? slim + ((size_t)q0 * SB + s_local) * NPS : nullptr,
+                                   owns && two ? slim + ((size_t)q1 * SB + s_local) * NPS : nullptr,
+                                   &coll_lo, &coll_hi, &f_lo, &f_hi);
+      f_lo = f_lo & start_fine;
+      f_hi = f_hi & start_fine;
+      if (T >= 32) {
+        coll_lo = __reduce_add_sync(kFull, coll_lo);
+        coll_hi = __reduce_add_sync(kFull, coll_hi);
+      } else {
+        for (uint32_t off = T >> 1; off >= 1; off >>= 1) {
+          coll_lo += __shfl_xor_sync(kFull, coll_lo, off);
+          coll_hi += __shfl_xor_sync(kFull, coll_hi, off);
+        }
+      }
+      const bool bad_lo = !__all_sync(kFull, f_lo), bad_hi = !__all_sync(kFull, f_hi);
+      if ((lane & (T - 1) & 31u) == 0 && owns) {
+        scoll[(q0 * SB + s_local) * WPS + wis] = coll_lo;
+        if (two) scoll[(q1 * SB + s_local) * WPS + wis] = coll_hi;
+      }
       __syncwarp();
       __threadfence_block();
-      if (lane == 0) stag[q * CW + warp] = (e << 8) | (my_ver & 0xFFu);
-      ++e;
-      ++evals;
+      if (lane == 0) {
+        stag[q0 * CW + warp] = (e << 8) | (bad_lo ? 0x80u : 0u) | (my_ver & 0x7Fu);
+        if (two) stag[q1 * CW + warp] = ((e + 1) << 8) | (bad_hi ? 0x80u : 0u) | (my_ver & 0x7Fu);
+      }
       tc0 = clock64();
+      if (stamp) Q.stats[8 + e * 8 + 1] = (unsigned long long)tc0; // ... and ends (tags written)
+      e += two ? 2 : 1;
+      ++evals;
       t_eval += tc0 - tc1;
     }
     if (Q.stats && blockIdx.x == 0 && c == 0 && threadIdx.x == 0) {
@@ -310,17 +300,24 @@ __global__ void __launch_bounds__(kP2MaxThreads) plan_pipeline_kernel(const __gr
       Q.stats[2] = (unsigned long long)t_eval; // SM clocks inside cost passes / waiting (warp 0)
       Q.stats[3] = (unsigned long long)t_wait;
     }
-  } else if (warp == CW) {
-    // ================================================================ fold warp
-    uint32_t my_ver = 0, e = 0;
+  } else if (warp < CW + kP2FoldWarps) {
+    // ================================================================ fold warps
+    // (iterations alternate between them: fold warp f takes e = f mod kP2FoldWarps)
+    const uint32_t fw = warp - CW;
+    float start[D];
+#pragma unroll
+    for (int j = 0; j < D; ++j) start[j] = __ldg(P.start + j);
+    uint32_t my_ver = 0, e = fw;
     long long t_fold = 0, t_fwait = 0, tf0 = clock64();
     for (;;) {
       bool leave = false;
+      uint32_t bad = 0; // compute warps that met an angle outside the verified ranges
       for (;;) {
         const uint32_t v = ldv(&S->ver);
         if (v != my_ver) {
           __threadfence_block();
-          e = ldv(&S->base);
+          const uint32_t b0 = ldv(&S->base);
+          e = b0 + (fw + kP2FoldWarps - b0 % kP2FoldWarps) % kP2FoldWarps;
           my_ver = v;
         }
         if (ldv(&S->decided) >= iters || ldv(&S->abort)) {
@@ -328,61 +325,105 @@ __global__ void __launch_bounds__(kP2MaxThreads) plan_pipeline_kernel(const __gr
           break;
         }
         if (e < iters) {
-          const uint32_t want = (e << 8) | (my_ver & 0xFFu);
-          bool ok = true;
-          for (uint32_t wi = lane; wi < CW; wi += 32) ok = ok && stag[(e % kP2Q) * CW + wi] == want;
-          if (__all_sync(kFull, ok)) break;
+          const uint32_t want = (e << 8) | (my_ver & 0x7Fu);
+          bool ok = true, b = false;
+          for (uint32_t wi = lane; wi < CW; wi += 32) {
+            const uint32_t tg = stag[(e % kP2Q) * CW + wi];
+            ok = ok && (tg & ~0x80u) == want;
+            b = b || (tg & 0x80u) != 0;
+          }
+          if (__all_sync(kFull, ok)) {
+            bad = __ballot_sync(kFull, b);
+            break;
+          }
         }
-        __nanosleep(100);
+        __nanosleep(40);
       }
       if (leave) break;
       __threadfence_block();
       const long long tf1 = clock64();
       t_fwait += tf1 - tf0;
+      const bool fstamp = Q.stats && blockIdx.x == 0 && c == 0 && lane == 0 && e < 256;
+      if (fstamp) Q.stats[8 + e * 8 + 2] = (unsigned long long)tf1; // fold sees every warp's tag
       const uint32_t q = e % kP2Q;
       unsigned long long key = kKeyNone;
       for (uint32_t s = lane; s < SB; s += 32) {
         const uint32_t t = blockIdx.x * SB + s;
+        const uint32_t tg = (uint32_t)(P.sample_offset + (t < P.m ? t : P.m - 1));
         const float *row = spart + ((size_t)q * SB + s) * NPS, *lrow = slim + ((size_t)q * SB + s) * NPS;
         float total = 0.0f, ltotal = 0.0f; // fixed order: left fold over the waypoints
-        uint32_t w = 0;
-        for (; w + 8 <= P.n; w += 8) { // loads first: the dependent chain is the 8 adds only
-          float v[8], lv[8];
+        int coll = 0;
+        if (bad == 0) {
+          uint32_t w = 0;
+          for (; w + 32 <= P.n; w += 32) { // loads first: the dependent chain is the adds only
+            float4 v[8];
 #pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            v[u] = row[w + u];
-            if (LIM) lv[u] = lrow[w + u];
+            for (int u = 0; u < 8; ++u) v[u] = *reinterpret_cast<const float4 *>(row + w + 4 * u);
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+              total = dm::add_(total, v[u].x);
+              total = dm::add_(total, v[u].y);
+              total = dm::add_(total, v[u].z);
+              total = dm::add_(total, v[u].w);
+            }
+            if (LIM) {
+#pragma unroll
+              for (int u = 0; u < 8; ++u) v[u] = *reinterpret_cast<const float4 *>(lrow + w + 4 * u);
+#pragma unroll
+              for (int u = 0; u < 8; ++u) {
+                ltotal = dm::add_(ltotal, v[u].x);
+                ltotal = dm::add_(ltotal, v[u].y);
+                ltotal = dm::add_(ltotal, v[u].z);
+                ltotal = dm::add_(ltotal, v[u].w);
+              }
+            }
           }
+          for (; w < P.n; ++w) {
+            total = dm::add_(total, row[w]);
+            if (LIM) ltotal = dm::add_(ltotal, lrow[w]);
+          }
+          for (uint32_t u = 0; u < WPS; ++u) coll += scoll[(q * SB + s) * WPS + u];
+        } else {
+          // rare: some angle of this CTA's samples is outside the ranges the straight-line
+          // arithmetic was verified for: redo the sample with IEEE divides and full-range sin / cos
+          const float *sb = sbase + (my_ver & 1u) * D * NP;
+          WpIn<D> in;
 #pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            total = dm::add_(total, v[u]);
-            if (LIM) ltotal = dm::add_(ltotal, lv[u]);
+          for (int j = 0; j < D; ++j) in.xprev[j] = in.vprev[j] = start[j];
+          for (uint32_t w = 0; w < P.n; ++w) {
+#pragma unroll
+            for (int j = 0; j < D; ++j) in.x[j] = dm::add_(sb[j * NP + w], seps[((size_t)q * SB + s) * 8 + j]);
+            const WpOut<D> o = waypoint_cost_general<D, GM, true, LIM, FKM>(P, in);
+            total = dm::add_(total, o.a2);
+            if (LIM) ltotal = dm::add_(ltotal, o.l2);
+            coll += o.coll;
+#pragma unroll
+            for (int j = 0; j < D; ++j) {
+              in.xprev[j] = in.x[j];
+              in.vprev[j] = o.vnew[j];
+            }
           }
         }
-        for (; w < P.n; ++w) {
-          total = dm::add_(total, row[w]);
-          if (LIM) ltotal = dm::add_(ltotal, lrow[w]);
-        }
-        float score = dm::add_((float)scoll[q * SB + s], dm::mul_(P.smooth_scale, total)); // :81,100,107-108
+        float score = dm::add_((float)coll, dm::mul_(P.smooth_scale, total)); // :81,100,107-108
         if (LIM && P.limit_weight != 0.0f) score = dm::add_(score, dm::mul_(P.limit_weight, ltotal));
         if (t < P.m) {
-          const unsigned long long kk =
-              ((unsigned long long)key_hi(P.select_mode, score) << 32) | (uint32_t)(P.sample_offset + t);
+          const unsigned long long kk = ((unsigned long long)key_hi(P.select_mode, score) << 32) | tg;
           key = kk < key ? kk : key;
         }
       }
       key = warp_min_u64(key);
       if (lane == 0)
         st_gpu(Q.entries + ((size_t)(e % kP2Ring) * k + c) * nctas + blockIdx.x, p2_pack(key, p2_tag(e, my_ver)));
-      ++e;
       tf0 = clock64();
+      if (fstamp) Q.stats[8 + e * 8 + 3] = (unsigned long long)tf0; // key published
+      e += kP2FoldWarps;
       t_fold += tf0 - tf1;
     }
-    if (Q.stats && blockIdx.x == 0 && c == 0 && lane == 0) {
+    if (Q.stats && blockIdx.x == 0 && c == 0 && lane == 0 && fw == 0) {
       Q.stats[4] = (unsigned long long)t_fold;
       Q.stats[5] = (unsigned long long)t_fwait;
     }
-  } else if (warp == CW + 1) {
+  } else if (warp == CW + kP2FoldWarps) {
     // ================================================================ collect warp
     uint32_t cur_hi = (uint32_t)(__ldg(P.pend_keys + c) >> 32); // the seed pass (gt.cu:180-191)
     uint32_t ver = 0, accepts = 0;
@@ -396,11 +437,19 @@ __global__ void __launch_bounds__(kP2MaxThreads) plan_pipeline_kernel(const __gr
       for (uint32_t spins = 1;; ++spins) { // every CTA's key of (i, ver): coalesced polls, no atomics
         bool ok = true;
         mn = kKeyNone;
-        for (uint32_t u = lane; u < nctas; u += 32) {
-          const unsigned long long v = ld_gpu(row + u);
-          ok = ok && p2_tag_of(v) == want;
-          const unsigned long long sv = p2_strip(v);
-          mn = sv < mn ? sv : mn;
+        for (uint32_t u0 = 0; u0 < nctas; u0 += 32 * 8) { // up to 8 loads in flight per lane
+          unsigned long long v[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const uint32_t idx = u0 + u * 32 + lane;
+            v[u] = idx < nctas ? ld_gpu(row + idx) : p2_pack(kKeyNone, want);
+          }
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            ok = ok && p2_tag_of(v[u]) == want;
+            const unsigned long long sv = p2_strip(v[u]);
+            mn = sv < mn ? sv : mn;
+          }
         }
         if (__all_sync(kFull, ok)) break;
         if ((spins & 0xFFFu) == 0 &&
@@ -437,6 +486,8 @@ __global__ void __launch_bounds__(kP2MaxThreads) plan_pipeline_kernel(const __gr
       }
       const long long tk1 = clock64();
       t_poll += tk1 - tk0;
+      const bool kstamp = Q.stats && blockIdx.x == 0 && c == 0 && lane == 0 && i < 256;
+      if (kstamp) Q.stats[8 + i * 8 + 4] = (unsigned long long)tk1; // every CTA's key seen
       const uint32_t hi = (uint32_t)(mn >> 32);
       if (hi < cur_hi) { // keep-best (generate_trajectories.cu:225-241, D5/D6 fixed)
         cur_hi = hi;
@@ -473,6 +524,7 @@ __global__ void __launch_bounds__(kP2MaxThreads) plan_pipeline_kernel(const __gr
       }
       tk0 = clock64();
       t_decide += tk0 - tk1;
+      if (kstamp) Q.stats[8 + i * 8 + 5] = (unsigned long long)tk0; // decided
     }
     if (Q.stats && blockIdx.x == 0 && c == 0 && lane == 0) {
       Q.stats[6] = (unsigned long long)t_poll;
@@ -499,7 +551,8 @@ __global__ void __launch_bounds__(kP2MaxThreads) plan_pipeline_kernel(const __gr
     // ================================================================ noise warp
     // one d-vector of noise per sample and iteration (generate_trajectories.cu:37-44), drawn up
     // to Q - 1 iterations ahead of the last decided one: one Box-Muller pair per lane
-    for (uint32_t g = 0; g < iters; ++g) {
+    const uint32_t nw = warp - (CW + kP2FoldWarps + 1);
+    for (uint32_t g = nw; g < iters; g += kP2NoiseWarps) {
       bool leave = false;
       while (g >= ldv(&S->decided) + kP2Q) {
         if (ldv(&S->abort)) {
@@ -533,7 +586,7 @@ __global__ void __launch_bounds__(kP2MaxThreads) plan_pipeline_kernel(const __gr
       }
       __syncwarp();
       __threadfence_block();
-      if (lane == 0) S->noise = g + 1;
+      if (lane == 0) snz[g % kP2Q] = g + 1;
     }
   }
 }

@@ -7,7 +7,7 @@ import numpy as np
 from doapp_b200 import capi
 from tests import synth
 g = synth.box_grid(128, 0.01)
-for depth in ("1", "2", "3", "4", "6"):
+for depth in ("1", "6", "8", "10"):
     os.environ["DOAPP_PERSIST_DEPTH"] = depth
     ctx = capi.Context(k=1, m=1024, n=64, sigma=0.05, select_mode=1)
     ctx.set_grid(g, 0.01)
