@@ -110,6 +110,12 @@ def build(force: bool = False, verbose: bool = False) -> str:
                  os.path.join(host_dir, "follower_check.hpp"), LIB]
         cxx = shutil.which("g++") or "g++"
         common = ["-O2", "-std=c++17", "-fPIC", "-I", os.path.join(ROOT, "include"), "-I", host_dir]
+        # the reference vendors nanoflann (header-only, third party): with it on the include path
+        # PlanningState::updateDistanceGrid(const KDTree&) exists as in planning_state.cuh:25-28
+        nanoflann = os.environ.get("DOAPP_NANOFLANN_INCLUDE",
+                                   "/root/reference/perturbator/nanoflann/include")
+        if os.path.exists(os.path.join(nanoflann, "nanoflann.hpp")):
+            common += ["-DDOAPP_WITH_NANOFLANN", "-isystem", nanoflann]
         if force or _stale(HOST_LIB, hdeps):
             subprocess.run([cxx, *common, "-shared", host_src, "-o", HOST_LIB, "-L", LIB_DIR,
                             "-ldoapp_b200", "-Wl,-rpath,$ORIGIN"], check=True)
@@ -120,6 +126,13 @@ def build(force: bool = False, verbose: bool = False) -> str:
                             "-ldoapp_planning_state", "-ldoapp_b200", "-Wl,-rpath,$ORIGIN"],
                            check=True)
             _stamp(HOST_TEST, hdeps + [test_src, HOST_LIB])
+        node_src = os.path.join(host_dir, "motion_planner_main.cpp")
+        node_bin = os.path.join(LIB_DIR, "motion_planner_main")
+        if os.path.exists(node_src) and (force or _stale(node_bin, hdeps + [node_src, HOST_LIB])):
+            subprocess.run([cxx, *common, node_src, "-o", node_bin, "-L", LIB_DIR,
+                            "-ldoapp_planning_state", "-ldoapp_b200", "-Wl,-rpath,$ORIGIN"],
+                           check=True)
+            _stamp(node_bin, hdeps + [node_src, HOST_LIB])
     return LIB
 
 

@@ -340,7 +340,38 @@ __device__ __forceinline__ Pending pending_decide(const CostParams &P, uint32_t 
     pd.improve = true;
     if (blockIdx.x == 0 && threadIdx.x == 0) P.found_better[c] = 1;
   } else if (P.pend_mode != PEND_NONE) {
-    const unsigned long long pk = __ldg(P.pend_keys + c);
+    unsigned long long pk;
+    if (P.xr_nranks > 1 && P.pend_mode == PEND_KEEP_BEST) {
+      // the ranks' keys of the previous iteration arrive in this rank's mailbox (local memory,
+      // written by the peers over NVLink): lanes of warp 0 poll one rank each
+      __shared__ unsigned long long s_pk;
+      if (threadIdx.x < 32) {
+        unsigned long long v = kKeyNone;
+        if (threadIdx.x < P.xr_nranks) {
+          const unsigned long long *slot = P.xr_recv + (size_t)c * 8 + threadIdx.x;
+          unsigned long long t0 = 0;
+          for (uint32_t spins = 1;; ++spins) {
+            asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(slot) : "memory");
+            if (v != kKeyNone) break;
+            if ((spins & 0x3FFu) == 0) {
+              unsigned long long now;
+              asm volatile("mov.u64 %0, %globaltimer;" : "=l"(now));
+              if (t0 == 0) t0 = now;
+              if (now - t0 > P.xr_timeout_ns || *(volatile unsigned int *)P.xr_error != 0) {
+                atomicExch(P.xr_error, 1u);
+                break;
+              }
+            }
+          }
+        }
+        v = warp_min_u64(v);
+        if (threadIdx.x == 0) s_pk = v;
+      }
+      __syncthreads();
+      pk = s_pk;
+    } else {
+      pk = __ldg(P.pend_keys + c);
+    }
     const uint32_t hi = (uint32_t)(pk >> 32);
     pd.tg = (uint32_t)pk;
     uint32_t cur_new = hi;

@@ -146,6 +146,21 @@ struct doapp_ctx {
   uint64_t graph_grid_generation = ~0ull;
   uint64_t graph_kernels = 0;
   int graph_end_traj_s = 0, graph_end_cur_s = 0, graph_end_key_w = -1;
+  // fused multi-GPU key exchange (xchg_send_kernel + mailbox polls in the cost launches): plans
+  // alternate between two mailbox sets, so two graphs are cached; the one not current lives here
+  struct GraphAlt {
+    cudaGraphExec_t exec = nullptr;
+    uint32_t iters = 0;
+    int noise_mode = -1;
+    const float *noise_ptr = nullptr;
+    uint64_t grid_generation = ~0ull, kernels = 0;
+    int end_traj_s = 0, end_cur_s = 0, end_key_w = -1;
+  } graph_alt;
+  int graph_parity = 0;   // mailbox set the current graph was captured for
+  int xr_parity = 0;      // mailbox set of the plan being enqueued
+  bool xr_on = false;     // the plan being enqueued merges its keys through the peer mailboxes
+  int xr_mode = -1;       // DOAPP_XCHG=0: always NCCL
+  DevBuf<unsigned int> xr_error;
   bool use_graph = true;
   // cached graph of the dynamic-obstacle replan loop (doapp_replan_dynamic)
   cudaGraphExec_t replan_exec = nullptr;
@@ -222,6 +237,10 @@ void invalidate_graph(doapp_ctx *ctx) {
   if (ctx->replan_exec) {
     cudaGraphExecDestroy(ctx->replan_exec);
     ctx->replan_exec = nullptr;
+  }
+  if (ctx->graph_alt.exec) {
+    cudaGraphExecDestroy(ctx->graph_alt.exec);
+    ctx->graph_alt.exec = nullptr;
   }
   if (ctx->graph_exec) {
     cudaGraphExecDestroy(ctx->graph_exec);
@@ -603,6 +622,20 @@ doapp_status enqueue_plan(doapp_ctx *ctx, uint32_t iters, int noise_mode, uint64
   CU(cudaMemsetAsync(ctx->keys.p, 0xFF, sizeof(unsigned long long) * 3 * k, ctx->stream));
   ST(launch_pass(ctx, climber_cost_params(ctx), PEND_NONE, 0, NOISE_ZERO, nullptr, true));
   nk += 1;
+  // Several ranks with the peer mailboxes mapped: the per-iteration MIN all-reduce becomes one
+  // tiny sending kernel after every cost launch (8-byte stores into every rank's mailbox over
+  // NVLink) and a poll of the own mailbox in the next cost launch's prologue -- no collective
+  // launch, no NCCL kernel, in the loop.  Mailbox sets alternate per plan (xr_parity).
+  const bool xr = ctx->xr_on && nccl != nullptr;
+  const size_t xr_slot = k * 8, xr_set = 3 * xr_slot;
+  unsigned long long *xr_own = xr ? ctx->mailbox.p + (size_t)ctx->xr_parity * xr_set : nullptr;
+  auto xr_recv_from = [&](CostParams &p, uint32_t it_of_keys) {
+    p.xr_nranks = (uint32_t)ctx->peer_nranks;
+    p.xr_recv = xr_own + (size_t)(it_of_keys % 3) * xr_slot;
+    p.xr_error = ctx->xr_error.p;
+    p.xr_timeout_ns = 20ull * 1000000000ull;
+  };
+  if (xr) ctx->last_plan_mode = 2;
   const size_t noise_iter_stride =
       (size_t)c.num_climbers * ctx->m_global * c.noise_waypoints * c.waypoint_dim;
   auto noise_of = [&](uint32_t it) -> const float * {
@@ -627,12 +660,25 @@ doapp_status enqueue_plan(doapp_ctx *ctx, uint32_t iters, int noise_mode, uint64
       p.pend_usum = ctx->usum.p + (size_t)((it + 1) & 1) * k * 8; // sums of iteration it-1
       p.usum_reset = ctx->usum.p + (size_t)(it & 1) * k * 8;      // zeroed for this iteration
     }
+    if (xr && it > 0) xr_recv_from(p, it - 1);
     if (ctx->profiling) CU(cudaEventRecord(ctx->prof_events[2 * it], ctx->stream));
     ST(launch_pass(ctx, p, it == 0 ? PEND_SEED : pend_it, it ? it - 1 : 0, noise_mode,
                    it ? noise_of(it - 1) : nullptr, true));
     if (ctx->profiling) CU(cudaEventRecord(ctx->prof_events[2 * it + 1], ctx->stream));
     nk += 1;
-    if (nccl) {
+    if (xr) {
+      XchgSendParams x{};
+      x.keys = ctx->keys.p + (size_t)ctx->key_w * k;
+      for (int r = 0; r < ctx->peer_nranks; ++r)
+        x.peer_slot[r] = ctx->peer_mbox[r] + (size_t)ctx->xr_parity * xr_set + (size_t)(it % 3) * xr_slot;
+      x.rearm_slot = xr_own + (size_t)((it + 1) % 3) * xr_slot;
+      x.rearm_set = it == 0 ? ctx->mailbox.p + (size_t)(1 - ctx->xr_parity) * xr_set : nullptr;
+      x.k = (uint32_t)k;
+      x.nranks = (uint32_t)ctx->peer_nranks;
+      x.rank = (uint32_t)ctx->peer_rank;
+      CU(launch_xchg_send(x, ctx->stream));
+      nk += 1;
+    } else if (nccl) {
       unsigned long long *kb = ctx->keys.p + (size_t)ctx->key_w * k;
       ncclResult_t r = nccl->AllReduce(kb, kb, k, ncclUint64, ncclMin, ctx->comm, ctx->stream);
       if (r != ncclSuccess)
@@ -679,6 +725,7 @@ doapp_status enqueue_plan(doapp_ctx *ctx, uint32_t iters, int noise_mode, uint64
     // the winner's noise of the last iteration is still needed to apply its keep-best
     p.noise_m = ctx->m_global;
     p.noise_t0 = 0;
+    if (xr && iters > 0) xr_recv_from(p, iters - 1);
     ST(launch_pass(ctx, p, iters == 0 ? PEND_SEED : pend_it, iters ? iters - 1 : 0,
                    noise_mode, iters ? noise_of(iters - 1) : nullptr, false));
     FinalParams f{};
@@ -726,6 +773,29 @@ doapp_status run_plan(doapp_ctx *ctx, uint32_t iters, int noise_mode) {
   // mailbox set alternates per launch, so the sequence is enqueued directly.
   const bool graph_ok = ctx->use_graph && !ctx->profiling &&
                         (pipeline ? (!ctx->comm && ctx->persist_graph_ok) : !persistent);
+  // launch-per-iteration path on several ranks: keys through the peer mailboxes when they are
+  // mapped (keep-best rule; the weighted rule also needs its exact integer SUM: NCCL)
+  ctx->xr_on = !pipeline && !persistent && ctx->comm && ctx->peer_ready &&
+               ctx->peer_nranks == ctx->nranks && ctx->xr_mode != 0 &&
+               ctx->cfg.update_mode == DOAPP_UPDATE_KEEP_BEST;
+  if (ctx->xr_on) {
+    ctx->xr_parity = (int)(ctx->peer_epoch & 1);
+    ctx->peer_epoch++;
+    if (ctx->graph_parity != ctx->xr_parity) { // the other mailbox set: the other cached graph
+      doapp_ctx::GraphAlt cur;
+      cur.exec = ctx->graph_exec; cur.iters = ctx->graph_iters; cur.noise_mode = ctx->graph_noise_mode;
+      cur.noise_ptr = ctx->graph_noise_ptr; cur.grid_generation = ctx->graph_grid_generation;
+      cur.kernels = ctx->graph_kernels; cur.end_traj_s = ctx->graph_end_traj_s;
+      cur.end_cur_s = ctx->graph_end_cur_s; cur.end_key_w = ctx->graph_end_key_w;
+      const doapp_ctx::GraphAlt alt = ctx->graph_alt;
+      ctx->graph_exec = alt.exec; ctx->graph_iters = alt.iters; ctx->graph_noise_mode = alt.noise_mode;
+      ctx->graph_noise_ptr = alt.noise_ptr; ctx->graph_grid_generation = alt.grid_generation;
+      ctx->graph_kernels = alt.kernels; ctx->graph_end_traj_s = alt.end_traj_s;
+      ctx->graph_end_cur_s = alt.end_cur_s; ctx->graph_end_key_w = alt.end_key_w;
+      ctx->graph_alt = cur;
+      ctx->graph_parity = ctx->xr_parity;
+    }
+  }
   if (!graph_ok) {
     uint64_t nk = 0;
     ST(enqueue_plan(ctx, iters, noise_mode, &nk));
@@ -736,7 +806,14 @@ doapp_status run_plan(doapp_ctx *ctx, uint32_t iters, int noise_mode) {
   bool hit = ctx->graph_exec && ctx->graph_iters == iters && ctx->graph_noise_mode == noise_mode &&
              ctx->graph_noise_ptr == nptr && ctx->graph_grid_generation == ctx->grid_generation;
   if (!hit) {
-    invalidate_graph(ctx);
+    if (ctx->graph_exec) { // this parity's graph only; the other mailbox set's graph stays cached
+      cudaGraphExecDestroy(ctx->graph_exec);
+      ctx->graph_exec = nullptr;
+    }
+    if (ctx->replan_exec) {
+      cudaGraphExecDestroy(ctx->replan_exec);
+      ctx->replan_exec = nullptr;
+    }
     cudaGraph_t graph = nullptr;
     CU(cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal));
     uint64_t nk = 0;
@@ -881,6 +958,8 @@ doapp_status doapp_create(const doapp_config *cfg, doapp_ctx **out) {
   const char *pdv = getenv("DOAPP_PERSIST_DEPTH");
   ctx->persist_depth = pdv ? atoi(pdv) : 0;
   if (ctx->persist_depth < 0 || ctx->persist_depth > kP2MaxDepth) ctx->persist_depth = 0;
+  const char *xcv = getenv("DOAPP_XCHG");
+  ctx->xr_mode = (xcv && xcv[0] == '0') ? 0 : -1;
   const char *pkv = getenv("DOAPP_PK");
   ctx->pk_mode = (pkv && (pkv[0] == '0' || pkv[0] == '1')) ? pkv[0] - '0' : -1;
   const char *xd = getenv("DOAPP_EXACT_DIV");
@@ -908,6 +987,8 @@ doapp_status doapp_create(const doapp_config *cfg, doapp_ctx **out) {
     ST(ensure(ctx, ctx->usum, 2 * k * 8));
     ST(ensure(ctx, ctx->found, k));
     ST(ensure(ctx, ctx->out, 4 + 2 * n * d));
+    ST(ensure(ctx, ctx->xr_error, 1));
+    CU(cudaMemsetAsync(ctx->xr_error.p, 0, sizeof(unsigned int), ctx->stream));
     ST(ensure(ctx, ctx->p2_error, 1));
     ST(ensure(ctx, ctx->p2_stats, 8 + 256 * 8));
     CU(cudaMemsetAsync(ctx->p2_error.p, 0, sizeof(unsigned int), ctx->stream));
@@ -952,7 +1033,7 @@ void doapp_destroy(doapp_ctx *ctx) {
   release(ctx->keys_float); release(ctx->cur_hi); release(ctx->found); release(ctx->grid_cells);
   release(ctx->lookup_coll); release(ctx->lookup_idx); release(ctx->dbg_a); release(ctx->dbg_b);
   release(ctx->dbg_c); release(ctx->vbad); release(ctx->usum); release(ctx->pkeys);
-  release(ctx->p2_entries); release(ctx->p2_stats); release(ctx->p2_error);
+  release(ctx->p2_entries); release(ctx->p2_stats); release(ctx->p2_error); release(ctx->xr_error);
   for (int r = 0; r < 8; ++r)
     if (ctx->peer_ready && r != ctx->peer_rank && ctx->peer_mbox[r]) cudaIpcCloseMemHandle(ctx->peer_mbox[r]);
   release(ctx->mailbox); release(ctx->presult); release(ctx->depth); release(ctx->fk_dev);
@@ -1513,11 +1594,18 @@ doapp_status doapp_plan_wait(doapp_ctx *ctx, float *best_traj, float *best_vel, 
   const size_t nd = (size_t)ctx->cfg.num_waypoints * ctx->cfg.waypoint_dim;
   CU(cudaMemcpyAsync(ctx->h_out.data(), ctx->out.p, (4 + 2 * nd) * sizeof(float),
                      cudaMemcpyDeviceToHost, ctx->stream));
-  unsigned int p2_err = 0;
+  unsigned int p2_err = 0, xr_err = 0;
   if (ctx->p2_ran)
     CU(cudaMemcpyAsync(&p2_err, ctx->p2_error.p, sizeof(p2_err), cudaMemcpyDeviceToHost, ctx->stream));
+  if (ctx->xr_on)
+    CU(cudaMemcpyAsync(&xr_err, ctx->xr_error.p, sizeof(xr_err), cudaMemcpyDeviceToHost, ctx->stream));
   CU(cudaStreamSynchronize(ctx->stream));
   ctx->plan_pending = false;
+  if (xr_err) {
+    CU(cudaMemsetAsync(ctx->xr_error.p, 0, sizeof(unsigned int), ctx->stream));
+    return fail(ctx, DOAPP_CUDA_ERROR,
+                "planner: a rank's argmin key did not arrive in the peer mailbox (timed out)");
+  }
   if (p2_err) {
     CU(cudaMemsetAsync(ctx->p2_error.p, 0, sizeof(unsigned int), ctx->stream));
     return fail(ctx, DOAPP_CUDA_ERROR,

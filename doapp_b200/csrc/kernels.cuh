@@ -106,6 +106,14 @@ struct CostParams {
   const long long *pend_usum;
   long long *usum_reset;
   float update_gain;
+  // Multi-GPU argmin merge without a collective launch (xr_nranks > 1): the pending keys of the
+  // previous iteration are not read from pend_keys but from this rank's peer mailbox, where every
+  // rank's xchg_send_kernel stored its key over NVLink: xr_recv[(c * 8) + r] is rank r's key for
+  // climber c (kKeyNone until it arrives); the minimum is the merged key.
+  uint32_t xr_nranks;
+  const unsigned long long *xr_recv;
+  unsigned int *xr_error;          // set when a peer's key did not arrive within xr_timeout_ns
+  unsigned long long xr_timeout_ns;
   // launch geometry (filled by launch_cost): 2^parts_log2 threads per sample, each owning
   // wpp consecutive waypoints; 2^pw_log2 of them per CTA, the rest across a cluster
   uint32_t parts_log2, pw_log2, wpp;
@@ -240,6 +248,17 @@ cudaError_t launch_verify_div(dm::FastDiv d, uint32_t lo_bits, uint32_t hi_bits,
 cudaError_t persistent_plan_config(const CostParams &p, int d, int sm_count, PersistParams *q,
                                    bool *ok);
 cudaError_t launch_persistent_plan(const PersistParams &q, int d, cudaStream_t st);
+// Sends this rank's per-climber keys of one iteration into every rank's mailbox slot (one 8-byte
+// store per peer and climber over NVLink) after re-arming the own slot of the next iteration
+// and, on the first iteration of a plan, the own mailbox set of the next plan.
+struct XchgSendParams {
+  const unsigned long long *keys;   // [k] this rank's keys of the iteration
+  unsigned long long *peer_slot[8]; // rank r's mailbox slot of this iteration: [k][8]
+  unsigned long long *rearm_slot;   // own slot of the next iteration [k][8]
+  unsigned long long *rearm_set;    // own set of the next plan [3][k][8], or nullptr
+  uint32_t k, nranks, rank;
+};
+cudaError_t launch_xchg_send(const XchgSendParams &p, cudaStream_t st);
 cudaError_t launch_update_vector(const UpdateParams &p, int sm_count, cudaStream_t st);
 cudaError_t launch_final(const FinalParams &p, cudaStream_t st);
 // Occupancy (u8) -> exact Euclidean distance field (f32): three launches (rows, then a

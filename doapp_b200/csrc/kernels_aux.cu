@@ -66,6 +66,24 @@ __global__ void __launch_bounds__(256) update_vector_kernel(const __grid_constan
   }
 }
 
+// ------------------------------------------------------ key exchange, sending side
+// One thread per (climber, peer).  Order: re-arm own slots, fence, then the remote stores -- a
+// peer can only write a re-armed slot after it has received the key sent here (kernels.cuh).
+__global__ void xchg_send_kernel(const __grid_constant__ XchgSendParams P) {
+  const uint32_t total = P.k * 8;
+  for (uint32_t i = threadIdx.x; i < total; i += blockDim.x) P.rearm_slot[i] = kKeyNone;
+  if (P.rearm_set)
+    for (uint32_t i = threadIdx.x; i < 3 * total; i += blockDim.x) P.rearm_set[i] = kKeyNone;
+  __threadfence_system();
+  __syncthreads();
+  for (uint32_t i = threadIdx.x; i < P.k * P.nranks; i += blockDim.x) {
+    const uint32_t c = i / P.nranks, r = i - c * P.nranks;
+    const unsigned long long key = P.keys[c];
+    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(P.peer_slot[r] + (size_t)c * 8 + P.rank), "l"(key) : "memory");
+  }
+  __threadfence_system();
+}
+
 // --------------------------------------------------------------- final kernel
 // planning_state.cu:113-127: strict-< argmin over the climbers' scores (first
 // wins), then the winner's trajectory and backward-difference velocities.
@@ -607,6 +625,11 @@ cudaError_t launch_pipeline_plan(const Persist2Params &q, int d, int sm_count, c
 cudaError_t launch_verify_div(dm::FastDiv d, uint32_t lo_bits, uint32_t hi_bits, int mode,
                               unsigned long long *bad, int sm_count, cudaStream_t st) {
   verify_div_kernel<<<sm_count * 8, 256, 0, st>>>(d, lo_bits, hi_bits, mode, bad);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_xchg_send(const XchgSendParams &p, cudaStream_t st) {
+  xchg_send_kernel<<<1, 256, 0, st>>>(p);
   return cudaGetLastError();
 }
 

@@ -142,7 +142,7 @@ void PlanningState::publish_trajectory(doapp_host::Publisher &pub) {
   _have_goal = false;
 }
 
-void PlanningState::updateDistanceGrid(const std::vector<float> &distances) {
+void PlanningState::uploadDistanceGrid(const std::vector<float> &distances) {
   synchronize();
   doapp_status st = doapp_grid_alloc(ctx, DOAPP_GRID_F32, DOAPP_FRAME_CDG, (uint32_t)dims.length,
                                      (uint32_t)dims.width, (uint32_t)dims.height, dims.resolution);

@@ -14,6 +14,19 @@
 #include "doapp/doapp.h"
 #include "ros_mirror.hpp"
 
+// The reference's updateDistanceGrid takes a nanoflann KD-tree over the obstacle points
+// (planning_state.cuh:25-28, cpu_distance_grid.cuh:50-52).  nanoflann is a header-only third
+// party library vendored by the reference (perturbator/nanoflann, 1.3.2): when it is on the
+// include path the same overload exists here.
+#if !defined(DOAPP_WITH_NANOFLANN) && defined(__has_include)
+#if __has_include(<nanoflann.hpp>)
+#define DOAPP_WITH_NANOFLANN 1
+#endif
+#endif
+#ifdef DOAPP_WITH_NANOFLANN
+#include <nanoflann.hpp>
+#endif
+
 namespace doapp {
 namespace cpu_distance_grid {
 // perturbator/include/cpu_distance_grid.cuh:13-18
@@ -23,6 +36,24 @@ struct Dimensions {
   std::size_t height; // z
   double resolution;  // meters
 };
+#ifdef DOAPP_WITH_NANOFLANN
+// Dataset adaptor with the interface of cpu_distance_grid.cuh:20-48, over a plain [P][3] array
+// (the reference's adaptor wraps its own managed-memory Matrix<float, Dynamic, 3>).
+class MatrixPointcloudAdaptor {
+public:
+  using coord_t = float;
+  explicit MatrixPointcloudAdaptor(const std::vector<float> &xyz) noexcept : xyz_(&xyz) {}
+  std::size_t kdtree_get_point_count() const noexcept { return xyz_->size() / 3; }
+  float kdtree_get_pt(std::size_t index, std::size_t dimension) const { return (*xyz_)[3 * index + dimension]; }
+  template <typename BoundingBox> bool kdtree_get_bbox(BoundingBox &) const noexcept { return false; }
+
+private:
+  const std::vector<float> *xyz_;
+};
+// cpu_distance_grid.cuh:50-52
+using KDTree = nanoflann::KDTreeSingleIndexAdaptor<
+    nanoflann::L2_Simple_Adaptor<float, MatrixPointcloudAdaptor>, MatrixPointcloudAdaptor, 3>;
+#endif
 } // namespace cpu_distance_grid
 } // namespace doapp
 
@@ -48,9 +79,27 @@ public:
   // planning_state.cu:46-54 (with the missing write restored)
   std::vector<float> plan_lerp() const;
 
-  // dense host distance grid (fp32, index ix + L*iy + L*W*iz) -> device; replaces the
-  // KD-tree fill of updateDistanceGrid (planning_state.cuh:25-28, cpu_distance_grid.cu:87-202)
-  void updateDistanceGrid(const std::vector<float> &distances);
+#ifdef DOAPP_WITH_NANOFLANN
+  // planning_state.cuh:25-28, same signature.  The reference fills the distance grid on the host
+  // with one nearest-neighbour query per voxel (cpu_distance_grid.cu:87-202, 10^6 KD-tree
+  // queries for its 100^3 grid); here the tree's points are scattered into the occupancy grid
+  // and the exact Euclidean distance transform runs on the device (doapp_grid_scatter +
+  // doapp_grid_distance_field) -- distances between voxel centres instead of voxel centre to
+  // raw point, at most half a voxel diagonal apart.
+  void updateDistanceGrid(const doapp::cpu_distance_grid::KDTree &tree) noexcept {
+    const auto &pts = tree.dataset;
+    doapp_host::PointCloudXYZ cloud;
+    const std::size_t count = pts.kdtree_get_point_count();
+    cloud.xyz.resize(3 * count);
+    for (std::size_t i = 0; i < count; ++i)
+      for (std::size_t a = 0; a < 3; ++a) cloud.xyz[3 * i + a] = pts.kdtree_get_pt(i, a);
+    updatePointCloud(cloud, true);
+    buildDistanceField();
+  }
+#endif
+  // dense host distance grid (fp32, index ix + L*iy + L*W*iz) -> device (a caller that already
+  // holds the distances; not in the reference)
+  void uploadDistanceGrid(const std::vector<float> &distances);
   // the grid feed the reference never wired: an OccupancyGrid message, or an xyz cloud
   // scattered into a uint8 occupancy grid of the constructor's dimensions
   void updateOccupancyGrid(const doapp_host::OccupancyGridMsg &msg);

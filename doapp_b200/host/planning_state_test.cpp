@@ -1,9 +1,10 @@
 // planning_state_test.cpp — drives PlanningState the way perturbator/src/main.cu:24-43 does
 // (joint_state + goal_state callbacks, plan(), publish_trajectory()) without ROS, and prints the
 // published JointTrajectory as JSON for tests/test_host_gpu.py to check against the oracle.
-//   planning_state_test k m n d grid_n resolution iterations cloud.bin|- [follower_joints [edt|- [urdf]]]
+//   planning_state_test k m n d grid_n resolution iterations cloud.bin|- [follower_joints [edt|kdtree|- [urdf]]]
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <memory>
 #include <vector>
 
@@ -33,9 +34,23 @@ int main(int argc, char **argv) {
     cloud.xyz.resize(bytes / sizeof(float));
     if (std::fread(cloud.xyz.data(), 1, bytes, f) != (size_t)bytes) return 3;
     std::fclose(f);
-    planning_state.updatePointCloud(cloud);
-    if (argc > 10 && argv[10][0] != '-')
-      planning_state.buildDistanceField(); // sphere test on the derived distance grid
+    const bool want_tree = argc > 10 && std::strcmp(argv[10], "kdtree") == 0;
+    if (want_tree) {
+#ifdef DOAPP_WITH_NANOFLANN
+      // the reference's own entry point: a nanoflann KD-tree over the obstacle points
+      // (planning_state.cuh:25-28)
+      const doapp::cpu_distance_grid::MatrixPointcloudAdaptor adaptor(cloud.xyz);
+      doapp::cpu_distance_grid::KDTree tree(3, adaptor, nanoflann::KDTreeSingleIndexAdaptorParams(10));
+      tree.buildIndex();
+      planning_state.updateDistanceGrid(tree);
+#else
+      return 7; // built without nanoflann
+#endif
+    } else {
+      planning_state.updatePointCloud(cloud);
+      if (argc > 10 && argv[10][0] != '-')
+        planning_state.buildDistanceField(); // sphere test on the derived distance grid
+    }
   }
   if (argc > 11) planning_state.useUrdfKinematics(true);
 

@@ -25,13 +25,21 @@ def main():
     torch.cuda.set_device(lr)
     dev = torch.device("cuda", lr)
     dist.init_process_group("nccl", device_id=dev)
-    for mode_kw, peers in ((dict(), False), (dict(), True), (dict(update_mode=1, update_gain=1e-3), False)):
-        check(rank, world, lr, dev, mode_kw, peers)
+    # (update rule, peer mailboxes mapped, shape): NCCL per iteration; the persistent planner
+    # merging keys in-kernel; the weighted rule; and a problem too large for the persistent
+    # planner, whose cost launches trade keys through the mailboxes (xchg_send_kernel)
+    small, large = (2, 1000, 64, 8), (2, 40001, 32, 7)
+    for mode_kw, peers, shape in ((dict(), False, small), (dict(), True, small),
+                                  (dict(update_mode=1, update_gain=1e-3), False, small),
+                                  (dict(), True, large), (dict(), False, large)):
+        check(rank, world, lr, dev, mode_kw, peers, shape)
+        if peers:  # twice more: the mailbox sets alternate per plan
+            check(rank, world, lr, dev, mode_kw, peers, shape, plans=3)
     dist.barrier()
     dist.destroy_process_group()
 
 
-def check(rank, world, lr, dev, mode_kw, peers):
+def check(rank, world, lr, dev, mode_kw, peers, shape, plans=1):
     """keep-best (8*k-byte MIN all-reduce per iteration) or weighted update (plus one exact
     int64 SUM all-reduce of the fixed-point update-vector sums)."""
     import torch
@@ -39,7 +47,7 @@ def check(rank, world, lr, dev, mode_kw, peers):
     from doapp_b200 import capi, sharding
     from tests import synth
     import oracle
-    k, mg, n, iters = 2, 1000, 64, 8
+    k, mg, n, iters = shape
     off, cnt = sharding.shard_range(mg, rank, world)
     ctx = capi.Context(k=k, m=cnt, n=n, device=lr, sigma=0.05, select_mode=1, sample_offset=off,
                        global_samples_per_climber=mg, **mode_kw)
@@ -58,8 +66,10 @@ def check(rank, world, lr, dev, mode_kw, peers):
     assert np.array_equal(ctx.grid_download((128, 128, 128)), grid), "grid broadcast differs"
     start, goal = synth.START, synth.GOALS[1]
     init = capi.plan_lerp(start, goal, n)
-    r = ctx.plan(start, goal, init, iters)
+    for _ in range(plans):
+        r = ctx.plan(start, goal, init, iters)
     st = ctx.plan_state()
+    mode = ctx.plan_mode()
     ctx.close()
     # every rank holds the same kept trajectories
     t = torch.from_numpy(st["trajectories"].copy()).to(dev)
@@ -80,7 +90,7 @@ def check(rank, world, lr, dev, mode_kw, peers):
         ro = orc.plan(start, init, iters, threads=8)
         assert np.array_equal(ro["trajectories"].view(np.uint32), st["trajectories"].view(np.uint32))
         assert np.array_equal(ro["best_traj"].view(np.uint32), r["best_traj"].view(np.uint32))
-        print(f"multigpu_check ok: world={world} mode={mode_kw} peer_mailboxes={peer_ok} best_score={r['best_score']:.6f} "
+        print(f"multigpu_check ok: world={world} shape={shape} plans={plans} mode={mode_kw} peer_mailboxes={peer_ok} plan_mode={mode} best_score={r['best_score']:.6f} "
               f"found_better={st['found_better'].tolist()}", flush=True)
     dist.barrier()
 

@@ -138,3 +138,32 @@ def test_urdf_kinematics_through_planning_state(capi, oracle_mod, tmp_path):
     epos, _, _ = oracle_mod.build_message(cur, goal, r["best_traj"], r["best_vel"], 0.1)
     assert np.array_equal(pos.view(np.uint32), epos.view(np.uint32))
     assert np.float32(msg["cost"]) == np.float32(r["best_score"])
+
+
+@pytest.mark.gpu
+def test_update_distance_grid_from_kdtree(capi, tmp_path):
+    """PlanningState::updateDistanceGrid(const KDTree&) (planning_state.cuh:25-28, nanoflann tree
+    over the obstacle points) gives the plan of the explicit scatter + distance-field calls."""
+    k, m, n, d, iters, gn, res = 2, 64, 32, 5, 4, 64, 0.02
+    path = tmp_path / "cloud.bin"
+    synth.cloud(30000, 0).astype(np.float32).tofile(path)
+    outs = []
+    for mode in ("edt", "kdtree"):
+        out = subprocess.run([BIN, str(k), str(m), str(n), str(d), str(gn), str(res), str(iters),
+                              str(path), "6", mode], capture_output=True, text=True, timeout=120)
+        if mode == "kdtree" and out.returncode == 7:
+            pytest.skip("host library built without nanoflann")
+        assert out.returncode == 0, out.stderr
+        outs.append(json.loads(out.stdout))
+    assert outs[0]["points"] == outs[1]["points"] and outs[0]["cost"] == outs[1]["cost"]
+
+
+@pytest.mark.gpu
+def test_motion_planner_node_loop(capi):
+    """The node's plan / publish cycle of perturbator/src/main.cu:31-44 at its shipped shape
+    (k = 1000, n = 50, d = 4, m = 5, 100^3 grid at 1 cm), driven without ROS."""
+    exe = os.path.join(os.path.dirname(BIN), "motion_planner_main")
+    out = subprocess.run([exe, "3", "10"], capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0, out.stdout + out.stderr
+    lines = [ln for ln in out.stdout.splitlines() if ln.startswith("cycle")]
+    assert len(lines) == 3 and all("52 points" in ln for ln in lines)  # n + 2 points per message
