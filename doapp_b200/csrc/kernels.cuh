@@ -151,7 +151,7 @@ constexpr int kP2Q = 16;           // iterations in the shared-memory rings (>= 
 constexpr int kP2MaxDepth = 15;
 constexpr int kP2FoldWarps = 2;    // iterations alternate between them
 constexpr int kP2NoiseWarps = 3;
-constexpr int kP2HelperWarps = kP2FoldWarps + 1 + kP2NoiseWarps; // fold, collect, noise
+constexpr int kP2HelperWarps = kP2FoldWarps + 2 + kP2NoiseWarps; // fold, collect, send, noise
 constexpr int kP2MaxComputeWarps = 14;
 constexpr int kP2MaxThreads = 32 * (kP2MaxComputeWarps + kP2HelperWarps);
 struct Persist2Params {

@@ -233,9 +233,10 @@ __global__ void __launch_bounds__(32) edt_lines_kernel(const int32_t *in, void *
   const bool live = x < nx;
   const uint64_t base = (uint64_t)blockIdx.y * line_stride + (live ? x : nx - 1);
   for (uint32_t u = 0; u < n; ++u) g[u * 32 + lane] = __ldg(in + base + (uint64_t)u * stride);
-  auto f = [&](int xx, int i) -> long long {
-    return (long long)(xx - i) * (xx - i) + g[i * 32 + lane];
-  };
+  // 32-bit arithmetic throughout: (x - i)^2 < 2^20 (n <= kEdtMaxDim) and g <= kEdtInf = 2^29,
+  // so every value below stays under 2^31 (64-bit multiplies and divides made this scan
+  // several times slower)
+  auto f = [&](int xx, int i) -> int { return (xx - i) * (xx - i) + g[i * 32 + lane]; };
   int q = 0;
   s[lane] = 0;
   t[lane] = 0;
@@ -245,13 +246,13 @@ __global__ void __launch_bounds__(32) edt_lines_kernel(const int32_t *in, void *
       q = 0;
       s[lane] = (uint16_t)u;
     } else {
-      const long long i = s[q * 32 + lane];
-      const long long num = (long long)u * u - i * i + g[u * 32 + lane] - g[i * 32 + lane];
-      const long long den = 2 * (u - i);
-      long long w = num / den;
-      if ((num % den != 0) && (num < 0)) --w; // floor division
+      const int i = s[q * 32 + lane];
+      const int num = u * u - i * i + g[u * 32 + lane] - g[i * 32 + lane];
+      const int den = 2 * (u - i);
+      int w = num / den;
+      if ((num - w * den != 0) && (num < 0)) --w; // floor division
       w += 1;
-      if (w < (long long)n) {
+      if (w < (int)n) {
         ++q;
         s[q * 32 + lane] = (uint16_t)u;
         t[q * 32 + lane] = (uint16_t)w;
@@ -259,7 +260,7 @@ __global__ void __launch_bounds__(32) edt_lines_kernel(const int32_t *in, void *
     }
   }
   for (int u = (int)n - 1; u >= 0; --u) {
-    const long long v = f(u, s[q * 32 + lane]);
+    const int v = f(u, s[q * 32 + lane]);
     if (live) {
       if (TO_FLOAT)
         reinterpret_cast<float *>(out_v)[base + (uint64_t)u * stride] =

@@ -7,20 +7,25 @@
 // kernel therefore runs ONE CTA PER SM with specialised warps and no CTA-wide barrier, atomic or
 // fence anywhere in the loop:
 //
-//   compute warps   one sample per group of T <= 32 lanes, every lane TWO consecutive waypoints
-//                   per step in packed fp32x2 arithmetic (waypoint_cost2, as cost_kernel_pk);
-//                   they cost iteration e on the CURRENT trajectory speculatively, up to `depth`
-//                   iterations ahead of the last decided one, and leave per-waypoint sums in a
-//                   shared-memory ring;
-//   fold warp       lane s folds sample s's per-waypoint sums in the canonical order (left fold,
+//   compute warps   one WAYPOINT per lane (up to 64 lanes = two warps per sample), TWO
+//                   ITERATIONS per pass: the halves of every packed fp32x2 register are the same
+//                   waypoint under the noise of iteration e and of e + 1 (fma.rn.f32x2, the
+//                   arithmetic of cost_kernel_pk); they cost the CURRENT trajectory
+//                   speculatively, up to `depth` iterations ahead of the last decided one, and
+//                   leave per-waypoint sums in a shared-memory ring;
+//   fold warps (2)  lane s folds sample s's per-waypoint sums in the canonical order (left fold,
 //                   waypoint 0 first: oracle ORC_SUM_WAYPOINT), takes the CTA's minimum key and
-//                   publishes it with ONE 8-byte store into the CTA's own slot of the
+//                   publishes it with ONE 8-byte atomic exchange into the CTA's own slot of the
 //                   iteration's entry ring in global memory;
 //   collect warp    reads every CTA's slot of the oldest undecided iteration (coalesced 8-byte
-//                   loads, no atomics), merges across GPUs through NVLink peer mailboxes (one
-//                   8-byte store per peer), applies the keep-best (generate_trajectories.cu:225-241,
-//                   D5/D6 fixed) to the other trajectory buffer and bumps the version;
-//   noise warp      draws the Philox / Box-Muller noise vectors of later iterations into a ring.
+//                   loads, no atomics) -- on several GPUs its own rank's peer mailbox instead,
+//                   four iterations per poll -- applies the keep-best
+//                   (generate_trajectories.cu:225-241, D5/D6 fixed) to the other trajectory
+//                   buffer and bumps the version;
+//   send warp       (several GPUs, first CTA) merges the rank's CTAs and stores the rank's key
+//                   into every rank's mailbox over NVLink (one 8-byte reduction per peer),
+//                   running ahead of the collect warp so that round trips overlap;
+//   noise warps (3) draw the Philox / Box-Muller noise vectors of later iterations into a ring.
 //
 // Every published word carries its own validity: key = {score bits : 8-bit tag : 24-bit sample},
 // tag = (iteration / ring) mod 16 and (trajectory version) mod 16.  A reader polls until all
@@ -72,9 +77,13 @@ __device__ __forceinline__ unsigned long long ld_sys(const unsigned long long *p
   asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
   return v;
 }
-__device__ __forceinline__ void st_sys(unsigned long long *p, unsigned long long v) {
-  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-  asm volatile("fence.acq_rel.sys;" ::: "memory"); // push it out now
+// Remote publish without a return value: the slot is written by this sender only, so it knows
+// the slot's content `cur` and turns it into `v` with ONE reduction (performed at the target, a
+// peer's memory over NVLink).  An atomic exchange would work too, but its unused result
+// serialises the sender on the NVLink round trip (3.3 us per iteration measured): the next
+// exchange reuses the result register.
+__device__ __forceinline__ void xor_sys(unsigned long long *p, unsigned long long cur, unsigned long long v) {
+  asm volatile("red.relaxed.sys.global.xor.b64 [%0], %1;" ::"l"(p), "l"(cur ^ v) : "memory");
 }
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
   unsigned long long t;
@@ -233,17 +242,14 @@ __global__ void __launch_bounds__(kP2MaxThreads) plan_pipeline_kernel(const __gr
           leave = true;
           break;
         }
-        if (e < iters && e < dec + depth && snz[e % kP2Q] == e + 1) {
-          // a pass costs the same for one iteration as for two: when the next iteration may run
-          // too, wait for its noise rather than waste the hi halves
-          if (e + 1 < iters && e + 1 < dec + depth) {
-            if (snz[(e + 1) % kP2Q] == e + 2) {
-              two = true;
-              break;
-            }
-          } else {
-            break;
-          }
+        // a pass costs the same for one iteration as for two: unless only one is left (or the
+        // depth is 1), wait until BOTH may run -- starting a single pass the moment the window
+        // opens by one would keep the pipeline full of half-empty passes
+        const bool pair = depth >= 2 && e + 1 < iters;
+        if (e < iters && e + (pair ? 1u : 0u) < dec + depth && snz[e % kP2Q] == e + 1 &&
+            (!pair || snz[(e + 1) % kP2Q] == e + 2)) {
+          two = pair;
+          break;
         }
         __nanosleep(32); // a spinning warp would take issue slots from the working ones
       }
@@ -430,50 +436,32 @@ __global__ void __launch_bounds__(kP2MaxThreads) plan_pipeline_kernel(const __gr
     bool dead = false;
     const unsigned long long t_start = globaltimer_ns();
     long long t_poll = 0, t_decide = 0, tk0 = clock64();
-    for (uint32_t i = 0; i < iters && !dead; ++i) {
-      const uint32_t want = p2_tag(i, ver);
-      const unsigned long long *row = Q.entries + ((size_t)(i % kP2Ring) * k + c) * nctas;
-      unsigned long long mn;
-      for (uint32_t spins = 1;; ++spins) { // every CTA's key of (i, ver): coalesced polls, no atomics
-        bool ok = true;
-        mn = kKeyNone;
-        for (uint32_t u0 = 0; u0 < nctas; u0 += 32 * 8) { // up to 8 loads in flight per lane
-          unsigned long long v[8];
-#pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            const uint32_t idx = u0 + u * 32 + lane;
-            v[u] = idx < nctas ? ld_gpu(row + idx) : p2_pack(kKeyNone, want);
-          }
-#pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            ok = ok && p2_tag_of(v[u]) == want;
-            const unsigned long long sv = p2_strip(v[u]);
-            mn = sv < mn ? sv : mn;
-          }
-        }
-        if (__all_sync(kFull, ok)) break;
-        if ((spins & 0xFFFu) == 0 &&
-            (*(volatile unsigned int *)Q.error != 0 || globaltimer_ns() - t_start > Q.timeout_ns)) {
-          dead = true;
-          break;
-        }
-      }
-      if (dead) break;
-      mn = warp_min_u64(mn);
-      if (Q.nranks > 1) {
-        // rank keys through the peers' mailboxes: the climber's first CTA stores this rank's key
-        // into every rank's mailbox (one 8-byte store per peer over NVLink, the word carries its
-        // own tag), every CTA polls its own rank's mailbox -- local memory
-        const size_t slot = ((size_t)(i % kP2Ring) * k + c) * 8;
-        if (blockIdx.x == 0 && lane < Q.nranks) st_sys(Q.mailbox[lane] + slot + Q.rank, p2_pack(mn, want));
-        for (uint32_t spins = 1;; ++spins) {
-          unsigned long long v = 0;
+    uint32_t i = 0;
+    while (i < iters && !dead) {
+      // ---- the merged keys of iteration i (and, on several ranks, of up to three more)
+      unsigned long long keys4[4] = {kKeyNone, kKeyNone, kKeyNone, kKeyNone};
+      uint32_t ready = 0;
+      if (Q.nranks <= 1) {
+        const uint32_t want = p2_tag(i, ver);
+        const unsigned long long *row = Q.entries + ((size_t)(i % kP2Ring) * k + c) * nctas;
+        unsigned long long mn = kKeyNone;
+        for (uint32_t spins = 1;; ++spins) { // every CTA's key of (i, ver): coalesced polls, no atomics
           bool ok = true;
-          if (lane < Q.nranks) {
-            v = ld_sys(Q.mailbox[Q.rank] + slot + lane);
-            ok = p2_tag_of(v) == want;
+          mn = kKeyNone;
+          for (uint32_t u0 = 0; u0 < nctas; u0 += 32 * 8) { // up to 8 loads in flight per lane
+            unsigned long long v[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+              const uint32_t idx = u0 + u * 32 + lane;
+              v[u] = idx < nctas ? ld_gpu(row + idx) : p2_pack(kKeyNone, want);
+            }
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+              ok = ok && p2_tag_of(v[u]) == want;
+              const unsigned long long sv = p2_strip(v[u]);
+              mn = sv < mn ? sv : mn;
+            }
           }
-          mn = lane < Q.nranks ? p2_strip(v) : kKeyNone;
           if (__all_sync(kFull, ok)) break;
           if ((spins & 0xFFFu) == 0 &&
               (*(volatile unsigned int *)Q.error != 0 || globaltimer_ns() - t_start > Q.timeout_ns)) {
@@ -482,49 +470,92 @@ __global__ void __launch_bounds__(kP2MaxThreads) plan_pipeline_kernel(const __gr
           }
         }
         if (dead) break;
-        mn = warp_min_u64(mn);
+        keys4[0] = warp_min_u64(mn);
+        ready = 1;
+      } else {
+        // several ranks: the send warp of the climber's first CTA has merged this rank's CTAs
+        // and stored the rank's key into every rank's mailbox (the own one included); every CTA
+        // polls its own rank's mailbox -- local memory.  One round looks at FOUR iterations
+        // (lane group g = lane / 8: iteration i + g, one lane per rank), so the collect warp is
+        // not limited to one iteration per poll round trip.
+        const uint32_t g = lane >> 3, rl = lane & 7u;
+        for (uint32_t spins = 1;; ++spins) {
+          const uint32_t it = i + g;
+          const uint32_t want = p2_tag(it, ver);
+          unsigned long long v = p2_pack(kKeyNone, want);
+          if (it < iters && rl < Q.nranks)
+            v = ld_sys(Q.mailbox[Q.rank] + ((size_t)(it % kP2Ring) * k + c) * 8 + rl);
+          const uint32_t okb = __ballot_sync(kFull, it < iters && p2_tag_of(v) == want);
+          unsigned long long mn = p2_strip(v);
+#pragma unroll
+          for (int off = 4; off >= 1; off >>= 1) { // minimum inside the group of 8 lanes
+            const unsigned long long o = __shfl_xor_sync(kFull, mn, off);
+            mn = o < mn ? o : mn;
+          }
+          while (ready < 4 && ((okb >> (8 * ready)) & 0xFFu) == 0xFFu) ++ready; // consecutive ones
+          if (ready) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) keys4[q] = __shfl_sync(kFull, mn, 8 * q);
+            break;
+          }
+          if ((spins & 0xFFFu) == 0 &&
+              (*(volatile unsigned int *)Q.error != 0 || globaltimer_ns() - t_start > Q.timeout_ns)) {
+            dead = true;
+            break;
+          }
+        }
+        if (dead) break;
       }
       const long long tk1 = clock64();
       t_poll += tk1 - tk0;
-      const bool kstamp = Q.stats && blockIdx.x == 0 && c == 0 && lane == 0 && i < 256;
-      if (kstamp) Q.stats[8 + i * 8 + 4] = (unsigned long long)tk1; // every CTA's key seen
-      const uint32_t hi = (uint32_t)(mn >> 32);
-      if (hi < cur_hi) { // keep-best (generate_trajectories.cu:225-241, D5/D6 fixed)
-        cur_hi = hi;
-        ++accepts;
-        const uint32_t win = (uint32_t)mn & 0xFFFFFFu;
-        if (lane < 3) {
-          float a = 0.0f, b = 0.0f;
-          if (P.noise_mode == NOISE_PHILOX) {
-            dm::noise_pair(P.seed_lo, P.seed_hi, P.sigma, i, c, win, 0, lane, &a, &b);
-          } else if (P.noise_mode == NOISE_EXTERNAL) {
-            const float *pn = Q.noise_base + (size_t)i * Q.noise_iter_stride +
-                              ((size_t)c * P.noise_m + (size_t)(win - P.noise_t0)) * D;
-            a = 2 * lane < D ? __ldg(pn + 2 * lane) : 0.0f;
-            b = 2 * lane + 1 < D ? __ldg(pn + 2 * lane + 1) : 0.0f;
+      // ---- decide them in order; an accepted update voids the later ones (their version)
+      for (uint32_t q = 0; q < ready; ++q, ++i) {
+        const unsigned long long mn = keys4[q];
+        const bool kstamp = Q.stats && blockIdx.x == 0 && c == 0 && lane == 0 && i < 256;
+        if (kstamp) Q.stats[8 + i * 8 + 4] = (unsigned long long)tk1; // every key seen
+        const uint32_t hi = (uint32_t)(mn >> 32);
+        const bool accept = hi < cur_hi; // keep-best (generate_trajectories.cu:225-241, D5/D6 fixed)
+        if (accept) {
+          cur_hi = hi;
+          ++accepts;
+          const uint32_t win = (uint32_t)mn & 0xFFFFFFu;
+          if (lane < 3) {
+            float a = 0.0f, b = 0.0f;
+            if (P.noise_mode == NOISE_PHILOX) {
+              dm::noise_pair(P.seed_lo, P.seed_hi, P.sigma, i, c, win, 0, lane, &a, &b);
+            } else if (P.noise_mode == NOISE_EXTERNAL) {
+              const float *pn = Q.noise_base + (size_t)i * Q.noise_iter_stride +
+                                ((size_t)c * P.noise_m + (size_t)(win - P.noise_t0)) * D;
+              a = 2 * lane < D ? __ldg(pn + 2 * lane) : 0.0f;
+              b = 2 * lane + 1 < D ? __ldg(pn + 2 * lane + 1) : 0.0f;
+            }
+            if (2 * lane < D) swin[2 * lane] = a;
+            if (2 * lane + 1 < D) swin[2 * lane + 1] = b;
           }
-          if (2 * lane < D) swin[2 * lane] = a;
-          if (2 * lane + 1 < D) swin[2 * lane + 1] = b;
-        }
-        __syncwarp();
-        const float *src = sbase + (ver & 1u) * D * NP;
-        float *dst = sbase + ((ver + 1) & 1u) * D * NP;
-        for (uint32_t idx = lane; idx < (uint32_t)D * NP; idx += 32) dst[idx] = dm::add_(src[idx], swin[idx / NP]);
-        ++ver;
-        __syncwarp();
-        __threadfence_block();
-        if (lane == 0) {
-          S->base = i + 1;
+          __syncwarp();
+          const float *src = sbase + (ver & 1u) * D * NP;
+          float *dst = sbase + ((ver + 1) & 1u) * D * NP;
+          for (uint32_t idx = lane; idx < (uint32_t)D * NP; idx += 32) dst[idx] = dm::add_(src[idx], swin[idx / NP]);
+          ++ver;
+          __syncwarp();
           __threadfence_block();
-          S->ver = ver;
+          if (lane == 0) {
+            S->base = i + 1;
+            __threadfence_block();
+            S->ver = ver;
+            S->decided = i + 1;
+          }
+        } else if (lane == 0) {
           S->decided = i + 1;
         }
-      } else if (lane == 0) {
-        S->decided = i + 1;
+        if (kstamp) Q.stats[8 + i * 8 + 5] = (unsigned long long)clock64(); // decided
+        if (accept) { // the keys fetched for later iterations belong to the old version
+          ++i;
+          break;
+        }
       }
       tk0 = clock64();
       t_decide += tk0 - tk1;
-      if (kstamp) Q.stats[8 + i * 8 + 5] = (unsigned long long)tk0; // decided
     }
     if (Q.stats && blockIdx.x == 0 && c == 0 && lane == 0) {
       Q.stats[6] = (unsigned long long)t_poll;
@@ -547,11 +578,63 @@ __global__ void __launch_bounds__(kP2MaxThreads) plan_pipeline_kernel(const __gr
         if (Q.stats && c == 0) Q.stats[0] = accepts;
       }
     }
+  } else if (warp == CW + kP2FoldWarps + 1) {
+    // ================================================================ send warp (several ranks)
+    // Runs ahead of the collect warp: as soon as every CTA of this rank has published its key of
+    // (a, ver), the rank's key goes to every rank's mailbox -- one 8-byte word per peer over
+    // NVLink, carrying its own tag -- without waiting for the answers to earlier iterations, so
+    // the NVLink round trips of successive iterations overlap.
+    if (Q.nranks > 1 && blockIdx.x == 0) {
+      __shared__ unsigned long long slast[kP2Ring]; // what this rank's slot of ring index r holds
+      for (uint32_t r = lane; r < (uint32_t)kP2Ring; r += 32) slast[r] = kKeyNone; // as armed
+      __syncwarp();
+      uint32_t my_ver = 0, a = 0;
+      for (;;) {
+        const uint32_t v = ldv(&S->ver);
+        if (v != my_ver) {
+          __threadfence_block();
+          a = ldv(&S->base);
+          my_ver = v;
+        }
+        if (ldv(&S->decided) >= iters || ldv(&S->abort)) break;
+        if (a >= iters) {
+          __nanosleep(200);
+          continue;
+        }
+        const uint32_t want = p2_tag(a, my_ver);
+        const unsigned long long *row = Q.entries + ((size_t)(a % kP2Ring) * k + c) * nctas;
+        bool ok = true;
+        unsigned long long mn = kKeyNone;
+        for (uint32_t u0 = 0; u0 < nctas; u0 += 32 * 8) {
+          unsigned long long w8[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const uint32_t idx = u0 + u * 32 + lane;
+            w8[u] = idx < nctas ? ld_gpu(row + idx) : p2_pack(kKeyNone, want);
+          }
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            ok = ok && p2_tag_of(w8[u]) == want;
+            const unsigned long long sv = p2_strip(w8[u]);
+            mn = sv < mn ? sv : mn;
+          }
+        }
+        if (!__all_sync(kFull, ok)) continue;
+        mn = warp_min_u64(mn);
+        const unsigned long long word = p2_pack(mn, want), cur = slast[a % kP2Ring];
+        if (lane < Q.nranks)
+          xor_sys(Q.mailbox[lane] + ((size_t)(a % kP2Ring) * k + c) * 8 + Q.rank, cur, word);
+        __syncwarp();
+        if (lane == 0) slast[a % kP2Ring] = word;
+        __syncwarp();
+        ++a;
+      }
+    }
   } else {
     // ================================================================ noise warp
     // one d-vector of noise per sample and iteration (generate_trajectories.cu:37-44), drawn up
     // to Q - 1 iterations ahead of the last decided one: one Box-Muller pair per lane
-    const uint32_t nw = warp - (CW + kP2FoldWarps + 1);
+    const uint32_t nw = warp - (CW + kP2FoldWarps + 2);
     for (uint32_t g = nw; g < iters; g += kP2NoiseWarps) {
       bool leave = false;
       while (g >= ldv(&S->decided) + kP2Q) {
