@@ -501,12 +501,15 @@ def measure_c3(w, dd: Dist, local_rank, steps, warmup):
     sampler = ClockSampler(local_rank)
     sampler.start()
     l0 = ctx.launch_count()
-    dev_ms, t0 = 0.0, time.perf_counter()
-    for _ in range(steps):
-        r = ctx.replan_dynamic(start, goal, init, h_clouds)  # H2D of the clouds + loop + D2H
-        dev_ms += r["elapsed_ms"]                             # CUDA events around the loop only
-    e2e_s = time.perf_counter() - t0
+    dev_ms = 0.0
+    for _ in range(steps):  # clouds resident in HBM (staged by the warm-up calls): CUDA events
+        r = ctx.replan_dynamic(start, goal, init, None, staged_shape=(iters, P))
+        dev_ms += r["elapsed_ms"]
     launches = ctx.launch_count() - l0
+    t0 = time.perf_counter()
+    for _ in range(steps):  # e2e: the clouds streamed in (per-cloud copies overlap the loop) + D2H
+        r = ctx.replan_dynamic(start, goal, init, h_clouds)
+    e2e_s = time.perf_counter() - t0
     clocks = sampler.stop()
     wps_step = m * n * iters
     ms_step = dev_ms / steps
@@ -516,7 +519,8 @@ def measure_c3(w, dd: Dist, local_rank, steps, warmup):
         "value": wps_step / (ms_step * 1e-3), "unit": UNIT, "ms_per_step": ms_step,
         "config": dict(config_of(w, 1), points_per_cloud=P,
                        l2="cloud of every iteration is new data (72 MB per step streamed from "
-                          "HBM); grid L2-resident by design"),
+                          "HBM; in the e2e leg from pinned host memory, copy of cloud i+1 "
+                          "overlapping the replan of cloud i); grid L2-resident by design"),
         "iterations_per_sec": iters / (ms_step * 1e-3),
         "grid_rebuilds_per_sec": iters / (ms_step * 1e-3),
         "points_per_sec": P * iters / (ms_step * 1e-3),

@@ -350,9 +350,15 @@ class Context:
                                            C.addressof(lp)))
         return tot.value, cnt.value, lp.value
 
-    def replan_dynamic(self, start, goal, init_traj, clouds):
-        start, goal, init_traj, clouds = _f32(start), _f32(goal), _f32(init_traj), _f32(clouds)
-        iters, npts = clouds.shape[0], clouds.shape[1]
+    def replan_dynamic(self, start, goal, init_traj, clouds, staged_shape=None):
+        """clouds [iters][P][3] host array; or None with staged_shape = (iters, P): reuse the
+        clouds the previous call left in device memory (no host-to-device copy)."""
+        start, goal, init_traj = _f32(start), _f32(goal), _f32(init_traj)
+        if clouds is None:
+            iters, npts = staged_shape
+        else:
+            clouds = _f32(clouds)
+            iters, npts = clouds.shape[0], clouds.shape[1]
         bt = np.empty((self.n, self.d), np.float32)
         bs, ms = C.c_float(), C.c_float()
         self._ck(self.L.doapp_replan_dynamic(self.h, _p(start), _p(goal), _p(init_traj), iters,

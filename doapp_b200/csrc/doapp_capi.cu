@@ -171,6 +171,13 @@ struct doapp_ctx {
   uint64_t replan_grid_generation = ~0ull;
   uint64_t replan_kernels = 0;
   int replan_end[3] = {0, 0, -1};
+  // doapp_replan_dynamic streams the clouds in on a second stream, one event per cloud, so the
+  // H2D copy of cloud i + 1 overlaps the rebuild + replan of cloud i
+  cudaStream_t copy_stream = nullptr;
+  std::vector<cudaEvent_t> cloud_events;
+  size_t cloud_staged = 0;        // elements of the clouds now in ctx->cloud
+  bool replan_ext_wait_ok = true; // external event waits can be captured into the replan graph
+  bool replan_waits = false;      // the cached replan graph carries the per-cloud waits
 
   ncclComm_t comm = nullptr;
   int rank = 0, nranks = 1;
@@ -1038,6 +1045,8 @@ void doapp_destroy(doapp_ctx *ctx) {
     if (ctx->peer_ready && r != ctx->peer_rank && ctx->peer_mbox[r]) cudaIpcCloseMemHandle(ctx->peer_mbox[r]);
   release(ctx->mailbox); release(ctx->presult); release(ctx->depth); release(ctx->fk_dev);
   for (cudaEvent_t e : ctx->prof_events) cudaEventDestroy(e);
+  for (cudaEvent_t e : ctx->cloud_events) cudaEventDestroy(e);
+  if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->ev1) cudaEventDestroy(ctx->ev1);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -1696,8 +1705,7 @@ doapp_status doapp_replan_dynamic(doapp_ctx *ctx, const float *start, const floa
                                   size_t num_points, float *best_traj, float *best_score,
                                   float *elapsed_ms) {
   if (!ctx) return DOAPP_INVALID_ARG;
-  if (!start || !init_traj || (!clouds && num_points && iters))
-    return fail(ctx, DOAPP_INVALID_ARG, "doapp_replan_dynamic: null argument");
+  if (!start || !init_traj) return fail(ctx, DOAPP_INVALID_ARG, "doapp_replan_dynamic: null argument");
   if (ctx->grid.kind != DOAPP_GRID_U8)
     return fail(ctx, DOAPP_NOT_READY, "doapp_replan_dynamic: needs a U8 grid");
   (void)goal;
@@ -1706,12 +1714,31 @@ doapp_status doapp_replan_dynamic(doapp_ctx *ctx, const float *start, const floa
   ST(upload_traj(ctx, init_traj, true));
   ST(upload_start(ctx, start));
   const size_t cloud_elems = (size_t)iters * num_points * 3;
+  if (!clouds && cloud_elems && ctx->cloud_staged != cloud_elems)
+    return fail(ctx, DOAPP_NOT_READY,
+                "doapp_replan_dynamic: clouds == NULL reuses the clouds of the previous call, "
+                "which staged %zu floats, not %zu", ctx->cloud_staged, cloud_elems);
   ST(ensure(ctx, ctx->cloud, cloud_elems));
-  if (cloud_elems)
-    CU(cudaMemcpyAsync(ctx->cloud.p, clouds, cloud_elems * sizeof(float), cudaMemcpyHostToDevice,
-                       ctx->stream));
-  CU(cudaStreamSynchronize(ctx->stream));
+  if (!ctx->copy_stream) CU(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+  while (ctx->cloud_events.size() < iters) {
+    cudaEvent_t e = nullptr;
+    CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    ctx->cloud_events.push_back(e);
+  }
+  CU(cudaStreamSynchronize(ctx->stream)); // inputs staged; the previous loop no longer reads the clouds
+  if (clouds && cloud_elems) {
+    // one copy + one event per cloud on the copy stream: iteration it waits for cloud it only
+    for (uint32_t it = 0; it < iters; ++it) {
+      const size_t off = (size_t)it * num_points * 3;
+      CU(cudaMemcpyAsync(ctx->cloud.p + off, clouds + off, num_points * 3 * sizeof(float),
+                         cudaMemcpyHostToDevice, ctx->copy_stream));
+      CU(cudaEventRecord(ctx->cloud_events[it], ctx->copy_stream));
+    }
+    ctx->cloud_staged = cloud_elems;
+    if (!ctx->replan_ext_wait_ok) CU(cudaStreamSynchronize(ctx->copy_stream));
+  }
   CU(cudaEventRecord(ctx->ev0, ctx->stream));
+  bool capturing = false;
   const size_t k = c.num_climbers;
   // the whole loop (per iteration: clear + scatter + re-score + cost pass) as one sequence;
   // captured once into a CUDA graph and replayed while shapes and buffers stay the same
@@ -1721,6 +1748,9 @@ doapp_status doapp_replan_dynamic(doapp_ctx *ctx, const float *start, const floa
     CU(cudaMemsetAsync(ctx->keys.p, 0xFF, sizeof(unsigned long long) * 3 * k, ctx->stream));
     for (uint32_t it = 0; it < iters; ++it) {
       CU(cudaMemsetAsync(ctx->grid_cells.p, 0, ctx->grid_bytes, ctx->stream));
+      if (ctx->replan_ext_wait_ok && num_points)
+        CU(cudaStreamWaitEvent(ctx->stream, ctx->cloud_events[it],
+                               capturing ? cudaEventWaitExternal : cudaEventWaitDefault));
       ScatterParams sp{};
       sp.xyz = ctx->cloud.p + (size_t)it * num_points * 3;
       sp.num_points = num_points;
@@ -1778,25 +1808,36 @@ doapp_status doapp_replan_dynamic(doapp_ctx *ctx, const float *start, const floa
     const bool hit = ctx->replan_exec && ctx->replan_iters == iters &&
                      ctx->replan_points == num_points && ctx->replan_cloud == ctx->cloud.p &&
                      ctx->replan_cells == ctx->grid_cells.p &&
-                     ctx->replan_grid_generation == ctx->grid_generation;
+                     ctx->replan_grid_generation == ctx->grid_generation &&
+                     ctx->replan_waits == ctx->replan_ext_wait_ok;
     if (!hit) {
       if (ctx->replan_exec) cudaGraphExecDestroy(ctx->replan_exec);
       ctx->replan_exec = nullptr;
-      cudaGraph_t graph = nullptr;
-      CU(cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal));
       uint64_t nk = 0;
-      doapp_status st = enqueue(&nk);
-      cudaError_t ce = cudaStreamEndCapture(ctx->stream, &graph);
-      if (st != DOAPP_OK) {
+      for (int attempt = 0; attempt < 2 && !ctx->replan_exec; ++attempt) {
+        cudaGraph_t graph = nullptr;
+        CU(cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal));
+        capturing = true;
+        doapp_status st = enqueue(&nk);
+        capturing = false;
+        cudaError_t ce = cudaStreamEndCapture(ctx->stream, &graph);
+        if (st == DOAPP_OK && ce == cudaSuccess) {
+          ce = cudaGraphInstantiate(&ctx->replan_exec, graph, 0);
+          if (ce != cudaSuccess) ctx->replan_exec = nullptr;
+        }
         if (graph) cudaGraphDestroy(graph);
-        return st;
+        if (ctx->replan_exec) break;
+        if (attempt == 0 && ctx->replan_ext_wait_ok) {
+          // external event waits not capturable here: wait for the copies on the host instead
+          cudaGetLastError();
+          ctx->replan_ext_wait_ok = false;
+          CU(cudaStreamSynchronize(ctx->copy_stream));
+          continue;
+        }
+        if (st != DOAPP_OK) return st;
+        return fail(ctx, DOAPP_CUDA_ERROR, "replan graph: %s", cudaGetErrorString(ce));
       }
-      if (ce != cudaSuccess)
-        return fail(ctx, DOAPP_CUDA_ERROR, "cudaStreamEndCapture: %s", cudaGetErrorString(ce));
-      ce = cudaGraphInstantiate(&ctx->replan_exec, graph, 0);
-      cudaGraphDestroy(graph);
-      if (ce != cudaSuccess)
-        return fail(ctx, DOAPP_CUDA_ERROR, "cudaGraphInstantiate: %s", cudaGetErrorString(ce));
+      ctx->replan_waits = ctx->replan_ext_wait_ok;
       ctx->replan_iters = iters;
       ctx->replan_points = num_points;
       ctx->replan_cloud = ctx->cloud.p;

@@ -295,8 +295,11 @@ DOAPP_API doapp_status doapp_plan_wait(doapp_ctx *ctx, float *best_traj, float *
 DOAPP_API doapp_status doapp_plan_state(doapp_ctx *ctx, float *trajectories, float *scores,
                                         int32_t *rounded, uint8_t *found_better);
 /* Dynamic-obstacle replan (BASELINE config 3): every iteration first rebuilds
- * the grid from clouds[it] ([iters][num_points][3], device-staged once), then
- * runs one planner iteration. */
+ * the grid from clouds[it] ([iters][num_points][3]), then runs one planner
+ * iteration.  The clouds are copied in one by one on a second stream; iteration
+ * it waits for cloud it only, so the copy of the next cloud overlaps the replan.
+ * clouds == NULL reuses the clouds the previous call left in device memory
+ * (same iters and num_points).  elapsed_ms: CUDA events around the loop. */
 DOAPP_API doapp_status doapp_replan_dynamic(doapp_ctx *ctx, const float *start, const float *goal,
                                             const float *init_traj, uint32_t iters,
                                             const float *clouds, size_t num_points,
