@@ -28,7 +28,7 @@ PEER_HANDLE_BYTES = 64
 ABI_SYMBOLS = [
     "doapp_config_init", "doapp_version", "doapp_status_str", "doapp_create", "doapp_destroy",
     "doapp_last_error", "doapp_grid_alloc", "doapp_grid_upload", "doapp_grid_download",
-    "doapp_grid_from_msg", "doapp_grid_from_depth", "doapp_grid_distance_field", "doapp_grid_scatter", "doapp_grid_scatter_dev", "doapp_grid_lookup",
+    "doapp_grid_from_msg", "doapp_grid_from_depth", "doapp_grid_distance_field", "doapp_distance_field_noalloc", "doapp_grid_scatter", "doapp_grid_scatter_dev", "doapp_grid_lookup",
     "doapp_set_limits", "doapp_fk_model_rexarm", "doapp_set_fk_model", "doapp_noise_generate", "doapp_cost_eval", "doapp_stage_inputs",
     "doapp_cost_eval_dev", "doapp_read_results", "doapp_plan_lerp", "doapp_plan",
     "doapp_plan_async", "doapp_plan_wait", "doapp_plan_state", "doapp_replan_dynamic",
@@ -127,6 +127,8 @@ def load_library(path: str | None = None) -> C.CDLL:
     L.doapp_grid_from_depth.argtypes = [vp, vp, C.c_uint32, C.c_uint32, C.c_uint32, vp, vp, C.c_double,
                                         C.c_int8, C.c_int, vp]
     L.doapp_grid_distance_field.argtypes = [vp]
+    L.doapp_distance_field_noalloc.argtypes = [vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_double,
+                                               vp, vp]
     L.doapp_peer_export.argtypes = [vp, vp]
     L.doapp_peer_import.argtypes = [vp, vp, C.c_int32, C.c_int32]
     L.doapp_comm_unique_id.argtypes = [vp]
@@ -381,6 +383,17 @@ class Context:
     def grid_distance_field(self):
         """U8 occupancy -> F32 exact Euclidean distance field (same frame and dimensions)."""
         self._ck(self.L.doapp_grid_distance_field(self.h))
+
+    @staticmethod
+    def distance_field_noalloc(occ_dev_ptr: int, nx: int, ny: int, nz: int, resolution: float,
+                               dist_dev_ptr: int, stream: int = 0):
+        """doapp_distance_field_noalloc: device pointers in and out, static scratch inside the
+        library, no allocation; enqueues on `stream` (a cudaStream_t value, 0 = default)."""
+        L = load_library()
+        st = L.doapp_distance_field_noalloc(C.c_void_p(occ_dev_ptr), nx, ny, nz, float(resolution),
+                                            C.c_void_p(dist_dev_ptr), C.c_void_p(stream or None))
+        if st != OK:
+            raise DoappError(st, L.doapp_last_error(None).decode())
 
     def probe_gather(self, array_bytes: int, cell_bytes: int = 1) -> float:
         """Random single-cell loads per second from a scratch array (roofline denominator)."""

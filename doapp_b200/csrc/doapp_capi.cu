@@ -1302,6 +1302,60 @@ doapp_status doapp_grid_distance_field(doapp_ctx *ctx) {
   return DOAPP_OK;
 }
 
+// ---- distance field with NO allocation (no
+// counterpart in the reference).  The two int32 scratch planes of the distance transform live
+// in a file-scope device array instead of cudaMalloc'd buffers: every GPU that loads the
+// library holds DOAPP_NOALLOC_MAX_CELLS * 8 bytes (16 MiB) until the process exits.  In host
+// code `g_edt_scratch` is only a stand-in for the symbol; the device address is looked up once
+// per device with cudaGetSymbolAddress (that device current) and handed to the kernels.
+} // extern "C"
+static __device__ __align__(256) int32_t g_edt_scratch[2 * DOAPP_NOALLOC_MAX_CELLS];
+namespace {
+constexpr int kNoallocMaxDevices = 64;
+std::mutex g_noalloc_mu;
+int32_t *g_noalloc_ptr[kNoallocMaxDevices] = {};
+} // namespace
+extern "C" {
+
+doapp_status doapp_distance_field_noalloc(const uint8_t *occ_dev, uint32_t nx, uint32_t ny,
+                                          uint32_t nz, double resolution, float *dist_dev,
+                                          void *stream) {
+  doapp_ctx *ctx = nullptr; // errors go to the thread-local slot read by doapp_last_error(NULL)
+  if (!occ_dev || !dist_dev)
+    return fail(nullptr, DOAPP_INVALID_ARG, "doapp_distance_field_noalloc: null device pointer");
+  if (nx == 0 || ny == 0 || nz == 0 || !(resolution > 0.0))
+    return fail(nullptr, DOAPP_INVALID_ARG,
+                "doapp_distance_field_noalloc: empty grid or resolution <= 0");
+  if (nx > kEdtMaxDim || ny > kEdtMaxDim || nz > kEdtMaxDim)
+    return fail(nullptr, DOAPP_INVALID_ARG, "doapp_distance_field_noalloc: dimensions above %u",
+                kEdtMaxDim);
+  const uint64_t cells = (uint64_t)nx * ny * nz;
+  if (cells > (uint64_t)DOAPP_NOALLOC_MAX_CELLS)
+    return fail(nullptr, DOAPP_INVALID_ARG,
+                "doapp_distance_field_noalloc: %llu cells exceed the static scratch of %llu cells "
+                "(DOAPP_NOALLOC_MAX_CELLS); use doapp_grid_distance_field for larger grids",
+                (unsigned long long)cells, (unsigned long long)DOAPP_NOALLOC_MAX_CELLS);
+  int dev = -1;
+  CU(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kNoallocMaxDevices)
+    return fail(nullptr, DOAPP_INVALID_ARG, "doapp_distance_field_noalloc: device %d", dev);
+  int32_t *scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ptr[dev]) { // once per device, with that device current
+      void *p = nullptr;
+      CU(cudaGetSymbolAddress(&p, g_edt_scratch));
+      g_noalloc_ptr[dev] = static_cast<int32_t *>(p);
+    }
+    scratch = g_noalloc_ptr[dev];
+  }
+  // rows -> tmp_a, lines along y -> tmp_b, lines along z -> dist: every cell of both planes is
+  // written before it is read, so nothing has to start at zero
+  CU(launch_distance_field(occ_dev, nx, ny, nz, (float)resolution, scratch,
+                           scratch + DOAPP_NOALLOC_MAX_CELLS, dist_dev, (cudaStream_t)stream));
+  return DOAPP_OK;
+}
+
 doapp_status doapp_grid_lookup(doapp_ctx *ctx, const float *xyz, size_t num_points,
                                int64_t *cell_index, uint8_t *collides) {
   if (!ctx) return DOAPP_INVALID_ARG;

@@ -189,6 +189,29 @@ DOAPP_API doapp_status doapp_grid_from_depth(doapp_ctx *ctx, const uint16_t *dep
  * the reference's `distance <= collision_distance` (generate_trajectories.cu:389,412).
  * Every dimension must be <= 768. */
 DOAPP_API doapp_status doapp_grid_distance_field(doapp_ctx *ctx);
+/* Occupancy -> exact Euclidean distance field WITHOUT any allocation.  No counterpart in the
+ * reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same three launches and the same bits as doapp_grid_distance_field, but the transform's
+ * scratch (two int32 planes) is a static device array inside the library, so the entry point
+ * calls no cudaMalloc / cudaFree and needs no doapp_ctx.  Every GPU that loads the library
+ * holds DOAPP_NOALLOC_MAX_CELLS * 8 bytes = 16 MiB for it until the process exits.
+ *   occ_dev   DEVICE pointer, nx*ny*nz uint8 occupancy (non-zero = occupied), index
+ *             ix + nx*iy + nx*ny*iz, on the CURRENT device
+ *   dist_dev  DEVICE pointer, nx*ny*nz fp32: distance to the nearest occupied voxel centre in
+ *             metres (voxels * resolution), +inf for an empty grid
+ *   stream    a cudaStream_t (NULL = the default stream); the call only enqueues, the caller
+ *             synchronises
+ * Grids above DOAPP_NOALLOC_MAX_CELLS cells (128^3) or 768 cells per edge are rejected with
+ * DOAPP_INVALID_ARG and a message in doapp_last_error(NULL).  ALL calls on a device share the
+ * one scratch array: it keeps the last call's contents (harmless: every cell is written before
+ * it is read), and two calls that overlap on the GPU (different streams) RACE -- serialise
+ * them.  The first call on a device resolves the array's address (cudaGetSymbolAddress): make
+ * it once outside any stream capture. */
+#define DOAPP_NOALLOC_MAX_CELLS (128ull * 128ull * 128ull)
+DOAPP_API doapp_status doapp_distance_field_noalloc(const uint8_t *occ_dev, uint32_t nx,
+                                                    uint32_t ny, uint32_t nz, double resolution,
+                                                    float *dist_dev, void *stream);
 /* CPUDistanceGrid::operator() / OccupancyGrid::get(double...) on a batch of
  * points: writes the flat cell index (-1 if outside) and the collision
  * predicate for each point.  Debug / parity helper. */
