@@ -272,6 +272,75 @@ __global__ void __launch_bounds__(32) edt_lines_kernel(const int32_t *in, void *
   }
 }
 
+// Lines of up to kEdtBruteMaxN voxels: the lower envelope by exhaustive minimum instead of the
+// sequential scan.  out[u] = min_i (u - i)^2 + g[i] = u^2 + min_i (h[i] - 2 u i) with
+// h[i] = g[i] + i^2: ONE integer multiply-add and one minimum per (u, i) pair, no data-dependent
+// control flow, no division, every lane busy -- n^2 pairs per line, which at n = 128 is far
+// cheaper than a 128-step dependent scan whose every step waits on shared-memory round trips
+// (measured: 76 + 110 us per 128^3 field with the scan).  Same integers, hence the same bits.
+// A CTA owns 32 consecutive x (coalesced tile loads / stores, as the scan kernel) and the whole
+// line length; warp w takes the lines w, w + 8, ...; lane l the outputs l, l + 32, ...
+constexpr uint32_t kEdtBruteMaxN = 256;
+template <bool TO_FLOAT>
+__global__ void __launch_bounds__(256) edt_lines_bf_kernel(const int32_t *in, void *out_v, uint32_t nx,
+                                                           uint32_t n, uint64_t stride,
+                                                           uint64_t line_stride, float res) {
+  extern __shared__ __align__(16) unsigned char edt_smem[];
+  int32_t *h = reinterpret_cast<int32_t *>(edt_smem); // [n][33]
+  const uint32_t x0 = blockIdx.x * 32, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint64_t base = (uint64_t)blockIdx.y * line_stride + x0;
+  for (uint32_t idx = threadIdx.x; idx < n * 32; idx += blockDim.x) {
+    const uint32_t u = idx >> 5, xl = idx & 31;
+    const int32_t g = x0 + xl < nx ? __ldg(in + base + xl + (uint64_t)u * stride) : kEdtInf;
+    h[u * 33 + xl] = g + (int32_t)(u * u);
+  }
+  __syncthreads();
+  for (uint32_t xl = warp; xl < 32 && x0 + xl < nx; xl += 8) {
+    int32_t best[8], m2u[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      best[k] = 0x7FFFFFFF;
+      m2u[k] = -2 * (int32_t)(lane + 32 * k);
+    }
+    const int32_t *col = h + xl;
+    if (n <= 128) { // four outputs per lane
+#pragma unroll 4
+      for (uint32_t i = 0; i < n; ++i) {
+        const int32_t hv = col[i * 33];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) best[k] = min(best[k], hv + m2u[k] * (int32_t)i);
+      }
+    } else { // eight
+#pragma unroll 2
+      for (uint32_t i = 0; i < n; ++i) {
+        const int32_t hv = col[i * 33];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) best[k] = min(best[k], hv + m2u[k] * (int32_t)i);
+      }
+    }
+    __syncwarp(); // every lane has read the whole column: it may now take the results
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const uint32_t u = lane + 32 * k;
+      if (u < n) {
+        const int32_t v = best[k] + (int32_t)(u * u);
+        h[u * 33 + xl] = v >= kEdtInf ? kEdtInf : v;
+      }
+    }
+  }
+  __syncthreads();
+  for (uint32_t idx = threadIdx.x; idx < n * 32; idx += blockDim.x) {
+    const uint32_t u = idx >> 5, xl = idx & 31;
+    if (x0 + xl >= nx) continue;
+    const int32_t v = h[u * 33 + xl];
+    if (TO_FLOAT)
+      reinterpret_cast<float *>(out_v)[base + xl + (uint64_t)u * stride] =
+          v >= kEdtInf ? INFINITY : dm::mul_(sqrtf((float)v), res);
+    else
+      reinterpret_cast<int32_t *>(out_v)[base + xl + (uint64_t)u * stride] = v;
+  }
+}
+
 // ------------------------------------------------------- depth -> voxel kernel
 // One thread per pixel of every camera: deprojection exactly as convert_sensor_msg_to_pcl
 // (mapping_node.cpp:110-135: x = (u - cx) * depth * (0.001 / fx), z = depth * 0.001f, depth 0
@@ -667,13 +736,22 @@ cudaError_t launch_distance_field(const uint8_t *occ, uint32_t nx, uint32_t ny, 
   if (sz > 48 * 1024 &&
       (e = cudaFuncSetAttribute(edt_lines_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sz)) != cudaSuccess)
     return e;
+  static const bool scan_only = getenv("DOAPP_EDT_SCAN") != nullptr; // tuning / parity: the scan kernels only
   // along y: lines of plane z, element stride nx
-  edt_lines_kernel<false><<<dim3((nx + 31) / 32, nz), 32, sy, st>>>(tmp_a, tmp_b, nx, ny, nx,
-                                                                  (uint64_t)nx * ny, res);
+  if (ny <= kEdtBruteMaxN && !scan_only)
+    edt_lines_bf_kernel<false><<<dim3((nx + 31) / 32, nz), 256, (size_t)ny * 33 * 4, st>>>(
+        tmp_a, tmp_b, nx, ny, nx, (uint64_t)nx * ny, res);
+  else
+    edt_lines_kernel<false><<<dim3((nx + 31) / 32, nz), 32, sy, st>>>(tmp_a, tmp_b, nx, ny, nx,
+                                                                    (uint64_t)nx * ny, res);
   if ((e = cudaGetLastError()) != cudaSuccess) return e;
   // along z: lines of row y, element stride nx * ny
-  edt_lines_kernel<true><<<dim3((nx + 31) / 32, ny), 32, sz, st>>>(tmp_b, out, nx, nz,
-                                                                 (uint64_t)nx * ny, nx, res);
+  if (nz <= kEdtBruteMaxN && !scan_only)
+    edt_lines_bf_kernel<true><<<dim3((nx + 31) / 32, ny), 256, (size_t)nz * 33 * 4, st>>>(
+        tmp_b, out, nx, nz, (uint64_t)nx * ny, nx, res);
+  else
+    edt_lines_kernel<true><<<dim3((nx + 31) / 32, ny), 32, sz, st>>>(tmp_b, out, nx, nz,
+                                                                   (uint64_t)nx * ny, nx, res);
   return cudaGetLastError();
 }
 

@@ -87,6 +87,7 @@ __global__ void __launch_bounds__(kPkThreads, DOAPP_PK_MINBLOCKS)
 
   float total = 0.0f, ltotal = 0.0f;
   int coll = 0;
+  bool bad = false;
   for (uint32_t w = w0; w < w_end; w += 2) {
     const bool has_hi = w + 1 < w_end;
     f2 x[D], vnew[D];
@@ -102,26 +103,10 @@ __global__ void __launch_bounds__(kPkThreads, DOAPP_PK_MINBLOCKS)
     const bool valid0 = f0 & fine1 & fine2, valid1 = f1 & f0 & fine1;
     fine2 = f0 & (P.fast_ok != 0);
     fine1 = f1 & (P.fast_ok != 0);
-    if (!(valid0 & valid1)) { // rare: redo the offending waypoint(s) with IEEE divides, full sin/cos
-#pragma unroll 1
-      for (int h = 0; h < 2; ++h) {
-        if (h == 0 ? valid0 : valid1) continue;
-        WpIn<D> in;
-#pragma unroll
-        for (int j = 0; j < D; ++j) { // the hi waypoint's priors are the (possibly redone) lo results
-          in.x[j] = h ? f2_hi(x[j]) : f2_lo(x[j]);
-          in.xprev[j] = h ? f2_lo(x[j]) : xprev[j];
-          in.vprev[j] = h ? f2_lo(vnew[j]) : vprev[j];
-        }
-        const WpOut<D> o = waypoint_cost_general<D, GM, true, LIM, FKM>(P, in);
-#pragma unroll
-        for (int j = 0; j < D; ++j)
-          vnew[j] = h ? f2_pack(f2_lo(vnew[j]), o.vnew[j]) : f2_pack(o.vnew[j], f2_hi(vnew[j]));
-        a2 = h ? f2_pack(f2_lo(a2), o.a2) : f2_pack(o.a2, f2_hi(a2));
-        l2 = h ? f2_pack(f2_lo(l2), o.l2) : f2_pack(o.l2, f2_hi(l2));
-        if (h) cw1 = o.coll; else cw0 = o.coll;
-      }
-    }
+    // an angle outside the ranges the straight-line arithmetic was verified for (never in
+    // practice): remember it; the run is redone below with the general path.  Keeping the
+    // out-of-line call out of this loop saves ~50 register moves per pair around the call site.
+    bad = bad | !(valid0 & valid1);
 #pragma unroll
     for (int j = 0; j < D; ++j) {
       xprev[j] = f2_hi(x[j]);
@@ -144,6 +129,46 @@ __global__ void __launch_bounds__(kPkThreads, DOAPP_PK_MINBLOCKS)
         float *sl = slim + ((size_t)swi * WS + w) * 32 + lane;
         sl[0] = f2_lo(l2);
         sl[32] = f2_hi(l2);
+      }
+    }
+  }
+  if (bad) {
+    // Rare path: the whole run again, every waypoint with IEEE divides and full-range sin / cos
+    // (waypoint_cost_general).  Wherever the straight-line results are valid they equal these
+    // bit for bit, so redoing all of the run gives what redoing the offending waypoints would.
+    WpIn<D> in;
+    if (!MP || w0 == 0) {
+#pragma unroll
+      for (int j = 0; j < D; ++j) in.xprev[j] = in.vprev[j] = __ldg(P.start + j);
+    } else {
+#pragma unroll
+      for (int j = 0; j < D; ++j) {
+        const float x1 = add_(sbase[j * NP + w0 - 1], eps[j]);
+        const float x2 = add_(sbase[j * NP + w0 - 2], eps[j]);
+        in.xprev[j] = x1;
+        in.vprev[j] = div_(sub_(x1, x2), P.dt_div.b);
+      }
+    }
+    total = 0.0f;
+    ltotal = 0.0f;
+    coll = 0;
+#pragma unroll 1
+    for (uint32_t w = w0; w < w_end; ++w) {
+#pragma unroll
+      for (int j = 0; j < D; ++j) in.x[j] = add_(sbase[j * NP + w], eps[j]);
+      const WpOut<D> o = waypoint_cost_general<D, GM, true, LIM, FKM>(P, in);
+      coll += o.coll;
+      if (!MP) {
+        total = add_(total, o.a2);
+        if (LIM) ltotal = add_(ltotal, o.l2);
+      } else {
+        spart[((size_t)swi * WS + w) * 32 + lane] = o.a2;
+        if (LIM) slim[((size_t)swi * WS + w) * 32 + lane] = o.l2;
+      }
+#pragma unroll
+      for (int j = 0; j < D; ++j) {
+        in.xprev[j] = in.x[j];
+        in.vprev[j] = o.vnew[j];
       }
     }
   }

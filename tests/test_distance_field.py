@@ -28,11 +28,21 @@ def test_oracle_scan_equals_brute_force(oracle_mod):
 @pytest.mark.gpu
 @pytest.mark.parametrize("shape,res,fill", [((64, 64, 64), 0.02, "box"), ((128, 128, 128), 0.01, "box"),
                                             ((40, 50, 70), 0.02, 0.001), ((33, 65, 97), 0.01, 0.05),
-                                            ((32, 32, 32), 0.02, 0.0), ((16, 16, 300), 0.01, 0.002)])
+                                            ((32, 32, 32), 0.02, 0.0), ((16, 16, 300), 0.01, 0.002),
+                                            # lines of 129..256 voxels (eight outputs per lane of the
+                                            # exhaustive kernel), and above 256 (the scan kernel)
+                                            ((200, 40, 33), 0.01, 0.003), ((256, 130, 20), 0.01, 0.0005),
+                                            ((300, 20, 21), 0.01, 0.004), ((20, 257, 31), 0.01, 0.004),
+                                            ((128, 128, 128), 0.01, "cloud")])
 def test_distance_field_parity(capi, oracle_mod, shape, res, fill):
     rng = np.random.default_rng(7)
     if fill == "box":
         g = synth.box_grid(shape[0], res)
+    elif fill == "cloud":  # BASELINE config 3's grid: a 300k-point cloud scattered into 128^3
+        o = oracle_mod.Oracle(k=1, m=1, n=1)
+        o.set_grid(np.zeros(shape, np.uint8), res)
+        o.scatter(synth.cloud(300_000, 0, size=shape[0] * res), 1, True)
+        g = o.cells.copy()
     else:
         g = (rng.random(shape) < fill).astype(np.uint8)
     ctx = capi.Context(k=1, m=1, n=1)
