@@ -274,48 +274,53 @@ __global__ void __launch_bounds__(32) edt_lines_kernel(const int32_t *in, void *
 
 // Lines of up to kEdtBruteMaxN voxels: the lower envelope by exhaustive minimum instead of the
 // sequential scan.  out[u] = min_i (u - i)^2 + g[i] = u^2 + min_i (h[i] - 2 u i) with
-// h[i] = g[i] + i^2: ONE integer multiply-add and one minimum per (u, i) pair, no data-dependent
-// control flow, no division, every lane busy -- n^2 pairs per line, which at n = 128 is far
-// cheaper than a 128-step dependent scan whose every step waits on shared-memory round trips
-// (measured: 76 + 110 us per 128^3 field with the scan).  Same integers, hence the same bits.
-// A CTA owns 32 consecutive x (coalesced tile loads / stores, as the scan kernel) and the whole
-// line length; warp w takes the lines w, w + 8, ...; lane l the outputs l, l + 32, ...
+// h[i] = g[i] + i^2: ONE multiply-add and one minimum per (u, i) pair, no data-dependent control
+// flow, no division, every lane busy -- n^2 pairs per line, which at n = 128 is far cheaper than
+// a 128-step dependent scan whose every step waits on shared-memory round trips (measured: 76 +
+// 110 us per 128^3 field with the scan, 45 + 48 us with this kernel in integer arithmetic).
+// The arithmetic is fp32 and EXACT: finite squared distances are integers below 3 * 768^2 < 2^24,
+// products 2 u i < 2^21, so every FFMA / FMNMX result is an integer fp32 represents exactly
+// (scripts/micro/pipe_model.cu: IMAD occupies the FMA pipe for 2 cycles per warp instruction on
+// sm_100a, FFMA for 1).  "No obstacle" (kEdtInf = 2^29) stays far above every finite value; its
+// sums round, so anything >= 2^28 is reported as kEdtInf.  Same integers as the scan, hence the
+// same bits.  A CTA owns 32 consecutive x (coalesced tile loads / stores, as the scan kernel) and
+// the whole line length; warp w takes the lines w, w + 8, ...; lane l the outputs l, l + 32, ...
 constexpr uint32_t kEdtBruteMaxN = 256;
 template <bool TO_FLOAT>
 __global__ void __launch_bounds__(256) edt_lines_bf_kernel(const int32_t *in, void *out_v, uint32_t nx,
                                                            uint32_t n, uint64_t stride,
                                                            uint64_t line_stride, float res) {
   extern __shared__ __align__(16) unsigned char edt_smem[];
-  int32_t *h = reinterpret_cast<int32_t *>(edt_smem); // [n][33]
+  float *h = reinterpret_cast<float *>(edt_smem); // [n][33]
   const uint32_t x0 = blockIdx.x * 32, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const uint64_t base = (uint64_t)blockIdx.y * line_stride + x0;
   for (uint32_t idx = threadIdx.x; idx < n * 32; idx += blockDim.x) {
     const uint32_t u = idx >> 5, xl = idx & 31;
     const int32_t g = x0 + xl < nx ? __ldg(in + base + xl + (uint64_t)u * stride) : kEdtInf;
-    h[u * 33 + xl] = g + (int32_t)(u * u);
+    h[u * 33 + xl] = (float)(g + (int32_t)(u * u)); // exact below 2^24; kEdtInf + u^2 rounds (harmless)
   }
   __syncthreads();
   for (uint32_t xl = warp; xl < 32 && x0 + xl < nx; xl += 8) {
-    int32_t best[8], m2u[8];
+    float best[8], m2u[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-      best[k] = 0x7FFFFFFF;
-      m2u[k] = -2 * (int32_t)(lane + 32 * k);
+      best[k] = 3.0e38f;
+      m2u[k] = -2.0f * (float)(lane + 32 * k);
     }
-    const int32_t *col = h + xl;
+    const float *col = h + xl;
     if (n <= 128) { // four outputs per lane
 #pragma unroll 4
       for (uint32_t i = 0; i < n; ++i) {
-        const int32_t hv = col[i * 33];
+        const float hv = col[i * 33], fi = (float)i;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) best[k] = min(best[k], hv + m2u[k] * (int32_t)i);
+        for (int k = 0; k < 4; ++k) best[k] = fminf(best[k], dm::fma_(m2u[k], fi, hv));
       }
     } else { // eight
 #pragma unroll 2
       for (uint32_t i = 0; i < n; ++i) {
-        const int32_t hv = col[i * 33];
+        const float hv = col[i * 33], fi = (float)i;
 #pragma unroll
-        for (int k = 0; k < 8; ++k) best[k] = min(best[k], hv + m2u[k] * (int32_t)i);
+        for (int k = 0; k < 8; ++k) best[k] = fminf(best[k], dm::fma_(m2u[k], fi, hv));
       }
     }
     __syncwarp(); // every lane has read the whole column: it may now take the results
@@ -323,8 +328,8 @@ __global__ void __launch_bounds__(256) edt_lines_bf_kernel(const int32_t *in, vo
     for (int k = 0; k < 8; ++k) {
       const uint32_t u = lane + 32 * k;
       if (u < n) {
-        const int32_t v = best[k] + (int32_t)(u * u);
-        h[u * 33 + xl] = v >= kEdtInf ? kEdtInf : v;
+        const float v = dm::add_(best[k], (float)(u * u));
+        h[u * 33 + xl] = v >= 268435456.0f ? (float)kEdtInf : v;
       }
     }
   }
@@ -332,12 +337,12 @@ __global__ void __launch_bounds__(256) edt_lines_bf_kernel(const int32_t *in, vo
   for (uint32_t idx = threadIdx.x; idx < n * 32; idx += blockDim.x) {
     const uint32_t u = idx >> 5, xl = idx & 31;
     if (x0 + xl >= nx) continue;
-    const int32_t v = h[u * 33 + xl];
+    const float v = h[u * 33 + xl];
     if (TO_FLOAT)
       reinterpret_cast<float *>(out_v)[base + xl + (uint64_t)u * stride] =
-          v >= kEdtInf ? INFINITY : dm::mul_(sqrtf((float)v), res);
+          v >= (float)kEdtInf ? INFINITY : dm::mul_(sqrtf(v), res);
     else
-      reinterpret_cast<int32_t *>(out_v)[base + xl + (uint64_t)u * stride] = v;
+      reinterpret_cast<int32_t *>(out_v)[base + xl + (uint64_t)u * stride] = (int32_t)v;
   }
 }
 
