@@ -420,19 +420,11 @@ doapp_status persistent_eligible(doapp_ctx *ctx, PersistParams *q, bool *ok) {
   const doapp_config &c = ctx->cfg;
   if (ctx->persist_mode == 0 || c.update_mode != DOAPP_UPDATE_KEEP_BEST || c.noise_waypoints != 1)
     return DOAPP_OK;
-  // several ranks: only with the peer mailboxes mapped (doapp_peer_import), else NCCL per iteration
-  if (ctx->comm && !(ctx->peer_ready && ctx->peer_nranks == ctx->nranks)) return DOAPP_OK;
+  // First generation: ONE rank only.  Its in-kernel mailbox exchange polls without a bound
+  // (ADVICE r01); several ranks take plan_pipeline_kernel (bounded waits, error word) or the
+  // launch-per-iteration planner with xchg_send_kernel / NCCL instead.
+  if (ctx->comm && ctx->nranks > 1) return DOAPP_OK;
   CostParams p = base_cost_params(ctx);
-  // With several ranks the verdict must be the same everywhere (a rank in the persistent kernel
-  // would wait for keys a rank on the NCCL path never sends): decide it from the largest shard,
-  // which every rank can compute, then fill the geometry for this rank's own shard.
-  if (ctx->comm && ctx->nranks > 1) {
-    CostParams pm = p;
-    pm.m = (uint32_t)((ctx->m_global + ctx->nranks - 1) / ctx->nranks);
-    PersistParams qm{};
-    CU(persistent_plan_config(pm, c.waypoint_dim, ctx->sm_count, &qm, ok));
-    if (!*ok) return DOAPP_OK;
-  }
   CU(persistent_plan_config(p, c.waypoint_dim, ctx->sm_count, q, ok));
   return DOAPP_OK;
 }
