@@ -362,6 +362,7 @@ def measure_plan(key, w, dd: Dist, local_rank, steps, warmup, full):
     clocks = sampler.stop()
     res = ctx.plan_wait()
     assert np.array_equal(res["best_traj"], first["best_traj"]), "bench result not reproducible"
+    stats = ctx.plan_stats() if persistent else None
 
     # ---- e2e: host buffers through doapp_plan, copies inside the timed region ---------
     for _ in range(warmup):
@@ -399,6 +400,11 @@ def measure_plan(key, w, dd: Dist, local_rank, steps, warmup, full):
         "gpu_launches": int(launches),
         "clocks": clocks, "best_score": r["best_score"],
     }
+    if stats and stats["cost_passes"]:
+        # the persistent planner costs two iterations per pass, speculatively: passes beyond
+        # iterations / 2 were voided by accepted keep-best updates (mis-speculation)
+        out["planner_stats"] = dict(stats, iterations=iters,
+                                    passes_per_iteration=stats["cost_passes"] / iters)
 
     # ---- rooflines of the dominant kernel ---------------------------------------------
     peaks = {}
@@ -542,7 +548,7 @@ def brief(o):
     """Sub-object of the `also` block: the numbers, without the prose."""
     keep = ("value", "unit", "ms_per_step", "iterations_per_sec", "us_per_iteration", "e2e",
             "gpu_launches", "parity_vs_1gpu", "grid_rebuilds_per_sec", "points_per_sec",
-            "best_score")
+            "best_score", "planner_stats")
     b = {k: o[k] for k in keep if k in o}
     b["workload"] = o["config"]["workload"]
     if "run" in o:

@@ -501,6 +501,10 @@ doapp_status enqueue_plan_pipeline(doapp_ctx *ctx, Persist2Params q, uint32_t it
   q.error = ctx->p2_error.p;
   q.stats = ctx->p2_stats.p;
   q.timeout_ns = 20ull * 1000000000ull; // a peer that never arrives: leave after 20 s
+  {
+    static const char *pv = getenv("DOAPP_P2_POLL_NS"); // tuning
+    q.poll_ns = pv ? (uint32_t)atoi(pv) : 100u;
+  }
   ctx->last_plan_mode = 1;
   const bool multi = ctx->comm && ctx->peer_ready;
   if (multi) {

@@ -171,6 +171,7 @@ struct Persist2Params {
   unsigned int *error;              // device word: set when the key exchange timed out
   unsigned long long *stats;        // [8] accepted updates, cost passes of CTA 0, SM clocks by phase (or nullptr)
   unsigned long long timeout_ns;
+  uint32_t poll_ns;                 // back-off between polls of the collect / send warps
 };
 cudaError_t pipeline_plan_config(const CostParams &p, int d, int sm_count, Persist2Params *q, bool *ok);
 cudaError_t launch_pipeline_plan(const Persist2Params &q, int d, int sm_count, cudaStream_t st);

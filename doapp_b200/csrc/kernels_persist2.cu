@@ -468,6 +468,7 @@ __global__ void __launch_bounds__(kP2MaxThreads) plan_pipeline_kernel(const __gr
             dead = true;
             break;
           }
+          __nanosleep(Q.poll_ns); // a spinning warp takes issue slots from the compute warps of its scheduler
         }
         if (dead) break;
         keys4[0] = warp_min_u64(mn);
@@ -503,6 +504,7 @@ __global__ void __launch_bounds__(kP2MaxThreads) plan_pipeline_kernel(const __gr
             dead = true;
             break;
           }
+          __nanosleep(Q.poll_ns);
         }
         if (dead) break;
       }
@@ -619,7 +621,10 @@ __global__ void __launch_bounds__(kP2MaxThreads) plan_pipeline_kernel(const __gr
             mn = sv < mn ? sv : mn;
           }
         }
-        if (!__all_sync(kFull, ok)) continue;
+        if (!__all_sync(kFull, ok)) {
+          __nanosleep(Q.poll_ns);
+          continue;
+        }
         mn = warp_min_u64(mn);
         const unsigned long long word = p2_pack(mn, want), cur = slast[a % kP2Ring];
         if (lane < Q.nranks)
