@@ -1,7 +1,7 @@
 # time cost-kernel build variants (scripts/micro/variants/lib_*.so) against the in-tree build
 mkdir -p gpurun_out/v
 for v in default $(ls scripts/micro/variants/ 2>/dev/null | sed 's/^lib_//; s/\.so$//'); do
-  for w in c4s c5; do
+  for w in c4 c4s; do
     if [ $v = default ]; then unset DOAPP_LIB; else export DOAPP_LIB=$PWD/scripts/micro/variants/lib_$v.so; fi
     timeout 300 python bench.py --workload $w --no-cpu --no-also --steps 5 > gpurun_out/v/${v}_$w.json 2> gpurun_out/v/${v}_$w.err
     python - <<PY
