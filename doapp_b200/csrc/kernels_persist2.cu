@@ -4,8 +4,9 @@
 //
 // Small problems (BASELINE config 2: 1024 samples x 64 waypoints x 100 iterations) are bound by
 // latency, not throughput: one iteration is 65 536 waypoint-samples, under half a wave.  The
-// kernel therefore runs ONE CTA PER SM with specialised warps and no CTA-wide barrier, atomic or
-// fence anywhere in the loop:
+// kernel therefore runs ONE CTA PER SM with specialised warps and no CTA-wide barrier, grid
+// barrier, contended atomic or fence anywhere in the loop (the only atomics are publishing
+// stores into a slot nobody else writes):
 //
 //   compute warps   one WAYPOINT per lane (up to 64 lanes = two warps per sample), TWO
 //                   ITERATIONS per pass: the halves of every packed fp32x2 register are the same
