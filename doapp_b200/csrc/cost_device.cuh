@@ -511,6 +511,42 @@ __device__ __forceinline__ void fk_points2(const dm::f2 (&th)[D], float rpy_s, f
   out[4] = p;
 }
 
+// Raw cell values of two points (threshold form, see GridDev::tx_bits): the occupancy byte or the
+// bits of the distance; a point outside the grid reads as "no hit" (0 / +inf).  Separating the
+// load from the predicate lets a kernel count the hits LATER (cost_kernel_pk counts a pair's
+// lookups one iteration after it issued them, so an L2 round trip hides behind arithmetic).
+template <int GM> __device__ __forceinline__ uint32_t raw_no_hit() {
+  return GM == GM_U8_CDG ? 0u : 0x7f800000u;
+}
+template <int GM> __device__ __forceinline__ int hit_of(uint32_t raw, float thr) {
+  if (GM == GM_U8_CDG) return raw != 0u;
+  return __uint_as_float(raw) <= thr; // generate_trajectories.cu:412
+}
+template <int GM>
+__device__ __forceinline__ void lookup2(const CostParams &P, P3v p, uint32_t *raw_lo, uint32_t *raw_hi) {
+  using namespace dm;
+  const GridDev &g = P.grid;
+  const f2 ax = f2_add(p.x, f2_splat(g.x_off)), ay = f2_add(p.y, f2_splat(g.y_off));
+  const f2 az = f2_add(p.z, f2_splat(0.0f));
+  const f2 fx = f2_div_fast_unguarded(ax, P.res_div), fy = f2_div_fast_unguarded(ay, P.res_div),
+           fz = f2_div_fast_unguarded(az, P.res_div);
+  auto half = [&](float axh, float ayh, float azh, float fxh, float fyh, float fzh) -> uint32_t {
+    const bool in = (__float_as_uint(axh) < g.tx_bits) & (__float_as_uint(ayh) < g.ty_bits) &
+                    (__float_as_uint(azh) < g.tz_bits);
+    const uint32_t ix = __float2uint_rz(fxh), iy = __float2uint_rz(fyh), iz = __float2uint_rz(fzh);
+    const uint32_t lin = (iz * g.ny + iy) * g.nx + ix;
+    uint32_t raw = raw_no_hit<GM>();
+    if (GM == GM_U8_CDG) {
+      if (in) raw = __ldg((const uint8_t *)g.cells + lin);
+    } else {
+      if (in) raw = __float_as_uint(__ldg((const float *)g.cells + lin));
+    }
+    return raw;
+  };
+  *raw_lo = half(f2_lo(ax), f2_lo(ay), f2_lo(az), f2_lo(fx), f2_lo(fy), f2_lo(fz));
+  *raw_hi = half(f2_hi(ax), f2_hi(ay), f2_hi(az), f2_hi(fx), f2_hi(fy), f2_hi(fz));
+}
+
 // collides<GM, true> on two points (threshold form, see GridDev::tx_bits)
 template <int GM>
 __device__ __forceinline__ void collides2(const CostParams &P, P3v p, float thr, int *hit_lo,
@@ -617,10 +653,20 @@ __device__ __forceinline__ void waypoint_collisions2(const CostParams &P, const 
   *coll_hi = c_hi;
 }
 
+// the reference chain's five link points of two waypoints: raw cell values, to be counted later
+template <int D, int GM>
+__device__ __forceinline__ void waypoint_lookups2(const CostParams &P, const dm::f2 (&x)[D],
+                                                  uint32_t (&raw_lo)[5], uint32_t (&raw_hi)[5]) {
+  P3v pts[5];
+  fk_points2<D>(x, P.rpy_s, P.rpy_c, pts);
+#pragma unroll
+  for (int l = 0; l < 5; ++l) lookup2<GM>(P, pts[l], &raw_lo[l], &raw_hi[l]);
+}
+
 // waypoint_cost<..., FAST = true> on two CONSECUTIVE WAYPOINTS (lo = w, hi = w + 1) of one
 // sample.  xprev / vprev are waypoint w - 1's angles and velocities; the hi half's priors are
 // the lo half's own results.  fine_lo / fine_hi as waypoint_cost's return value.
-template <int D, int GM, bool LIM, bool FKM>
+template <int D, int GM, bool LIM, bool FKM, bool COLL = true>
 __device__ __forceinline__ void waypoint_cost2(const CostParams &P, const dm::f2 (&x)[D],
                                                const float (&xprev)[D], const float (&vprev)[D],
                                                dm::f2 (&vnew)[D], dm::f2 *a2_out, dm::f2 *l2_out,
@@ -646,7 +692,12 @@ __device__ __forceinline__ void waypoint_cost2(const CostParams &P, const dm::f2
       l2 = f2_add(l2, f2_pack(__fmul_rn(h0, h0), __fmul_rn(h1, h1)));
     }
   }
-  waypoint_collisions2<D, GM, FKM>(P, x, coll_lo, coll_hi);
+  if (COLL) {
+    waypoint_collisions2<D, GM, FKM>(P, x, coll_lo, coll_hi);
+  } else { // the caller looks the link points up itself (waypoint_lookups2)
+    *coll_lo = 0;
+    *coll_hi = 0;
+  }
   *a2_out = a2;
   *l2_out = l2;
   *fine_lo = f_lo;

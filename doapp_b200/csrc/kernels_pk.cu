@@ -88,6 +88,17 @@ __global__ void __launch_bounds__(kPkThreads, DOAPP_PK_MINBLOCKS)
   float total = 0.0f, ltotal = 0.0f;
   int coll = 0;
   bool bad = false;
+  // Reference chain on a grid: the ten cell loads of a pair are issued in its iteration and
+  // COUNTED in the next one, so that an L1 miss (the 512^3 grid of BASELINE config 5 hits L1
+  // only 55 % of the time) waits behind a whole pair's arithmetic instead of ~60 instructions.
+  // Multi-part instances only (few samples, low occupancy: latency-bound): in the one-part
+  // instances the ten extra live registers cost more than the hidden latency gains (the 1M-sample
+  // launch hits L1 99.7 % of the time; measured 1327 -> 1361 us with deferral, 4.70e10 -> 4.95e10
+  // waypoint-samples/s on config 5).
+  constexpr bool DEFER = MP && GM != GM_NONE && !FKM;
+  uint32_t pend[10];
+#pragma unroll
+  for (int l = 0; l < 10; ++l) pend[l] = raw_no_hit<GM == GM_NONE ? GM_U8_CDG : GM>();
   for (uint32_t w = w0; w < w_end; w += 2) {
     const bool has_hi = w + 1 < w_end;
     f2 x[D], vnew[D];
@@ -99,7 +110,19 @@ __global__ void __launch_bounds__(kPkThreads, DOAPP_PK_MINBLOCKS)
     f2 a2, l2;
     int cw0, cw1;
     bool f0, f1;
-    waypoint_cost2<D, GM, LIM, FKM>(P, x, xprev, vprev, vnew, &a2, &l2, &cw0, &cw1, &f0, &f1);
+    waypoint_cost2<D, GM, LIM, FKM, !DEFER>(P, x, xprev, vprev, vnew, &a2, &l2, &cw0, &cw1, &f0, &f1);
+    if (DEFER) {
+      uint32_t rl[5], rh[5];
+      waypoint_lookups2<D, GM == GM_NONE ? GM_U8_CDG : GM>(P, x, rl, rh);
+#pragma unroll
+      for (int l = 0; l < 10; ++l) // the previous pair's lookups (cw0 / cw1 are zero here)
+        cw0 += hit_of<GM == GM_NONE ? GM_U8_CDG : GM>(pend[l], P.coll_dist);
+#pragma unroll
+      for (int l = 0; l < 5; ++l) {
+        pend[l] = rl[l];
+        pend[5 + l] = has_hi ? rh[l] : raw_no_hit<GM == GM_NONE ? GM_U8_CDG : GM>();
+      }
+    }
     const bool valid0 = f0 & fine1 & fine2, valid1 = f1 & f0 & fine1;
     fine2 = f0 & (P.fast_ok != 0);
     fine1 = f1 & (P.fast_ok != 0);
@@ -131,6 +154,10 @@ __global__ void __launch_bounds__(kPkThreads, DOAPP_PK_MINBLOCKS)
         sl[32] = f2_hi(l2);
       }
     }
+  }
+  if (DEFER) { // the last pair's lookups
+#pragma unroll
+    for (int l = 0; l < 10; ++l) coll += hit_of<GM == GM_NONE ? GM_U8_CDG : GM>(pend[l], P.coll_dist);
   }
   if (bad) {
     // Rare path: the whole run again, every waypoint with IEEE divides and full-range sin / cos
